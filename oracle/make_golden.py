@@ -1,0 +1,317 @@
+"""TEST INFRASTRUCTURE ONLY -- generates tests/golden/*.npz by running the UNMODIFIED reference
+(imported from /root/reference through oracle/ref_shim.py) on seeded synthetic inputs, and checks the
+CPU restatement (oracle/port.py) against it on the way.  Run in the build container:
+
+    python oracle/make_golden.py            # writes tests/golden/{meshes,pos_grid,pos_sphere,bar,align,writers}.npz
+
+The fixtures are the pin for the oracle (the reference has no golden vectors of its own).
+Nothing at test/bench time on the GPU box reads /root/reference.
+"""
+from __future__ import annotations
+
+import io
+import os
+import sys
+import types
+import contextlib
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import port  # noqa: E402
+from oracle.ref_shim import REFERENCE_ROOT, load_reference, scratch_cwd  # noqa: E402
+from animsnapbases_b200 import synth  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def rel(a, b):
+    a, b = np.asarray(a, float), np.asarray(b, float)
+    return float(np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300))
+
+
+# ------------------------------------------------------------------------------------------------ meshes
+def make_meshes():
+    data = os.path.join(REFERENCE_ROOT, "data")
+    out = {}
+    for name in ("bunny", "armadillo", "sphere"):
+        v, t = synth.read_obj_mesh(os.path.join(data, f"{name}.obj"))
+        out[f"{name}_verts"] = v
+        out[f"{name}_tris"] = t.astype(np.int32)
+    v, tets, tris = synth.read_medit_mesh(os.path.join(data, "bar.mesh"))
+    out["bar_verts"], out["bar_tets"], out["bar_tris"] = v, tets.astype(np.int32), tris.astype(np.int32)
+    np.savez_compressed(os.path.join(GOLD, "meshes.npz"), **out)
+    print("meshes:", {k: v.shape for k, v in out.items()})
+
+
+# ------------------------------------------------------------------------------------------------ reference drivers
+def ref_pos_objects(verts_f32, tris, mass, rest_shape, support, K, bases_type, splocs=None,
+                    min_dist=0.1, max_dist=0.25):
+    """Build reference posSnapshots/posComponents with object.__new__ (bypasses h5py)."""
+    from snapbases.posComponents import posComponents
+    from snapbases.posSnapshots import posSnapshots
+    from utils.support import GeodesicDistanceComputation
+
+    ps = object.__new__(posSnapshots)
+    ps.verts = np.asarray(verts_f32).astype(float)
+    ps.tris = tris
+    ps.frs, ps.nVerts, _ = ps.verts.shape
+    ps.rest_shape = rest_shape
+    ps.snapTensor = ps.verts.copy()
+    ps.mass = mass.copy()
+    ps.massL = np.sqrt(mass)            # == diagonal of cholesky(diag(m)), posSnapshots.py:156-159
+    ps.invMassL = 1.0 / ps.massL
+    ps.snapTensor *= ps.massL[:, None]  # posSnapshots.py:82
+    ps.mean = ps.snapTensor[0].copy() if rest_shape == "first" else np.mean(ps.snapTensor, axis=0)
+    rest = ps.verts[0] if rest_shape == "first" else np.mean(ps.verts, axis=0)
+    ps.compute_geodesic_distance = GeodesicDistanceComputation(rest, tris)
+    ps.pre_scale_factor = 1
+    ps.standarize()
+
+    pc = object.__new__(posComponents)
+    pc.basesType = bases_type
+    pc.pos_snapshots = ps
+    pc.numComp = K
+    pc.support = support
+    pc.storeSingVal = False
+    pc.comps = pc.weigs = None
+    pc.smooth_min_dist, pc.smooth_max_dist = min_dist, max_dist
+    pc.fileNameBases = "q_pos_"
+    sp = splocs or dict(max_itrs=1, admm=1, lam=2.0, rho=10.0)
+    pc.param = types.SimpleNamespace(splocs_max_itrs=sp["max_itrs"], splocs_admm_num_itrs=sp["admm"],
+                                     splocs_lambda=sp["lam"], splocs_rho=sp["rho"], q_standarize=True,
+                                     q_orthogonal=False, q_massWeight=True)
+    return ps, pc
+
+
+def run_ref_pos(pc, capture_splocs):
+    """Runs extract_k_components; captures SPLOCS' discarded (W, C) by wrapping the module-level
+    `tensordot` (last call with axes == (1, 0) is posComponents.py:183)."""
+    import snapbases.posComponents as mod
+    captured = {}
+    orig = mod.tensordot
+
+    def spy(a, b, axes=2):
+        if axes == (1, 0):
+            captured["W"], captured["C"] = np.array(a, copy=True), np.array(b, copy=True)
+        return orig(a, b, axes)
+
+    log = io.StringIO()
+    mod.tensordot = spy
+    try:
+        with contextlib.redirect_stdout(log):
+            pc.extract_k_components(None)
+    finally:
+        mod.tensordot = orig
+    return captured, log.getvalue()
+
+
+def pos_case(name, verts0, tris, F, K, n_bumps, sigma, splocs, seed):
+    verts0, _, _ = synth.normalize_unit_cube(verts0)
+    anim = synth.bump_animation(verts0, F, n_bumps=n_bumps, sigma=sigma, seed=seed)
+    anim = port.align_frames(anim.astype(np.float64), rigid=False)          # "_centered" pre-alignment
+    mass = synth.lumped_vertex_masses(anim[0].astype(float), tris)
+    out = dict(anim=anim, tris=tris.astype(np.int32), mass=mass, K=K, splocs=np.array(
+        [splocs["max_itrs"], splocs["admm"], splocs["lam"], splocs["rho"]], float))
+
+    # ---- reference: local support + SPLOCS
+    ps, pc = ref_pos_objects(anim, tris, mass, "first", "local", K, "SPLOCS", splocs)
+    cap, log = run_ref_pos(pc, True)
+    out.update(X=ps.snapTensor.copy(), mean=ps.mean.copy(), scale=ps.pre_scale_factor,
+               comps_local=pc.comps.copy(), weigs_local=pc.weigs.copy(), meas_local=pc.measures_at_largeDeforVerts,
+               splocs_W=cap["W"], splocs_C=cap["C"], splocs_log=np.array(log))
+    geo_ids = np.array([0, len(verts0) // 3, len(verts0) - 1])
+    out["geo_ids"] = geo_ids
+    out["geo_phi"] = np.array([ps.compute_geodesic_distance(int(i)) for i in geo_ids])
+    # ---- reference: global support PCA
+    ps2, pc2 = ref_pos_objects(anim, tris, mass, "first", "global", K, "PCA")
+    run_ref_pos(pc2, False)
+    out.update(comps_global=pc2.comps.copy(), weigs_global=pc2.weigs.copy(), meas_global=pc2.measures_at_largeDeforVerts)
+    # post-process (standardised, mass-weighted, not orthogonalised / orthogonalised)
+    with contextlib.redirect_stdout(io.StringIO()):
+        pc2.param.q_orthogonal = False
+        pc2.post_process_components()
+    out["post_global"] = pc2.comps.copy()
+
+    # ---- port vs reference
+    prep = port.prepare_snapshots(anim, mass, "first")
+    assert np.array_equal(prep["snapTensor"], ps.snapTensor), "standardise mismatch"
+    geo = port.GeodesicHeat(anim[0].astype(float), tris)
+    for i, gid in enumerate(geo_ids):
+        assert rel(geo(int(gid)), out["geo_phi"][i]) < 1e-9, "geodesic mismatch"
+    C, W, meas, picked, R = port.extract_k_components(prep["snapTensor"], K, "local", geo)
+    assert np.array_equal(C, out["comps_local"]) and np.array_equal(W, out["weigs_local"]), "deflation(local) mismatch"
+    assert np.array_equal(meas, out["meas_local"])
+    out["picked_local"] = picked
+    Wf, Cf, hist, centres = port.splocs_glob_optimization(prep["snapTensor"], C, W, R, geo, splocs["max_itrs"],
+                                                          splocs["admm"], splocs["lam"], splocs["rho"])
+    assert rel(Wf, cap["W"]) < 1e-12 and rel(Cf, cap["C"]) < 1e-12, ("splocs mismatch", rel(Wf, cap["W"]), rel(Cf, cap["C"]))
+    out["splocs_hist"], out["splocs_centres"] = hist, centres
+    Cg, Wg, measg, pickedg, _ = port.extract_k_components(prep["snapTensor"], K, "global")
+    assert np.array_equal(Cg, out["comps_global"]) and np.array_equal(Wg, out["weigs_global"])
+    out["picked_global"] = pickedg
+    post = port.post_process_pos(Cg, prep["mean"], prep["pre_scale_factor"], prep["invMassL"], True, False, True)
+    assert np.array_equal(post, out["post_global"])
+    np.savez_compressed(os.path.join(GOLD, f"{name}.npz"), **out)
+    print(f"{name}: N={len(verts0)} F={F} K={K}  port == reference (deflation bit-equal, splocs rel "
+          f"{rel(Wf, cap['W']):.1e}/{rel(Cf, cap['C']):.1e})")
+
+
+# ------------------------------------------------------------------------------------------------ bar / constraints
+def bar_case():
+    from snapbases.constraintsComponents import constraintsComponents
+    from snapbases.nonlinear_snapshots import nonlinearSnapshots
+
+    m = np.load(os.path.join(GOLD, "meshes.npz"))
+    verts, tets = m["bar_verts"], m["bar_tets"].astype(np.int64)
+    tets = tets[:600]
+    e, p, F = len(tets), 3, 24
+    snaps = synth.tet_rotation_snapshots(verts, tets, F, seed=0)           # (F, 3e, 3)
+    mass = synth.tet_element_masses(verts, tets, p)
+
+    param = types.SimpleNamespace(constProj_massWeight=True, constProj_standarize=True, constProj_orthogonal=True,
+                                  deim_desired_num_components=200, constProj_bases_interpolation_type="deim",
+                                  constProj_snapshots_type="tets_deformation_gradient", constProj_output_directory="")
+    ns = object.__new__(nonlinearSnapshots)
+    ns.param = param
+    ns.constraintsSize, ns.num_constained_elements, ns.dim, ns.frs = p, e, 3, F
+    ns.rest_shape = "first"
+    ns.snapTensor = snaps.copy()
+    ns.mass = mass.copy()
+    ns.massL = np.sqrt(mass)
+    ns.invMassL = 1.0 / ns.massL
+    ns.snapTensor *= ns.massL[:, None]
+    ns.standarize()
+    cc = object.__new__(constraintsComponents)
+    cc.param, cc.nonlinearSnapshots = param, ns
+    cc.storeSingVal, cc.file_name_sing, cc.support = False, "", "global"
+    cc.geom_interpol_verts = []
+    cc.comps = None
+
+    out = dict(snaps=snaps, mass=mass, tets=tets.astype(np.int32), X=ns.snapTensor.copy(), mean=ns.mean,
+               scale=ns.pre_scale_factor)
+    rows = []
+    writer = types.SimpleNamespace(writerow=lambda r: rows.append(list(r)))
+    with contextlib.redirect_stdout(io.StringIO()):
+        cc.compute_pod_for_vectorized_nonlinear_snapshots_tensor(writer)
+    out["pod_comps"] = cc.comps.copy()
+    out["pod_sing"] = np.array([r[1] for r in rows])
+    with contextlib.redirect_stdout(io.StringIO()):
+        cc.post_process_components()
+    out["post_comps"] = cc.comps.copy()
+    out["post_snap"] = ns.snapTensor.copy()
+    with contextlib.redirect_stdout(io.StringIO()):
+        cc.deim()
+    out["deim_Pt"], out["deim_alpha"], out["deim_ranges"] = cc.geom_Pt, cc.geom_alpha, cc.geom_alpha_ranges
+    with contextlib.redirect_stdout(io.StringIO()):
+        rec = cc.geom_constructed(10, "train")
+    out["deim_rec10_err"] = np.array([cc.frobenius_error(ns.snapTensor, rec)])
+
+    # port checks
+    prep = port.prepare_snapshots(snaps, mass, "first")
+    assert np.array_equal(prep["snapTensor"], out["X"])
+    C, S = port.pod_vectorized(prep["snapTensor"], 200)
+    assert np.array_equal(C, out["pod_comps"]) and np.array_equal(S, out["pod_sing"])
+    pc, psn = port.post_process_constraints(C, prep["snapTensor"], prep["mean"], prep["pre_scale_factor"],
+                                            prep["invMassL"], True, True, True)
+    assert np.array_equal(pc, out["post_comps"]) and np.array_equal(psn, out["post_snap"])
+    d = port.deim(pc, p)
+    assert np.array_equal(d["Pt"], out["deim_Pt"]) and np.array_equal(d["alpha"], out["deim_alpha"])
+    rec_p = port.deim_reconstruct(pc, psn, d["alpha"][:10], 10)      # reference quirk: alpha used as rows (H6)
+    assert abs(port.frobenius_error(psn, rec_p) - out["deim_rec10_err"][0]) < 1e-9 * out["deim_rec10_err"][0]
+
+    # ---- block deflation + block DEIM (reference)
+    ns2 = object.__new__(nonlinearSnapshots)
+    ns2.__dict__.update(ns.__dict__)
+    ns2.snapTensor = out["X"].copy()
+    cc2 = object.__new__(constraintsComponents)
+    cc2.param = types.SimpleNamespace(**{**param.__dict__, "deim_desired_num_components": 5,
+                                         "constProj_bases_interpolation_type": "deim_block_form"})
+    cc2.nonlinearSnapshots, cc2.storeSingVal, cc2.support, cc2.geom_interpol_verts = ns2, False, "global", []
+    with contextlib.redirect_stdout(io.StringIO()):
+        cc2.compute_nonlinearity_bases_blocks(None)
+    out.update(blk_comps=cc2.comps.copy(), blk_weigs=cc2.weigs.copy(), blk_meas=cc2.measures_at_largeDeforVerts,
+               blk_points=cc2.largeDeforPoints, blk_rows=cc2.largeDeforBlocks)
+    with contextlib.redirect_stdout(io.StringIO()):
+        cc2.post_process_components()
+        cc2.deim_blocksForm()
+    out.update(blk_post=cc2.comps.copy(), blk_deim_Pt=cc2.geom_Pt, blk_deim_alpha=cc2.geom_alpha)
+    Cb, Wb, mb, sidx, sp_ = port.nonlinearity_bases_blocks(out["X"], e, p, 5)
+    assert np.array_equal(Cb, out["blk_comps"]) and np.array_equal(Wb, out["blk_weigs"]) and np.array_equal(mb, out["blk_meas"])
+    pcb, _ = port.post_process_constraints(Cb, out["X"], prep["mean"], prep["pre_scale_factor"], prep["invMassL"], True, True, True)
+    assert np.array_equal(pcb, out["blk_post"])
+    db = port.deim_blocks(pcb, p)
+    assert np.array_equal(db["Pt"], out["blk_deim_Pt"]) and np.array_equal(db["alpha"], out["blk_deim_alpha"])
+    np.savez_compressed(os.path.join(GOLD, "bar.npz"), **out)
+    print(f"bar: e={e} p={p} F={F}: pod/post/deim/blocks port == reference; Pt[:8]={out['deim_Pt'][:8]}")
+
+
+# ------------------------------------------------------------------------------------------------ alignment + writers
+def align_case():
+    from utils.process import find_rbm_procrustes, transform
+
+    m = np.load(os.path.join(GOLD, "meshes.npz"))
+    v0, _, _ = synth.normalize_unit_cube(m["sphere_verts"])
+    rng = np.random.default_rng(3)
+    F = 6
+    frames = []
+    for f in range(F):
+        R = synth._rot(rng.standard_normal(3), 0.4 * rng.standard_normal())
+        if f == 4:
+            R = R @ np.diag([1.0, 1.0, -1.0])      # reflection: exercises the det(R) < 0 branch
+        frames.append((v0 + 0.01 * rng.standard_normal(v0.shape)) @ R.T + 0.1 * rng.standard_normal(3))
+    frames[0] = v0
+    frames = np.array(frames, np.float32)
+    out = dict(frames=frames)
+    for rigid in (True, False):
+        ref = []
+        for v in frames:
+            M = find_rbm_procrustes(v, frames[0], rigid)
+            ref.append(transform(v, M))
+        ref = np.array(ref, np.float32)
+        mine = port.align_frames(frames, rigid)
+        assert np.array_equal(mine, ref), "align mismatch"
+        out[f"aligned_rigid{int(rigid)}"] = ref
+    pre, mean, scale = port.preprocess_unit_cube(frames)
+    out.update(pre=pre, pre_mean=mean, pre_scale=np.array([scale]))
+    np.savez_compressed(os.path.join(GOLD, "align.npz"), **out)
+    print("align: port == reference (rigid and translation-only, incl. reflection branch)")
+
+
+def writers_case():
+    import utils.utils as ru
+    rng = np.random.default_rng(5)
+    B = rng.standard_normal((4, 7, 3))
+    with scratch_cwd() as d:
+        ru.store_components(os.path.join(d, "q_pos_"), 9, 4, 7, 3, B, ".bin", "K")
+        ref = open(os.path.join(d, "q_pos_F9K4.bin"), "rb").read()
+        pts = np.array([5, 3, 11, 2])
+        with contextlib.redirect_stdout(io.StringIO()):
+            ru.store_interpol_points_vector(os.path.join(d, "pts_"), 9, 4, pts, ".bin")
+        refp = open(os.path.join(d, "pts_F9K4_points4.bin"), "rb").read()
+    assert port.components_bin_bytes(B) == ref and port.points_bin_bytes(pts) == refp
+    np.savez_compressed(os.path.join(GOLD, "writers.npz"), B=B, bin=np.frombuffer(ref, np.uint8), pts=pts,
+                        pts_bin=np.frombuffer(refp, np.uint8))
+    print("writers: .bin layouts pinned")
+
+
+def main():
+    os.makedirs(GOLD, exist_ok=True)
+    load_reference()
+    make_meshes()
+    with scratch_cwd():
+        m = np.load(os.path.join(GOLD, "meshes.npz"))
+        gv, gt = synth.grid_mesh(24, 20)
+        pos_case("pos_grid", gv, gt, F=24, K=10, n_bumps=5, sigma=0.12,
+                 splocs=dict(max_itrs=3, admm=5, lam=2.0, rho=10.0), seed=0)
+        pos_case("pos_sphere", m["sphere_verts"], m["sphere_tris"].astype(np.int64), F=30, K=12, n_bumps=6, sigma=0.2,
+                 splocs=dict(max_itrs=2, admm=10, lam=2.0, rho=10.0), seed=1)
+        bar_case()
+        align_case()
+        writers_case()
+
+
+if __name__ == "__main__":
+    main()
