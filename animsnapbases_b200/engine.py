@@ -1,0 +1,346 @@
+"""Host-side orchestration of the basis hot path: which kernel runs when, on which shard, and which tiny
+collective follows.  All arithmetic is in `ops` (libasb.so kernels); this file only sequences launches, owns
+the device tensors and calls torch.distributed where a step has a real exchange.
+
+Row sharding: the vertex / constraint-row axis is split into contiguous blocks, one per
+rank.  Per-row tensors (X, R, C, Z, U, Lambda, e) are sharded; F x K, K x K, F x F results are all-reduced and
+kept replicated; argmax steps become a (value, index) pair reduction with the np.argmax tie rule.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from .ops import F64, I32, I64, pad_ld
+
+
+# ====================================================================================== communication
+class Comm:
+    """Thin wrapper over torch.distributed (NCCL on GPUs, gloo in the CPU tests). world == 1 -> no-ops."""
+
+    def __init__(self, enabled: bool | None = None):
+        import torch.distributed as dist
+        self.dist = dist
+        on = dist.is_available() and dist.is_initialized() if enabled is None else enabled
+        self.world = dist.get_world_size() if on else 1
+        self.rank = dist.get_rank() if on else 0
+
+    def allreduce_sum(self, t):
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return t
+
+    def allreduce_max(self, t):
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return t
+
+    def argmax_pairs(self, val, idx):
+        """Cross-rank (value, global index) reduction for a batch of pairs: largest value wins, ties go to the
+        lowest index (np.argmax).  val: (B,) f64, idx: (B,) i64; both are overwritten with the global result."""
+        if self.world == 1:
+            return val, idx
+        vals = [torch.empty_like(val) for _ in range(self.world)]
+        idxs = [torch.empty_like(idx) for _ in range(self.world)]
+        self.dist.all_gather(vals, val)
+        self.dist.all_gather(idxs, idx)
+        V = torch.stack(vals)                      # (world, B)
+        J = torch.stack(idxs)
+        m = V.max(dim=0).values
+        big = torch.iinfo(torch.int64).max
+        cand = torch.where(V == m[None], J, torch.full_like(J, big))
+        val.copy_(m)
+        idx.copy_(cand.min(dim=0).values)
+        return val, idx
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+
+
+@dataclass
+class Shard:
+    n_global: int
+    row0: int
+    n: int          # local rows
+    ld: int         # padded plane stride
+
+    @staticmethod
+    def make(n_global: int, world: int = 1, rank: int = 0, multiple: int = 32) -> "Shard":
+        per = (n_global + world - 1) // world
+        per = (per + multiple - 1) // multiple * multiple
+        row0 = min(n_global, rank * per)
+        n = max(0, min(n_global, row0 + per) - row0)
+        return Shard(n_global, row0, n, pad_ld(max(n, 1)))
+
+
+# ====================================================================================== snapshots (k2)
+@dataclass
+class SnapshotState:
+    X: torch.Tensor            # (F, 3, ld) planar, standardised
+    mean: torch.Tensor         # (3, ld)
+    scale: float               # pre_scale_factor
+    massL: torch.Tensor | None
+    invMassL: torch.Tensor | None
+    shard: Shard
+    frames: int
+
+
+def prepare_snapshots(ops, comm, verts_local, mass_local, rest_shape, shard, standarize=True, mass_weight=True):
+    """posSnapshots.do_snapshots_precomputations + standarize (snapbases/posSnapshots.py:64-105, :163-172) and
+    nonlinearSnapshots.snapshots_prepare/standarize (snapbases/nonlinear_snapshots.py:74-96, :268-288).
+    verts_local: device tensor (F, n_local, 3) float32 or float64 (this rank's rows);  mass_local: host array."""
+    F = verts_local.shape[0]
+    massL = invMassL = None
+    if mass_weight:
+        m = np.asarray(mass_local, dtype=np.float64)
+        mL = np.sqrt(m)                                    # cholesky of a diagonal matrix
+        inv = np.zeros_like(mL)
+        nz = mL != 0
+        inv[nz] = 1.0 / mL[nz]
+        massL, invMassL = ops.to_device(mL), ops.to_device(inv)
+    X = ops.ingest(verts_local, massL, shard.ld)
+    if rest_shape == "first":
+        mean = X[0].clone()
+    elif rest_shape == "average":
+        mean = ops.col_mean(X)
+    else:
+        print("Error! unknown rest shape: ", rest_shape)
+        raise SystemExit(1)
+    scale = 1
+    if standarize:
+        stats = ops.center_stats(X, mean, shard.n)
+        comm.allreduce_sum(stats)
+        s1, s2 = (float(v) for v in stats.tolist())
+        cnt = float(F) * shard.n_global * 3.0
+        mu = s1 / cnt
+        var = s2 / cnt - mu * mu
+        scale = 1.0 / np.sqrt(var)
+        ops.center_apply(X, mean, scale, shard.n)
+    return SnapshotState(X, mean, scale, massL, invMassL, shard, F)
+
+
+# ====================================================================================== deflation (k3-k9)
+def deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1, dmax=0.25, block=8,
+            keep_residual=True):
+    """Greedy deflation of snapbases/posComponents.py:67-122 on a row shard.
+
+    The residual R is explicit (like the reference) but the K rank-1 updates are applied `block` at a time
+    (asb_rank_update); inside a block the pending components are accounted for implicitly, so every component
+    costs ONE read pass over R (asb_deflate_gemv) plus 2/block of a read+write pass.
+    Returns C (K,3,ld), W (F,Kp), meas (K,3) = [sigma0, |R|_F, |R|_F^2], picked (K,) global vertex ids, R."""
+    F, _, ld = X.shape
+    N, row0 = shard.n, shard.row0
+    Kp = (K + 3) // 4 * 4
+    R = X.clone()
+    W = ops.zeros((F, Kp))
+    C = ops.zeros((K, 3, ld))
+    meas = ops.zeros((K, 3))
+    picked = ops.zeros((K,), I64)
+    e = ops.vertex_energy(R, N)
+    g = ops.empty((3, ld))
+    traj = ops.zeros((3, F))
+    coef = ops.zeros((16,))
+    scal = ops.zeros((2,))
+    val = ops.zeros((1,))
+    idx = ops.zeros((1,), I64)
+    s = ops.zeros((1, ld)) if local_support else None
+    k0 = 0
+    for k in range(K):
+        ops.argmax_first(e, N, row0, val, idx)
+        comm.argmax_pairs(val, idx)
+        picked[k:k + 1].copy_(idx)
+        if comm.world > 1:
+            traj.zero_()
+        ops.gather_traj(R, N, idx, row0, W, k0, C, k - k0, traj)
+        comm.allreduce_sum(traj)
+        ops.traj_rank1(traj, F, local_support, W, k, k0, coef, scal)
+        if local_support:
+            geodesic.support(idx, 0, 1.0, dmin, dmax, row0, N, s)
+        ops.deflate_gemv(R, N, W, k, g)
+        ops.deflate_finish(g, C, k, k0, coef, s[0] if local_support else None, scal, e, N, meas[k])
+        if comm.world > 1:
+            comm.allreduce_sum(meas[k, 2:3])
+            meas[k, 1:2] = torch.sqrt(meas[k, 2:3])
+        if k - k0 + 1 == block or k == K - 1:
+            ops.rank_update(R, N, W, C, k0, k - k0 + 1, e)
+            k0 = k + 1
+    return C, W, meas, picked, (R if keep_residual else None)
+
+
+# ====================================================================================== SPLOCS (k10-k14)
+def splocs(ops, comm, X, shard, C, W, K, geodesic, num_iters, num_admm, lam, rho, dmin=0.1, dmax=0.25, log=print):
+    """SPLOCS global optimisation of snapbases/posComponents.py:132-189 in Gram form.
+
+    Per outer iteration:  P = X C^T, Q = C C^T (DMMA, all-reduced)  ->  Gauss-Seidel weight sweep on F x K
+    -> centre argmax + geodesic support maps (memoised)  ->  H^-1 = (W^T W + rho I)^-1,  B0 = (H^-1 W^T) X
+    -> num_admm fused iterations (C is the ADMM variable Z; the reference sets C = Z, :181)  -> energy.
+    C (K,3,ld) and W (F,Kp) are updated in place; U persists over outer iterations (:136).
+    Returns per-iteration (energy, E_rms) and the centre ids."""
+    F, _, ld = X.shape
+    N, row0 = shard.n, shard.row0
+    M = 3 * ld
+    Xm, Cm = X.view(F, M), C.view(K, M)
+    Kp = W.shape[1]
+    U = ops.zeros((K, 3, ld))
+    Lambda = ops.zeros((K, ld))
+    B0 = ops.empty((K, 3, ld))
+    H = ops.zeros((K, Kp))
+    Hinv = ops.zeros((K, Kp))
+    Hr = ops.zeros((K, Kp))
+    Fp = (F + 1) // 2 * 2
+    Aw = ops.zeros((K, Fp))
+    WQ = ops.zeros((F, Kp))
+    info = ops.zeros((1,), I32)
+    val = ops.zeros((K,))
+    idx = ops.zeros((K,), I64)
+    sp = ops.zeros((K,))
+    scal3 = ops.zeros((3,))
+    # |X|_F^2 (for the energy through Gram identities)
+    ex = ops.vertex_energy(X, N)
+    xnorm2 = ex[:N].sum().reshape(1)
+    comm.allreduce_sum(xnorm2)
+    xnorm2 = float(xnorm2.item())
+
+    def grams():
+        P = ops.gemm_nt(Xm, F, Cm, K, M)
+        Q = ops.gemm_nt(Cm, K, Cm, K, M, symmetric=True)
+        comm.allreduce_sum(P)
+        comm.allreduce_sum(Q)
+        return P, Q
+
+    def centres(with_sparsity):
+        ops.component_centers(C, Lambda if with_sparsity else None, K, N, row0, val, idx, sp)
+        comm.argmax_pairs(val, idx)
+        if with_sparsity:
+            comm.allreduce_sum(sp)
+
+    P, Q = grams()
+    centres(False)
+    hist, centre_hist = [], []
+    for it in range(num_iters):
+        ops.weights_sweep(P, Q, W, F, K)
+        ids = idx.tolist()                                              # K ints -> host (memoisation key)
+        centre_hist.append(ids)
+        geodesic.support(idx, 1, lam, dmin, dmax, row0, N, Lambda, ids_host=ids)
+        ops.gram_small(W, F, K, rho, H)                                 # H = W^T W + rho I
+        ops.spd_inverse(H, K, Hinv, info)
+        ops.small_gemm(0, 1, K, F, K, 1.0, Hinv, W, Aw)                 # Aw = H^-1 W^T   (K x F)
+        ops.gemm_nn(Aw, K, F, Xm, M, 1.0, B0.view(K, M))                # B0 = H^-1 (W^T X)
+        ops.axpby(Hr.view(1, -1), rho, Hinv.view(1, -1), None, 0.0, None, K * Kp)
+        for _ in range(num_admm):
+            ops.admm_iter(Hr, B0, C, U, Lambda, K, N, 1.0 / rho)
+        P, Q = grams()
+        centres(True)
+        # energy = |X - W C|^2 + sum Lambda |c|  via  |X|^2 - 2 <W, P> + <W Q, W>
+        ops.small_gemm(0, 0, F, K, K, 1.0, W, Q, WQ)
+        ops.batched_dot(W.view(1, -1), P_pad(ops, P, Kp).view(1, -1), F * Kp, scal3[0:1])
+        ops.batched_dot(W.view(1, -1), WQ.view(1, -1), F * Kp, scal3[1:2])
+        scal3[2:3] = sp.sum()
+        wp, wqw, sparsity = (float(v) for v in scal3.tolist())
+        r2 = max(xnorm2 - 2.0 * wp + wqw, 0.0)
+        e_rms = np.sqrt(r2) / np.sqrt(3.0 * shard.n_global * F)
+        energy = r2 + sparsity
+        hist.append((energy, e_rms))
+        if int(info.item()) != 0:
+            raise FloatingPointError("SPLOCS: W^T W + rho I is not positive definite")
+        if log is not None and comm.rank == 0:
+            log("itr %03d, Energy =%f, Error =%f" % (it, energy, e_rms))
+    return np.array(hist), np.array(centre_hist)
+
+
+def P_pad(ops, P, Kp):
+    """P is (F, K) contiguous; W is (F, Kp). Return P with Kp columns (zero padded) for element-wise dots."""
+    if P.shape[1] == Kp:
+        return P
+    out = ops.zeros((P.shape[0], Kp))
+    out[:, :P.shape[1]] = P
+    return out
+
+
+# ====================================================================================== POD (k15)
+def pod(ops, comm, X, shard, k_desired):
+    """Tall-skinny PCA of the (3 ep x F) snapshot matrix (snapbases/constraintsComponents.py:298-320):
+    Gram X X^T on the DMMA pipe (+ all-reduce), F x F symmetric eigensolve (replicated), back-projection
+    U^T = S^-1 V^T X.  Returns comps (K,3,ld) planar, all F singular values (host, descending)."""
+    F, _, ld = X.shape
+    M = 3 * ld
+    Xm = X.view(F, M)
+    Fp = (F + 1) // 2 * 2
+    G = ops.zeros((F, Fp))
+    ops.gemm_nt(Xm, F, Xm, F, M, symmetric=True, out=G)
+    comm.allreduce_sum(G)
+    evals, info = ops.syevd(G, F)                       # rows of G = eigenvectors, ascending eigenvalues
+    ev = evals.cpu().numpy()
+    if int(info.item()) != 0:
+        raise FloatingPointError("syevd failed")
+    lam = ev[::-1].copy()
+    sig = np.sqrt(np.maximum(lam, 0.0))
+    K = min(int(k_desired), F)
+    floor = F * np.finfo(np.float64).eps * lam[0]      # Gram accuracy floor: modes below are undefined
+    inv = np.where(lam[:K] > floor, 1.0 / np.where(sig[:K] > 0, sig[:K], 1.0), 0.0)
+    order = ops.to_device(np.arange(F - 1, F - 1 - K, -1).astype(np.int64))
+    A = torch.index_select(G, 0, order).contiguous()    # descending order (data movement only)
+    comps = ops.empty((K, 3, ld))
+    ops.gemm_nn(A, K, F, Xm, M, 1.0, comps.view(K, M), row_scale=ops.to_device(inv))
+    return comps, sig
+
+
+# ====================================================================================== post-processing (k18)
+def orthogonalize_rows(ops, comm, T, shard, K):
+    """Per-dimension orthonormalisation of the K rows of T[:, d, :] (economic QR of the (N x K) matrix,
+    snapbases/constraintsComponents.py:431-433) by CGS2: Q equals LAPACK's up to the sign of each column."""
+    N = shard.n
+    h = ops.zeros((max(K, 1),))
+    nrm2 = ops.zeros((1,))
+    for d in range(3):
+        for k in range(K):
+            for _ in range(2):
+                if k > 0:
+                    ops.cgs_dots(T, k, d, N, h)
+                    comm.allreduce_sum(h[:k])
+                ops.cgs_project(T, k, d, N, h if k > 0 else None, nrm2)
+                comm.allreduce_sum(nrm2)
+            ops.row_scale(T, k, d, nrm2)
+    return T
+
+
+# ====================================================================================== DEIM (k19)
+def deim(ops, comm, C, shard, K):
+    """Classical DEIM point selection shared by x/y/z (snapbases/constraintsComponents.py:797-860).
+    C: (K, 3, ld) planar post-processed basis.  Returns Pt (K,) global row ids (host int64) or None if a residual
+    vanished (the reference prints an error and returns, :832-834)."""
+    N, row0 = shard.n, shard.row0
+    ld = C.shape[2]
+    Kp = (K + 3) // 4 * 4
+    Pt = ops.zeros((K,), I64)
+    e = ops.zeros((ld,))
+    a = ops.zeros((3, Kp))
+    ldv = K + 1
+    Vp = ops.zeros((3, ldv, ldv))
+    maxabs = ops.zeros((K,))
+    info = ops.zeros((1,), I32)
+    val = ops.zeros((1,))
+    idx = ops.zeros((1,), I64)
+    for k in range(K):
+        if k > 0:
+            if comm.world > 1:
+                Vp.zero_()
+            ops.deim_gather(C, N, row0, Pt, k, Vp)
+            comm.allreduce_sum(Vp)
+            ops.deim_solve(Vp, k, a, info)
+        ops.deim_residual(C, N, k, a, e, maxabs[k:k + 1])
+        ops.argmax_first(e, N, row0, val, idx)
+        comm.argmax_pairs(val, idx)
+        Pt[k:k + 1].copy_(idx)
+    comm.allreduce_max(maxabs)
+    mx = maxabs.cpu().numpy()
+    if int(info.item()) != 0:
+        raise FloatingPointError("DEIM: singular interpolation matrix at step %d" % int(info.item()))
+    # np.allclose(r, 0) <=> max|r| <= 1e-8
+    if K > 1 and np.any(mx[1:] <= 1e-8):
+        print("ERROR!: zero residual!!")
+        return None
+    return Pt.cpu().numpy()

@@ -1,0 +1,211 @@
+"""Heat-method geodesic distances on the GPU (reference: utils/support.py:139-208, GeodesicDistanceComputation).
+
+Set-up (once per mesh, like the reference's `__init__` which pre-factorises with SuperLU, utils/support.py:153-171)
+assembles the cotangent Laplacian `Lc`, the lumped areas `A`, the time step `t = 10 h^2` and the per-triangle /
+per-corner geometric constants on the host with numpy/scipy.sparse -- geometry only, no snapshot data.  Every
+*query* then runs on the device through libasb kernels:
+
+    u   = (A - t Lc)^-1 delta_idx          batched Jacobi-PCG   (SPD)
+    X   = -grad u / |grad u|               per triangle
+    div = integrated divergence            per-vertex gather over incident corners (deterministic)
+    phi = Lc^+ div                          batched Jacobi-PCG on -Lc (PSD, constant null space projected out)
+    phi -= min(phi); support map            fused in asb_support_map
+
+Several sources are solved at once (multi right-hand side); maps are memoised by vertex id because phi depends on
+the source vertex only (SPLOCS re-queries the same centres every outer iteration, posComponents.py:158-165).
+The mesh operator is global: with row-sharded snapshots every rank solves on the full mesh and keeps its row slice.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+from scipy import sparse
+
+
+def _veclen(v):
+    return np.sqrt(np.sum(v ** 2, axis=-1))
+
+
+def _normalized(v):
+    return v / _veclen(v)[..., None]
+
+
+def cotan_laplacian(verts, tris):
+    """Cotangent Laplacian (row sums zero, off-diagonals 0.5*(cot a + cot b)) and lumped vertex areas
+    (utils/support.py:81-136)."""
+    n = len(verts)
+    I, J, W = [], [], []
+    for i1, i2, i3 in ((0, 1, 2), (1, 2, 0), (2, 0, 1)):
+        a, b, c = tris[:, i1], tris[:, i2], tris[:, i3]
+        u = verts[b] - verts[a]
+        v = verts[c] - verts[a]
+        cot = (u * v).sum(axis=1) / _veclen(np.cross(u, v))
+        I += [b, c]
+        J += [c, b]
+        W += [0.5 * cot, 0.5 * cot]
+    L = sparse.csr_matrix((np.concatenate(W), (np.concatenate(I), np.concatenate(J))), shape=(n, n))
+    L = (L - sparse.diags(np.asarray(L.sum(axis=1)).ravel())).tocsr()
+    e1 = verts[tris[:, 1]] - verts[tris[:, 0]]
+    e2 = verts[tris[:, 2]] - verts[tris[:, 0]]
+    ta3 = 0.5 * _veclen(np.cross(e1, e2)) / 3.0
+    area = np.zeros(n)
+    for c in range(3):
+        area += np.bincount(tris[:, c], ta3, minlength=n)
+    return L, area
+
+
+class HeatGeodesics:
+    def __init__(self, ops, verts, tris, m: float = 10.0, tol: float = 1e-12, max_iter: int = 20000,
+                 check_every: int = 25):
+        self.ops = ops
+        verts = np.asarray(verts, dtype=np.float64)
+        tris = np.asarray(tris, dtype=np.int64)
+        self.n = n = len(verts)
+        self.T = len(tris)
+        self.ldx = (n + 31) // 32 * 32
+        self.tol, self.max_iter, self.check_every = tol, max_iter, check_every
+        e01 = verts[tris[:, 1]] - verts[tris[:, 0]]
+        e12 = verts[tris[:, 2]] - verts[tris[:, 1]]
+        e20 = verts[tris[:, 0]] - verts[tris[:, 2]]
+        area = 0.5 * _veclen(np.cross(e01, e12))
+        un = _normalized(np.cross(_normalized(e01), _normalized(e12)))
+        inv2a = (1.0 / (2.0 * area))[:, None]
+        # gradient constants in the order the kernel consumes them: (n x e01) u2 + (n x e12) u0 + (n x e20) u1
+        gconst = np.concatenate([np.cross(un, e01) * inv2a, np.cross(un, e12) * inv2a, np.cross(un, e20) * inv2a], axis=1)
+        # per-corner divergence constants (cot1, e1, cot2, e2) with the reference's 1/tan(arccos(.)) cotangents
+        dconst = np.empty((self.T, 3, 8))
+        for c, (i1, i2, i3) in enumerate(((0, 1, 2), (1, 2, 0), (2, 0, 1))):
+            v1, v2, v3 = tris[:, i1], tris[:, i2], tris[:, i3]
+            e1 = verts[v2] - verts[v1]
+            e2 = verts[v3] - verts[v1]
+            eo = verts[v3] - verts[v2]
+            with np.errstate(all="ignore"):
+                cot1 = 1 / np.tan(np.arccos((_normalized(-e2) * _normalized(-eo)).sum(axis=1)))
+                cot2 = 1 / np.tan(np.arccos((_normalized(-e1) * _normalized(eo)).sum(axis=1)))
+            dconst[:, c, 0] = cot1
+            dconst[:, c, 1:4] = e1
+            dconst[:, c, 4] = cot2
+            dconst[:, c, 5:8] = e2
+        # vertex -> incident corner CSR (corner id = 3 t + c), stable order = (c, t) like the reference's three passes
+        corner_vertex = tris.T.ravel()                              # c-major: corner (c, t) -> vertex
+        corner_id = (np.arange(self.T)[None, :] * 3 + np.arange(3)[:, None]).ravel()
+        order = np.argsort(corner_vertex, kind="stable")
+        vc_idx = corner_id[order].astype(np.int32)
+        vc_ptr = np.zeros(n + 1, dtype=np.int32)
+        np.cumsum(np.bincount(corner_vertex, minlength=n), out=vc_ptr[1:])
+
+        h = np.mean([_veclen(e01), _veclen(e12), _veclen(e20)])
+        self.t = m * h ** 2
+        Lc, va = cotan_laplacian(verts, tris)
+        heat = (sparse.diags(va) - self.t * Lc).tocsr()
+        pois = (-Lc).tocsr()
+        heat.sort_indices()
+        pois.sort_indices()
+        self.heat = self._upload_csr(heat)
+        self.pois = self._upload_csr(pois)
+        dh = heat.diagonal()
+        dp = pois.diagonal()
+        dp = np.where(dp > 0, dp, 1.0)
+        self.heat_dinv = self._pad(1.0 / dh)
+        self.pois_dinv = self._pad(1.0 / dp)
+        self.tri = ops.to_device(tris.astype(np.int32))
+        self.gconst = ops.to_device(np.ascontiguousarray(gconst))
+        self.dconst = ops.to_device(np.ascontiguousarray(dconst.reshape(self.T * 3, 8)))
+        self.vc_ptr = ops.to_device(vc_ptr)
+        self.vc_idx = ops.to_device(vc_idx)
+        self.stats = {"queries": 0, "cache_hits": 0, "solves": 0, "heat_iters": 0, "poisson_iters": 0}
+        self._cache = {}
+
+    def _pad(self, v):
+        out = np.zeros(self.ldx)
+        out[: self.n] = v
+        return self.ops.to_device(out)
+
+    def _upload_csr(self, m):
+        return (self.ops.to_device(m.indptr.astype(np.int32)), self.ops.to_device(m.indices.astype(np.int32)),
+                self.ops.to_device(m.data.astype(np.float64)))
+
+    # ------------------------------------------------------------------ batched PCG
+    def _pcg(self, csr, dinv, b, singular: bool, key: str):
+        """Solve A x = b for every row of b (B, ldx); returns x.  Jacobi preconditioner, device-resident scalars,
+        one host read of the residuals every `check_every` iterations."""
+        ops, n = self.ops, self.n
+        B = b.shape[0]
+        x = ops.zeros((B, self.ldx))
+        r = b.clone()
+        if singular:
+            ops.remove_mean(r, n)
+        z = ops.zeros((B, self.ldx))
+        ops.axpby(z, 1.0, r, dinv, 0.0, None, n)
+        p = z.clone()
+        Ap = ops.zeros((B, self.ldx))
+        rz = ops.zeros((B,))
+        rz_new = ops.zeros((B,))
+        pAp = ops.zeros((B,))
+        ops.batched_dot(r, z, n, rz)
+        rz0 = rz.clone()
+        it = 0
+        while it < self.max_iter:
+            for _ in range(self.check_every):
+                ops.spmv(csr, p, Ap)
+                ops.batched_dot(p, Ap, n, pAp)
+                ops.pcg_update_xr(x, r, z, p, Ap, dinv, rz, pAp, n)
+                ops.batched_dot(r, z, n, rz_new)
+                ops.pcg_update_p(p, z, rz_new, rz, n)
+                rz, rz_new = rz_new, rz
+                it += 1
+            ratio = float(torch.max(rz / rz0).item())     # host sync, once per `check_every` iterations
+            if not np.isfinite(ratio):
+                raise FloatingPointError("PCG broke down (non-finite residual)")
+            if ratio < self.tol * self.tol:
+                break
+        self.stats[key] += it
+        return x
+
+    # ------------------------------------------------------------------ queries
+    def distances(self, idx_dev):
+        """phi (B, ldx) for the B source vertices in idx_dev (int64 device tensor); phi is NOT yet shifted by its
+        minimum (asb_support_map does that, utils/support.py:206)."""
+        ops, n = self.ops, self.n
+        B = idx_dev.numel()
+        rhs = ops.empty((B, self.ldx))
+        ops.delta_rhs(idx_dev, n, rhs)
+        u = self._pcg(self.heat, self.heat_dinv, rhs, False, "heat_iters")
+        Xt = ops.empty((B, self.T, 3))
+        div = ops.zeros((B, self.ldx))
+        ops.heat_divergence(u, self.tri, self.gconst, self.dconst, self.vc_ptr, self.vc_idx, n, Xt, div)
+        # reference solves Lc phi = div; we solve (-Lc) psi = div  =>  phi = -psi
+        psi = self._pcg(self.pois, self.pois_dinv, div, True, "poisson_iters")
+        phi = ops.empty((B, self.ldx))
+        ops.axpby(phi, -1.0, psi, None, 0.0, None, n)
+        self.stats["solves"] += B
+        return phi
+
+    def support(self, idx_dev, mode, lam, dmin, dmax, row0, nloc, out, ids_host=None, chunk=64):
+        """out[b, :nloc] = support map of source idx_dev[b] restricted to rows [row0, row0+nloc).
+        mode 0: 1 - map (deflation mask), 1: lam * map (SPLOCS Lambda), 2: phi - min(phi).
+        With `ids_host` (the same indices as a host list) rows are memoised per vertex id."""
+        ops = self.ops
+        B = idx_dev.numel()
+        self.stats["queries"] += B
+        if ids_host is None:
+            for b0 in range(0, B, chunk):
+                sl = slice(b0, min(B, b0 + chunk))
+                phi = self.distances(idx_dev[sl])
+                ops.support_map(phi, self.n, dmin, dmax, mode, lam, row0, nloc, out[sl])
+            return out
+        key = (mode, float(lam), float(dmin), float(dmax), row0, nloc)
+        cache = self._cache.setdefault(key, {})
+        missing = sorted({int(i) for i in ids_host if int(i) not in cache})
+        for b0 in range(0, len(missing), chunk):
+            ids = missing[b0:b0 + chunk]
+            idt = ops.to_device(np.asarray(ids, dtype=np.int64))
+            phi = self.distances(idt)
+            rows = ops.zeros((len(ids), out.shape[1]))
+            ops.support_map(phi, self.n, dmin, dmax, mode, lam, row0, nloc, rows)
+            for j, i in enumerate(ids):
+                cache[i] = rows[j]
+        self.stats["cache_hits"] += B - len(missing)
+        for b, i in enumerate(ids_host):
+            out[b].copy_(cache[int(i)])
+        return out

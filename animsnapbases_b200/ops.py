@@ -1,0 +1,324 @@
+"""Device operator set of the basis engine: one Python method per C-ABI entry point of libasb.so.
+
+PyTorch is used for device memory, streams and (in engine.py) torch.distributed only; every arithmetic
+step of the hot path is a hand-written sm_100a kernel behind include/asb.h.  The class refuses to
+construct without a CUDA device and the built library -- there is no CPU path in the product.
+(tests/numpy_ops.py holds a numpy stand-in with the same interface, used only to exercise the host-side
+orchestration and the world_size-2 gloo path on machines without a GPU.)
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import _lib
+
+F64 = torch.float64
+I64 = torch.int64
+I32 = torch.int32
+
+
+def pad_ld(n: int) -> int:
+    """Plane stride of the planar layout: next multiple of 32."""
+    return (int(n) + 31) // 32 * 32
+
+
+class CudaOps:
+    name = "cuda"
+
+    def __init__(self, device=None):
+        if not torch.cuda.is_available():
+            raise _lib.AsbError("animsnapbases_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.lib = _lib.load()
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        torch.cuda.set_device(self.device)
+        sms, major, minor = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        _lib.check(self.lib.asb_device_info(ctypes.byref(sms), ctypes.byref(major), ctypes.byref(minor)), "device_info")
+        self.sm_count, self.cc = sms.value, (major.value, minor.value)
+        if self.cc[0] < 10:
+            raise _lib.AsbError(f"libasb.so is built for sm_100a only; found compute capability {self.cc}")
+        self._ws = None
+        self._ws2 = None
+        self.timers = None
+
+    # ------------------------------------------------------------------ plumbing
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    @staticmethod
+    def _p(t):
+        if t is None:
+            return None
+        return ctypes.c_void_p(t.data_ptr())
+
+    def _call(self, name, *args):
+        ev = self.timers.get(name) if self.timers is not None else None
+        if ev is not None:
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            _lib.check(getattr(self.lib, name)(*args, self._stream()), name)
+            b.record()
+            ev.append((a, b))
+            return
+        _lib.check(getattr(self.lib, name)(*args, self._stream()), name)
+
+    def time_kernels(self, names):
+        """Record CUDA events (on torch's current stream, the one every kernel is launched on) around each launch
+        of the named C-ABI entry points; `kernel_times()` returns {name: (launches, total_ms)} after a sync."""
+        self.timers = {n: [] for n in names} if names else None
+
+    def kernel_times(self):
+        self.synchronize()
+        out = {}
+        for n, evs in (self.timers or {}).items():
+            out[n] = (len(evs), float(sum(a.elapsed_time(b) for a, b in evs)))
+        return out
+
+    def empty(self, shape, dtype=F64):
+        return torch.empty(shape, dtype=dtype, device=self.device)
+
+    def zeros(self, shape, dtype=F64):
+        return torch.zeros(shape, dtype=dtype, device=self.device)
+
+    def to_device(self, a, dtype=None):
+        t = torch.as_tensor(a)
+        if dtype is not None:
+            t = t.to(dtype)
+        return t.to(self.device, non_blocking=True).contiguous()
+
+    def workspace(self, nbytes: int):
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = torch.empty(int(nbytes) + 256, dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def ws_for(self, rows: int, cols: int):
+        return self.workspace(self.lib.asb_workspace_bytes(int(rows), int(cols)))
+
+    def launch_count(self) -> int:
+        return int(self.lib.asb_launch_count())
+
+    def reset_launch_count(self):
+        self.lib.asb_reset_launch_count()
+
+    def synchronize(self):
+        torch.cuda.synchronize(self.device)
+
+    # ------------------------------------------------------------------ boundary
+    def ingest(self, src, row_scale, ld):
+        R, N, _ = src.shape
+        X = self.empty((R, 3, ld))
+        fn = "asb_ingest_f32" if src.dtype == torch.float32 else "asb_ingest_f64"
+        self._call(fn, self._p(src), self._p(row_scale), self._p(X), R, N, ld)
+        return X
+
+    def export_aos(self, T, row_scale, N):
+        R, _, ld = T.shape
+        out = self.empty((R, N, 3))
+        self._call("asb_export_aos", self._p(T), self._p(row_scale), self._p(out), R, N, ld)
+        return out
+
+    def pack_bin(self, T, K, N):
+        out = self.empty((3, K, N))
+        self._call("asb_pack_bin", self._p(T), self._p(out), K, N, T.shape[2])
+        return out
+
+    # ------------------------------------------------------------------ centering
+    def col_mean(self, X):
+        F, _, ld = X.shape
+        mean = self.empty((3, ld))
+        self._call("asb_col_mean", self._p(X), self._p(mean), F, ld)
+        return mean
+
+    def center_stats(self, X, mean, N):
+        F, _, ld = X.shape
+        out = self.empty((2,))
+        self._call("asb_center_stats", self._p(X), self._p(mean), F, N, ld, self._p(out), self._p(self.ws_for(F, 3 * ld)))
+        return out
+
+    def center_apply(self, X, mean, scale, N):
+        F, _, ld = X.shape
+        self._call("asb_center_apply", self._p(X), self._p(mean), float(scale), F, N, ld)
+
+    def unstandardize(self, T, mean, scale, N):
+        R, _, ld = T.shape
+        self._call("asb_unstandardize", self._p(T), self._p(mean), float(scale), R, N, ld)
+
+    # ------------------------------------------------------------------ deflation
+    def vertex_energy(self, R, N, out=None):
+        F, _, ld = R.shape
+        e = self.empty((ld,)) if out is None else out
+        self._call("asb_vertex_energy", self._p(R), self._p(e), F, N, ld, self._p(self.ws_for(F, 3 * ld)))
+        return e
+
+    def argmax_first(self, v, n, index_offset, out_val, out_idx):
+        self._call("asb_argmax_first", self._p(v), n, index_offset, self._p(out_val), self._p(out_idx),
+                   self._p(self.ws_for(1, n)))
+
+    def gather_traj(self, R, N, idx_dev, row0, W, k0, C, npend, traj):
+        """W: (F, Kmax) weights, C: (Kmax, 3, ld) components; pending block = columns/rows [k0, k0+npend)."""
+        F, _, ld = R.shape
+        Wp = ctypes.c_void_p(W.data_ptr() + 8 * k0) if npend else None
+        Cp = ctypes.c_void_p(C.data_ptr() + 8 * k0 * 3 * ld) if npend else None
+        self._call("asb_gather_traj", self._p(R), F, N, ld, self._p(idx_dev), row0, Wp, W.shape[1], Cp, npend,
+                   self._p(traj))
+
+    def traj_rank1(self, traj, F, local_support, W, k, k0, coef, scal):
+        npend = k - k0
+        ldw = W.shape[1]
+        wout = ctypes.c_void_p(W.data_ptr() + 8 * k)
+        Wp = ctypes.c_void_p(W.data_ptr() + 8 * k0) if npend else None
+        self._call("asb_traj_rank1", self._p(traj), F, int(bool(local_support)), wout, ldw, Wp, npend,
+                   self._p(coef) if npend else None, self._p(scal))
+
+    def deflate_gemv(self, R, N, W, k, g):
+        F, _, ld = R.shape
+        w = ctypes.c_void_p(W.data_ptr() + 8 * k)
+        self._call("asb_deflate_gemv", self._p(R), F, N, ld, w, W.shape[1], self._p(g), self._p(self.ws_for(F, 3 * ld)))
+
+    def deflate_finish(self, g, C, k, k0, coef, s, scal, e, N, meas):
+        ld = C.shape[2]
+        npend = k - k0
+        Cp = ctypes.c_void_p(C.data_ptr() + 8 * k0 * 3 * ld) if npend else None
+        cout = ctypes.c_void_p(C.data_ptr() + 8 * k * 3 * ld)
+        self._call("asb_deflate_finish", self._p(g), Cp, npend, self._p(coef) if npend else None, self._p(s), self._p(scal),
+                   cout, self._p(e), N, ld, self._p(meas), self._p(self.ws_for(1, 3 * ld)))
+
+    def rank_update(self, R, N, W, C, k0, nb, e):
+        F, _, ld = R.shape
+        Wb = ctypes.c_void_p(W.data_ptr() + 8 * k0)
+        Cb = ctypes.c_void_p(C.data_ptr() + 8 * k0 * 3 * ld)
+        self._call("asb_rank_update", self._p(R), F, N, ld, Wb, W.shape[1], Cb, nb, self._p(e),
+                   self._p(self.ws_for(F, 3 * ld)))
+
+    # ------------------------------------------------------------------ dense contractions
+    def gemm_nt(self, A, ra, B, rb, M, symmetric=False, out=None):
+        """D = A[:ra, :M] @ B[:rb, :M].T for row-major 2-D views A, B (stride(0) = leading dimension)."""
+        D = self.empty((ra, rb)) if out is None else out
+        nbytes = self.lib.asb_gemm_nt_workspace_bytes(ra, rb, M, int(symmetric))
+        if self._ws2 is None or self._ws2.numel() < nbytes:
+            self._ws2 = torch.empty(int(nbytes) + 256, dtype=torch.uint8, device=self.device)
+        self._call("asb_gemm_nt", self._p(A), A.stride(0), ra, self._p(B), B.stride(0), rb, M, self._p(D), D.stride(0),
+                   int(symmetric), self._p(self._ws2))
+        return D
+
+    def gemm_nn(self, A, r, q, B, M, alpha, out, row_scale=None):
+        """out[:r, :M] = alpha * diag(row_scale) * A[:r, :q] @ B[:q, :M]."""
+        self._call("asb_gemm_nn", self._p(A), A.stride(0), r, q, self._p(B), B.stride(0), M, float(alpha),
+                   self._p(row_scale), self._p(out), out.stride(0))
+        return out
+
+    def admm_iter(self, Hr, B0, Z, U, Lambda, K, N, inv_rho):
+        ld = Z.shape[2]
+        self._call("asb_admm_iter", self._p(Hr), Hr.stride(0), self._p(B0), self._p(Z), self._p(U), self._p(Lambda), K, N, ld,
+                   float(inv_rho))
+
+    # ------------------------------------------------------------------ small dense
+    def gram_small(self, W, F, K, diag_add, G):
+        self._call("asb_gram_small", self._p(W), W.stride(0), F, K, float(diag_add), self._p(G), G.stride(0))
+
+    def spd_inverse(self, H, K, Hinv, info):
+        scratch = self.empty((K, Hinv.stride(0)))
+        self._call("asb_spd_inverse", self._p(H), H.stride(0), K, self._p(Hinv), Hinv.stride(0), self._p(scratch), self._p(info))
+
+    def small_gemm(self, transA, transB, m, n, k, alpha, A, B, D):
+        self._call("asb_small_gemm", int(transA), int(transB), m, n, k, float(alpha), self._p(A), A.stride(0), self._p(B),
+                   B.stride(0), self._p(D), D.stride(0))
+
+    def weights_sweep(self, P, Q, W, F, K):
+        self._call("asb_weights_sweep", self._p(P), P.stride(0), self._p(Q), Q.stride(0), self._p(W), W.stride(0), F, K,
+                   self._p(self.ws_for(1, 4096)))
+
+    def component_centers(self, C, Lambda, K, N, index_offset, val, idx, sp):
+        ld = C.shape[2]
+        self._call("asb_component_centers", self._p(C), self._p(Lambda), K, N, ld, index_offset, self._p(val), self._p(idx),
+                   self._p(sp), self._p(self.workspace(8 * (64 * K * 3 + 1024))))
+
+    def syevd(self, A, n):
+        """In place: rows of A become the eigenvectors (ascending eigenvalues returned)."""
+        w = self.empty((n,))
+        info = self.zeros((1,), I32)
+        nbytes = self.lib.asb_syevd_workspace_bytes(n)
+        if nbytes < 0:
+            raise _lib.AsbError("cuSOLVER workspace query failed")
+        ws = torch.empty(int(nbytes) + 256, dtype=torch.uint8, device=self.device)
+        self._call("asb_syevd", self._p(A), A.stride(0), n, self._p(w), self._p(ws), int(nbytes), self._p(info))
+        return w, info
+
+    def cgs_dots(self, T, k, d, N, h):
+        self._call("asb_cgs_dots", self._p(T), k, d, N, T.shape[2], self._p(h), self._p(self.workspace(8 * (2 * self.sm_count * max(k, 1) + 1024))))
+
+    def cgs_project(self, T, k, d, N, h, nrm2):
+        self._call("asb_cgs_project", self._p(T), k, d, N, T.shape[2], self._p(h), self._p(nrm2), self._p(self.workspace(8 * (T.shape[2] // 256 + 1024))))
+
+    def row_scale(self, T, k, d, nrm2):
+        self._call("asb_row_scale", self._p(T), k, d, T.shape[2], self._p(nrm2))
+
+    # ------------------------------------------------------------------ DEIM
+    def deim_gather(self, C, N, row0, Pt, k, Vp):
+        self._call("asb_deim_gather", self._p(C), C.shape[2], N, row0, self._p(Pt), k, self._p(Vp), Vp.shape[1])
+
+    def deim_solve(self, Vp, k, a, info):
+        ws = self.workspace(3 * k * (k + 1) * 8 + 1024)
+        self._call("asb_deim_solve", self._p(Vp), Vp.shape[1], k, self._p(a), a.stride(0), self._p(ws), self._p(info))
+
+    def deim_residual(self, C, N, k, a, e, maxabs):
+        self._call("asb_deim_residual", self._p(C), C.shape[2], N, k, self._p(a), a.stride(0), self._p(e), self._p(maxabs),
+                   self._p(self.ws_for(1, C.shape[2])))
+
+    # ------------------------------------------------------------------ geodesics
+    def spmv(self, csr, x, y):
+        rowptr, colidx, vals = csr
+        nrhs, ldx = x.shape
+        self._call("asb_spmv_csr", self._p(rowptr), self._p(colidx), self._p(vals), rowptr.numel() - 1, self._p(x), self._p(y),
+                   nrhs, ldx)
+
+    def batched_dot(self, x, y, n, out):
+        nrhs, ldx = x.shape
+        self._call("asb_batched_dot", self._p(x), self._p(y), n, nrhs, ldx, self._p(out), self._p(self.workspace(8 * (65 * nrhs + 1024))))
+
+    def pcg_update_xr(self, x, r, z, p, Ap, dinv, rz, pAp, n):
+        nrhs, ldx = x.shape
+        self._call("asb_pcg_update_xr", self._p(x), self._p(r), self._p(z), self._p(p), self._p(Ap), self._p(dinv), self._p(rz),
+                   self._p(pAp), None, n, nrhs, ldx)
+
+    def pcg_update_p(self, p, z, rz_new, rz_old, n):
+        nrhs, ldx = p.shape
+        self._call("asb_pcg_update_p", self._p(p), self._p(z), self._p(rz_new), self._p(rz_old), None, n, nrhs, ldx)
+
+    def axpby(self, y, alpha, a, row_scale, beta, c, n):
+        nrhs, ldx = y.shape
+        self._call("asb_axpby", self._p(y), float(alpha), self._p(a), self._p(row_scale), float(beta), self._p(c), n, nrhs, ldx)
+
+    def remove_mean(self, x, n):
+        nrhs, ldx = x.shape
+        self._call("asb_remove_mean", self._p(x), n, nrhs, ldx, self._p(self.workspace(8 * (66 * nrhs + 1024))))
+
+    def heat_divergence(self, u, tri, gconst, dconst, vc_ptr, vc_idx, n, Xt, div):
+        nrhs, ldx = u.shape
+        self._call("asb_heat_divergence", self._p(u), nrhs, ldx, self._p(tri), self._p(gconst), self._p(dconst), tri.shape[0],
+                   self._p(vc_ptr), self._p(vc_idx), n, self._p(Xt), self._p(div))
+
+    def support_map(self, phi, n, dmin, dmax, mode, lam, row0, nloc, out):
+        nrhs, ldx = phi.shape
+        self._call("asb_support_map", self._p(phi), n, nrhs, ldx, float(dmin), float(dmax), int(mode), float(lam), row0, nloc,
+                   self._p(out), out.stride(0), self._p(self.workspace(8 * (66 * nrhs + 1024))))
+
+    def delta_rhs(self, idx, n, rhs):
+        nrhs, ldx = rhs.shape
+        self._call("asb_delta_rhs", self._p(idx), n, nrhs, ldx, self._p(rhs))
+
+    # ------------------------------------------------------------------ alignment
+    def align(self, frames, rigid):
+        """frames: (F, N, 3) float32 on the device -> aligned float32 (F, N, 3) and the (F, 12) transforms."""
+        F, N, _ = frames.shape
+        cent = self.empty((F, 3))
+        M = self.empty((F, 9))
+        T = self.empty((F, 12))
+        out = torch.empty_like(frames)
+        ws = self._p(self.workspace(8 * (32 * 9 * F + 1024)))
+        self._call("asb_align_centroids", self._p(frames), F, N, self._p(cent), ws)
+        self._call("asb_align_cov", self._p(frames), F, N, self._p(cent), self._p(M), ws)
+        self._call("asb_align_solve", self._p(M), self._p(cent), F, int(bool(rigid)), self._p(T))
+        self._call("asb_align_apply", self._p(frames), F, N, self._p(T), self._p(out))
+        return out, T

@@ -1,0 +1,232 @@
+/*
+ * asb.h -- C-ABI of libasb.so, the B200 (sm_100a) snapshot-basis engine that sits under the
+ * posComponents / constraintsComponents Python protocol of ShMonem/animSnapBases.
+ *
+ * The reference has no FFI of its own (it is pure numpy/scipy); every entry point below names the
+ * reference call site (file:line, relative to the reference root) whose arithmetic it replaces.
+ * INTEGRATION.md shows the ctypes stub a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - plain C types only; every array argument is a DEVICE pointer owned by the caller; no hidden
+ *     allocation (workspaces are passed in, sizes come from asb_workspace_bytes()).
+ *   - `stream` is a cudaStream_t passed as void*; all calls are asynchronous on that stream.
+ *   - return 0 on success, negative on error; asb_last_error() returns a thread-local message.
+ *   - snapshot / component tensors live in HBM in PLANAR layout  T[r][d][n]  (r = frame or component,
+ *     d = x|y|z, n = vertex / constraint row) with plane stride `ld` (multiple of 32, padding = 0),
+ *     i.e. an  R x (3*ld)  row-major matrix.  The reference's (R, N, 3) AoS layout exists only at the
+ *     host boundary (asb_ingest_* / asb_export_aos / asb_pack_bin).
+ *   - all arithmetic is IEEE fp64; reductions are fixed-order (deterministic run to run).
+ */
+#ifndef ASB_H_
+#define ASB_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* asb_stream_t;
+
+#define ASB_OK 0
+#define ASB_ERR_ARG (-1)
+#define ASB_ERR_CUDA (-2)
+#define ASB_ERR_UNSUPPORTED (-3)
+#define ASB_ERR_NUMERIC (-4)
+
+/* ---- library -------------------------------------------------------------------------------- */
+int asb_version(void);
+const char* asb_last_error(void);
+/* SM count / compute capability of the current device. */
+int asb_device_info(int* sm_count, int* cc_major, int* cc_minor);
+/* Number of kernel launches issued through this library since the last reset (bench `gpu_launches`). */
+int64_t asb_launch_count(void);
+void asb_reset_launch_count(void);
+/* Scratch bytes every reducing entry point may need for (rows x cols)-sized problems. */
+int64_t asb_workspace_bytes(int64_t rows, int64_t cols);
+
+/* ---- boundary: AoS <-> planar (host formats) -------------------------------------------------- */
+/* X[f][d][n] = (double)src[f][n][d] * (row_scale ? row_scale[n] : 1); padding n in [N, ld) = 0.
+ * posSnapshots.read + `snapTensor *= massL[:, None]`  (snapbases/posSnapshots.py:110, :82);
+ * nonlinear_snapshots.py:89 for the f64 variant. */
+int asb_ingest_f32(const float* src, const double* row_scale, double* X, int64_t R, int64_t N, int64_t ld,
+                   asb_stream_t stream);
+int asb_ingest_f64(const double* src, const double* row_scale, double* X, int64_t R, int64_t N, int64_t ld,
+                   asb_stream_t stream);
+/* dst[r][n][d] = T[r][d][n] * (row_scale ? row_scale[n] : 1)   (planar -> reference layout;
+ * the optional scale is `comps *= invMassL[:, None]`, snapbases/posComponents.py:289-292). */
+int asb_export_aos(const double* T, const double* row_scale, double* dst, int64_t R, int64_t N, int64_t ld,
+                   asb_stream_t stream);
+/* Body of the reference `.bin` basis file: out[d][k][i] = T[k][d][i], k < K  (utils/utils.py:28-34). */
+int asb_pack_bin(const double* T, double* out, int64_t K, int64_t N, int64_t ld, asb_stream_t stream);
+
+/* ---- k2: mean-centering / standardisation ------------------------------------------------------ */
+/* mean[c] = (sum_f X[f][c]) / F, sequential in f  (np.mean(axis=0), snapbases/posSnapshots.py:89). */
+int asb_col_mean(const double* X, double* mean, int64_t F, int64_t ld, asb_stream_t stream);
+/* out[0] = sum (x - mean), out[1] = sum (x - mean)^2 over the valid F x N x 3 entries
+ * (the two moments np.std needs, snapbases/posSnapshots.py:168-171). ws: asb_workspace_bytes(F, 3*ld). */
+int asb_center_stats(const double* X, const double* mean, int64_t F, int64_t N, int64_t ld, double* out2,
+                     void* ws, asb_stream_t stream);
+/* X = (X - mean) * scale with two roundings, as `X -= mean; X *= s` (snapbases/posSnapshots.py:168,:172). */
+int asb_center_apply(double* X, const double* mean, double scale, int64_t F, int64_t N, int64_t ld,
+                     asb_stream_t stream);
+/* T[r][d][n] = T[r][d][n] * inv_scale_mul + mean[d][n]  is NOT what the reference does; it divides:
+ * T = T / scale + mean   (`comps /= pre_scale_factor; comps += mean`, snapbases/posComponents.py:279-282). */
+int asb_unstandardize(double* T, const double* mean, double scale, int64_t R, int64_t N, int64_t ld,
+                      asb_stream_t stream);
+
+/* ---- k3..k9: greedy deflation ("PCA" of snapbases/posComponents.py:67-122) --------------------- */
+/* e[n] = sum_f ((x^2 + y^2) + z^2), f ascending; `block` > 1 sums the energies of `block` consecutive
+ * rows into e[n / block] (element energy, snapbases/constraintsComponents.py:86-96). (:78-79) */
+int asb_vertex_energy(const double* R, double* e, int64_t F, int64_t N, int64_t ld, void* ws, asb_stream_t stream);
+/* First index of the maximum of v[0..n) (np.argmax tie rule): out_val[0], out_idx[0] = index + index_offset.
+ * ws: asb_workspace_bytes(1, n). */
+int asb_argmax_first(const double* v, int64_t n, int64_t index_offset, double* out_val, int64_t* out_idx,
+                     void* ws, asb_stream_t stream);
+/* traj[d][f] = R[f][d][idx] - sum_{j<npend} Wp[f*ldw + j] * Cp[j][d][idx]   where idx = *idx_dev - row0;
+ * no-op (traj untouched) when idx is outside [0, N): only the owning shard writes. (:83, R[:, idx, :]) */
+int asb_gather_traj(const double* R, int64_t F, int64_t N, int64_t ld, const int64_t* idx_dev, int64_t row0,
+                    const double* Wp, int64_t ldw, const double* Cp, int64_t npend, double* traj,
+                    asb_stream_t stream);
+/* Rank-1 SVD of the 3 x F trajectory in closed form (3x3 Gram -> Jacobi eigen):  w = sigma0 * Vt[0]
+ * (:83-85); if local_support: w = project_weight(+-w) with the larger 2-norm (:90-94, :52-58).
+ * Writes w to wout[f*ldw] (a column of the F x K weight matrix), scal[0]=sigma0, scal[1]=w.w,
+ * and coef[j] = w . Wp[:, j] for the npend pending components of the current block. */
+int asb_traj_rank1(const double* traj, int64_t F, int local_support, double* wout, int64_t ldw,
+                   const double* Wp, int64_t npend, double* coef, double* scal, asb_stream_t stream);
+/* One pass over R:  g[d][n] = sum_f w[f*ldw] * R[f][d][n]   (`tensordot(wk, R, (0, 0))`, :102-105).
+ * ws: asb_workspace_bytes(F, 3*ld). */
+int asb_deflate_gemv(const double* R, int64_t F, int64_t N, int64_t ld, const double* w, int64_t ldw, double* g,
+                     void* ws, asb_stream_t stream);
+/* Finish component k:  g -= sum_j coef[j] * Cp[j];  c = (s ? s[n] : 1) * g / scal[1]  -> cout;
+ * e[n] -= (2 s - s^2) |g_n|^2 / scal[1]  (energy of R - w c^T without touching R);
+ * meas[0] = sigma0 (scal[0]), meas[1] = sqrt(sum_n e[n])  -- local shard partial in meas[2] (sum e). (:102-113) */
+int asb_deflate_finish(const double* g, const double* Cp, int64_t npend, const double* coef, const double* s,
+                       const double* scal, double* cout, double* e, int64_t N, int64_t ld, double* meas,
+                       void* ws, asb_stream_t stream);
+/* R[f] -= sum_{j<nb} Wb[f*ldw + j] * Cb[j]  for all frames (the pending rank-1 updates `R -= outer(wk, ck)`,
+ * :111, applied nb at a time), and e[n] recomputed exactly from the new R. nb <= 16. */
+int asb_rank_update(double* R, int64_t F, int64_t N, int64_t ld, const double* Wb, int64_t ldw, const double* Cb,
+                    int64_t nb, double* e, void* ws, asb_stream_t stream);
+
+/* ---- dense fp64 tensor-core contractions (DMMA m8n8k4) --------------------------------------- */
+/* D[i][j] = sum_m A[i][m] * B[j][m],  A: ra x M (lda), B: rb x M (ldb), D: ra x rb (ldd).
+ * symmetric != 0 (requires A == B): only tiles with j >= i are computed, then mirrored.
+ * Gram X X^T (constraintsComponents.py:306-313 via eigen), X C^T / C C^T (posComponents.py:144-156),
+ * per-dimension Gram for orthogonalisation.  ws: asb_gemm_nt_workspace_bytes(ra, rb, M). */
+int64_t asb_gemm_nt_workspace_bytes(int64_t ra, int64_t rb, int64_t M, int symmetric);
+int asb_gemm_nt(const double* A, int64_t lda, int64_t ra, const double* B, int64_t ldb, int64_t rb, int64_t M,
+                double* D, int64_t ldd, int symmetric, void* ws, asb_stream_t stream);
+/* D[i][m] = alpha * (row_scale ? row_scale[i] : 1) * sum_q A[i][q] * B[q][m],  A: r x q (lda, rows zero-padded to
+ * an even length), B: q x M (ldb), D: r x M (ldd).
+ * c = W^T X (posComponents.py:171), back-projection U^T = S^-1 V^T X (constraintsComponents.py:313). */
+int asb_gemm_nn(const double* A, int64_t lda, int64_t r, int64_t q, const double* B, int64_t ldb, int64_t M,
+                double alpha, const double* row_scale, double* D, int64_t ldd, asb_stream_t stream);
+/* One ADMM iteration, fused (posComponents.py:175-178, :252-256), in place on Z and U:
+ *   C = B0 + Hr (Z - U)          Hr = rho * (W^T W + rho I)^-1  (K x K, ldh)
+ *   V = C + U;  Z' = V * max(0, 1 - inv_rho * Lambda[k][n] / |V[k][:, n]|);  U' = V - Z'
+ * B0, Z, U: K x 3*ld planar; Lambda: K x ld.  K <= 256. */
+int asb_admm_iter(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda,
+                  int64_t K, int64_t N, int64_t ld, double inv_rho, asb_stream_t stream);
+
+/* ---- small replicated dense work ---------------------------------------------------------------- */
+/* G[j][l] = sum_f W[f][j] W[f][l] + (j == l ? diag_add : 0)   (posComponents.py:170, :172). */
+int asb_gram_small(const double* W, int64_t ldw, int64_t F, int64_t K, double diag_add, double* G, int64_t ldg,
+                   asb_stream_t stream);
+/* Hinv = H^-1 for SPD H (K x K) via Cholesky (replaces cho_factor/cho_solve, posComponents.py:172,:176).
+ * H is overwritten by its Cholesky factor. info_dev[0] != 0 if not positive definite. */
+int asb_spd_inverse(double* H, int64_t ldh, int64_t K, double* Hinv, int64_t ldi, double* scratch /* K x ldi */,
+                    int* info_dev, asb_stream_t stream);
+/* D = alpha * op(A) * op(B) for small matrices (everything L2 resident); D: m x n, inner k. */
+int asb_small_gemm(int transA, int transB, int64_t m, int64_t n, int64_t k, double alpha, const double* A,
+                   int64_t lda, const double* B, int64_t ldb, double* D, int64_t ldd, asb_stream_t stream);
+/* Gauss-Seidel non-negative weight sweep in Gram form (posComponents.py:144-156):
+ *   P = X C^T (F x K), Q = C C^T (K x K);  W updated in place (F x K, ldw).  ws: F*K doubles + 4096. */
+int asb_weights_sweep(const double* P, int64_t ldp, const double* Q, int64_t ldq, double* W, int64_t ldw,
+                      int64_t F, int64_t K, void* ws, asb_stream_t stream);
+/* For every component k: idx[k] = first argmax_n sum_d C[k][d][n]^2 (+ index_offset), val[k] = that maximum,
+ * sp[k] = sum_n Lambda[k][n] * |C[k][:, n]| when Lambda != NULL  (posComponents.py:161, :184). */
+int asb_component_centers(const double* C, const double* Lambda, int64_t K, int64_t N, int64_t ld,
+                          int64_t index_offset, double* val, int64_t* idx, double* sp, void* ws, asb_stream_t stream);
+/* Symmetric eigen-decomposition of the replicated F x F Gram (cuSOLVER Dsyevd): A <- eigenvectors
+ * (column-major = rows of A are eigenvectors when A is read row-major ... see DESIGN.md), w ascending. */
+int64_t asb_syevd_workspace_bytes(int64_t n);
+int asb_syevd(double* A, int64_t lda, int64_t n, double* w, void* ws, int64_t ws_bytes, int* info_dev,
+              asb_stream_t stream);
+/* Per-dimension classical Gram-Schmidt with re-orthogonalisation (CGS2) over the rows of T[:, d, :]:
+ * replaces scipy qr(mode='economic') of (N x K) per dimension (constraintsComponents.py:431-433).
+ * This entry does ONE projection pass of row k against rows [0,k):  h = Q_{<k} t_k;  t_k -= Q_{<k}^T h;
+ * and returns |t_k|^2 partial in nrm2[0].  Host drives two passes + normalisation (and the all-reduce). */
+int asb_cgs_project(double* T, int64_t k, int64_t d, int64_t N, int64_t ld, const double* h, double* nrm2, void* ws,
+                    asb_stream_t stream);
+int asb_cgs_dots(const double* T, int64_t k, int64_t d, int64_t N, int64_t ld, double* h, void* ws,
+                 asb_stream_t stream);
+int asb_row_scale(double* T, int64_t k, int64_t d, int64_t ld, const double* nrm2, asb_stream_t stream);
+
+/* ---- k19: DEIM (snapbases/constraintsComponents.py:797-860) ------------------------------------ */
+/* Rows of the basis at the selected points: Vp[d][j][l] = C[l][d][Pt[j] - row0] for l <= k, j < k, if the
+ * row is local (else left untouched; buffer must be zeroed, shards are summed). */
+int asb_deim_gather(const double* C, int64_t ld, int64_t N, int64_t row0, const int64_t* Pt, int64_t k,
+                    double* Vp, int64_t ldv, asb_stream_t stream);
+/* Solve the three k x k systems  V[Pt, :k, d] a_d = v_k[Pt, d]  (LU, partial pivoting; np.linalg.lstsq in
+ * the reference, :823).  Vp as above (column k = rhs). a: 3 x lda_a. */
+int asb_deim_solve(const double* Vp, int64_t ldv, int64_t k, double* a, int64_t lda_a, void* ws, int* info_dev,
+                   asb_stream_t stream);
+/* r[d][n] = sum_{l<k} a[d][l] C[l][d][n] - C[k][d][n];  e[n] = (rx^2 + ry^2) + rz^2  (:823-836);
+ * maxabs[0] = max |r|.  For k == 0: r = C[0]. */
+int asb_deim_residual(const double* C, int64_t ld, int64_t N, int64_t k, const double* a, int64_t lda_a,
+                      double* e, double* maxabs, void* ws, asb_stream_t stream);
+
+/* ---- k6/k7: heat-method geodesics + support maps (utils/support.py:139-208) --------------------- */
+/* y[b] = A x[b] for nrhs vectors of length n (ldx apart), CSR with int32 indices. */
+int asb_spmv_csr(const int32_t* rowptr, const int32_t* colidx, const double* vals, int64_t n, const double* x,
+                 double* y, int64_t nrhs, int64_t ldx, asb_stream_t stream);
+/* dots[b] = sum_i x[b][i] * y[b][i]  (fixed order). ws: asb_workspace_bytes(nrhs, n). */
+int asb_batched_dot(const double* x, const double* y, int64_t n, int64_t nrhs, int64_t ldx, double* dots,
+                    void* ws, asb_stream_t stream);
+/* Fused PCG vector updates; scalars live on the device (no host sync inside the iteration):
+ *   step 1: alpha = rz / pAp;  x += alpha p;  r -= alpha Ap;  z = dinv .* r    (z optional when dinv == NULL)
+ *   step 2: beta = rz_new / rz_old;  p = z + beta p
+ * active[b] == 0 freezes a converged right-hand side. */
+int asb_pcg_update_xr(double* x, double* r, double* z, const double* p, const double* Ap, const double* dinv,
+                      const double* rz, const double* pAp, const int32_t* active, int64_t n, int64_t nrhs,
+                      int64_t ldx, asb_stream_t stream);
+int asb_pcg_update_p(double* p, const double* z, const double* rz_new, const double* rz_old,
+                     const int32_t* active, int64_t n, int64_t nrhs, int64_t ldx, asb_stream_t stream);
+/* y[b] = alpha * a[b] .* row_scale + beta * c[b]  (row_scale and c optional): Jacobi / smoother building block. */
+int asb_axpby(double* y, double alpha, const double* a, const double* row_scale, double beta, const double* c, int64_t n,
+              int64_t nrhs, int64_t ldx, asb_stream_t stream);
+/* x[b] -= mean(x[b])  (projection onto the complement of the constant null space of the cotan Laplacian). */
+int asb_remove_mean(double* x, int64_t n, int64_t nrhs, int64_t ldx, void* ws, asb_stream_t stream);
+/* Heat-method step 2+3: per triangle unit gradient of u, integrated divergence gathered per vertex through a
+ * vertex->corner CSR (deterministic, no atomics).  tri: T x 3 int32;  gconst: T x 9 (n x e12, n x e20, n x e01
+ * scaled by 1/(2A));  dconst: T x 3 x 8 per-corner (cot1, e1[3], cot2, e2[3]) with the reference's
+ * 1/tan(arccos(.)) cotangents (utils/support.py:183-204). */
+int asb_heat_divergence(const double* u, int64_t nrhs, int64_t ldx, const int32_t* tri, const double* gconst,
+                        const double* dconst, int64_t T, const int32_t* vc_ptr, const int32_t* vc_idx, int64_t n,
+                        double* Xt, double* div, asb_stream_t stream);
+/* phi -= min(phi) (:206), then out[b][n - row0] for n in [row0, row0 + nloc):
+ *   mode 0: 1 - (clip(phi,dmin,dmax) - dmin)/(dmax - dmin)      (deflation mask s, posComponents.py:95-96)
+ *   mode 1: lambda * (clip(phi,dmin,dmax) - dmin)/(dmax - dmin) (SPLOCS Lambda_k, posComponents.py:162-165)
+ *   mode 2: phi itself */
+int asb_support_map(const double* phi, int64_t n, int64_t nrhs, int64_t ldx, double dmin, double dmax, int mode,
+                    double lambda, int64_t row0, int64_t nloc, double* out, int64_t ldo, void* ws,
+                    asb_stream_t stream);
+/* rhs[b][i] = (i == idx[b]) for nrhs sources given as device indices. */
+int asb_delta_rhs(const int64_t* idx, int64_t n, int64_t nrhs, int64_t ldx, double* rhs, asb_stream_t stream);
+
+/* ---- k1: Procrustes alignment (utils/process.py:198-250) ---------------------------------------- */
+/* cent[f][d] = mean_n frames[f][n][d]   (t0 / t1, :219-220). frames: F x N x 3 float32 AoS. */
+int asb_align_centroids(const float* frames, int64_t F, int64_t N, double* cent, void* ws, asb_stream_t stream);
+/* M[f] = (v0 - t1)^T (v_f - t0) as 9 doubles row-major (:225). */
+int asb_align_cov(const float* frames, int64_t F, int64_t N, const double* cent, double* M, void* ws,
+                  asb_stream_t stream);
+/* 3x3 SVD -> R = U V^T, det fix `R *= -1` (:226-228), T = [rigid ? R : I | t1 - R t0] (:229-233) as 12 doubles. */
+int asb_align_solve(const double* M, const double* cent, int64_t F, int rigid, double* T, asb_stream_t stream);
+/* out[f][n] = float32(T[f] * [v; 1])   (:198-208, stored float32 :246). */
+int asb_align_apply(const float* frames, int64_t F, int64_t N, const double* T, float* out, asb_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ASB_H_ */

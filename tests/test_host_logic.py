@@ -1,0 +1,90 @@
+"""CPU suite (-m "not gpu"): host-side orchestration with the numpy stand-in ops against the golden fixtures, the
+C-ABI surface (library loads, exports every symbol include/asb.h declares -- no compute without a GPU), row sharding."""
+import ctypes
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+from numpy_ops import NumpyOps
+import pipeline_checks
+from animsnapbases_b200 import _lib, engine
+
+
+def test_library_exports_every_declared_symbol():
+    from animsnapbases_b200.build import build_library
+    path = build_library()
+    lib = ctypes.CDLL(path)
+    protos = _lib.parse_header()
+    assert len(protos) >= 50
+    for name in protos:
+        assert hasattr(lib, name), f"{name} declared in include/asb.h but not exported by libasb.so"
+    out = subprocess.run(["nm", "-D", "--defined-only", path], capture_output=True, text=True).stdout
+    exported = {l.split()[-1] for l in out.splitlines() if " T asb_" in l}
+    assert exported == set(protos), f"header/library mismatch: {exported ^ set(protos)}"
+    assert _lib.load().asb_version() == 100
+
+
+def test_product_has_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from animsnapbases_b200.ops import CudaOps
+    with pytest.raises(_lib.AsbError):
+        CudaOps()
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "animsnapbases_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in txt and "from oracle" not in txt and "numpy_ops" not in txt.replace(
+                    "tests/numpy_ops.py", ""), f"{f} references test infrastructure"
+
+
+def test_shard_partition():
+    for n, world in ((1000, 1), (1000, 3), (14290, 8), (33, 2), (1_000_000, 8)):
+        shards = [engine.Shard.make(n, world, r) for r in range(world)]
+        assert sum(s.n for s in shards) == n
+        assert all(s.row0 % 32 == 0 and s.ld % 32 == 0 and s.ld >= s.n for s in shards)
+        assert all(shards[i].row0 + shards[i].n == shards[i + 1].row0 for i in range(world - 1))
+
+
+@pytest.mark.parametrize("name", ["pos_grid", "pos_sphere"])
+def test_position_pipeline_host_logic(name):
+    assert pipeline_checks.check_positions(NumpyOps(), engine.Comm(enabled=False), name)
+
+
+def test_deflation_block_size_invariance():
+    """Blocking the rank-1 updates must not change which vertices are picked nor the components."""
+    import torch
+    from conftest import golden, planar_to_aos, rel
+    g = golden("pos_sphere")
+    ops, comm = NumpyOps(), engine.Comm(enabled=False)
+    N = g["anim"].shape[1]
+    sh = engine.Shard.make(N)
+    st = engine.prepare_snapshots(ops, comm, torch.from_numpy(g["anim"]), g["mass"], "first", sh)
+    outs = [engine.deflate(ops, comm, st.X, sh, int(g["K"]), False, block=b) for b in (1, 5, 16)]
+    for C, W, meas, picked, R in outs[1:]:
+        assert np.array_equal(picked.numpy(), outs[0][3].numpy())
+        assert rel(planar_to_aos(C, N), planar_to_aos(outs[0][0], N)) < 1e-12
+        assert rel(R.numpy(), outs[0][4].numpy()) < 1e-10
+
+
+def test_bar_pipeline_host_logic():
+    assert pipeline_checks.check_bar(NumpyOps(), engine.Comm(enabled=False))
+
+
+def test_two_rank_gloo_row_sharding():
+    """world_size 2 over gloo: sharded deflation + SPLOCS + POD + DEIM reproduce the single-process golden results."""
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29613", PYTHONPATH=ROOT + os.pathsep + os.path.join(ROOT, "tests"))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29613", os.path.join(ROOT, "tests", "gloo_worker.py")],
+                       capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "RANK0 OK" in r.stdout and "RANK1 OK" in r.stdout

@@ -1,0 +1,92 @@
+"""CPU suite: the oracle restatement (oracle/port.py) against the golden vectors produced by the reference itself
+(tests/golden/*.npz, oracle/make_golden.py).  When /root/reference is mounted the port is also checked against the
+live reference on a fresh seed.  LAPACK results may differ in the last bits between hosts, hence rtol 1e-9 (not ==)."""
+import numpy as np
+import pytest
+
+from conftest import golden, rel
+from oracle import port
+
+RT = 1e-9
+
+
+def _pos(name):
+    g = golden(name)
+    prep = port.prepare_snapshots(g["anim"], g["mass"], "first")
+    geo = port.GeodesicHeat(g["anim"][0].astype(float), g["tris"].astype(np.int64))
+    return g, prep, geo
+
+
+@pytest.mark.parametrize("name", ["pos_grid", "pos_sphere"])
+def test_port_positions(name):
+    g, prep, geo = _pos(name)
+    K = int(g["K"])
+    assert np.array_equal(prep["snapTensor"], g["X"]) and prep["pre_scale_factor"] == float(g["scale"])
+    for i, gid in enumerate(g["geo_ids"]):
+        assert rel(geo(int(gid)), g["geo_phi"][i]) < 1e-8
+    C, W, meas, picked, R = port.extract_k_components(prep["snapTensor"], K, "local", geo)
+    assert np.array_equal(picked, g["picked_local"])
+    assert rel(C, g["comps_local"]) < RT and rel(W, g["weigs_local"]) < RT and rel(meas, g["meas_local"]) < RT
+    it, admm, lam, rho = g["splocs"]
+    Wf, Cf, hist, cent = port.splocs_glob_optimization(prep["snapTensor"], C, W, R, geo, int(it), int(admm), lam, rho)
+    assert rel(Wf, g["splocs_W"]) < RT and rel(Cf, g["splocs_C"]) < RT and np.array_equal(cent, g["splocs_centres"])
+    Cg, Wg, mg, pg, _ = port.extract_k_components(prep["snapTensor"], K, "global")
+    assert np.array_equal(pg, g["picked_global"])
+    sg = np.sign((Wg * g["weigs_global"]).sum(axis=0))
+    assert rel(Cg * sg[:, None, None], g["comps_global"]) < RT
+    post = port.post_process_pos(Cg, prep["mean"], prep["pre_scale_factor"], prep["invMassL"], True, False, True)
+    assert rel(post[sg > 0], g["post_global"][sg > 0]) < RT
+
+
+def test_port_bar():
+    b = golden("bar")
+    prep = port.prepare_snapshots(b["snaps"], b["mass"], "first")
+    assert np.array_equal(prep["snapTensor"], b["X"])
+    C, S = port.pod_vectorized(prep["snapTensor"], 200)
+    assert np.allclose(S[:-1], b["pod_sing"][:-1], rtol=1e-9, atol=1e-12 * S[0])
+    d = port.deim(b["post_comps"], 3)
+    assert np.array_equal(d["Pt"], b["deim_Pt"]) and np.array_equal(d["alpha"], b["deim_alpha"])
+    rec = port.deim_reconstruct(b["post_comps"], b["post_snap"], d["alpha"][:10], 10)
+    assert abs(port.frobenius_error(b["post_snap"], rec) - b["deim_rec10_err"][0]) < 1e-7 * b["deim_rec10_err"][0]
+    Cb, Wb, mb, sidx, sp_ = port.nonlinearity_bases_blocks(b["X"], len(b["tets"]), 3, 5)
+    assert np.array_equal(sidx, b["blk_points"]) and np.array_equal(sp_, b["blk_rows"])
+    sg = np.sign((Wb * b["blk_weigs"]).sum(axis=0))
+    assert rel(Cb * sg[:, None, None], b["blk_comps"]) < RT
+    db = port.deim_blocks(b["blk_post"], 3)
+    assert np.array_equal(db["Pt"], b["blk_deim_Pt"])
+
+
+def test_port_align_and_writers():
+    a = golden("align")
+    for rigid in (True, False):
+        out = port.align_frames(a["frames"], rigid)
+        assert np.abs(out - a[f"aligned_rigid{int(rigid)}"]).max() <= 1e-6      # float32 LAPACK may differ across hosts
+    pre, mean, scale = port.preprocess_unit_cube(a["frames"])
+    assert np.allclose(pre, a["pre"]) and np.isclose(scale, a["pre_scale"][0])
+    w = golden("writers")
+    assert port.components_bin_bytes(w["B"]) == w["bin"].tobytes()
+    assert port.points_bin_bytes(w["pts"]) == w["pts_bin"].tobytes()
+
+
+def test_port_against_live_reference():
+    from oracle import ref_shim
+    if not ref_shim.reference_available():
+        pytest.skip("reference not mounted (GPU box)")
+    import contextlib, io
+    from animsnapbases_b200 import synth
+    import oracle.make_golden as mg
+    ref_shim.load_reference()
+    with ref_shim.scratch_cwd():
+        verts0, tris = synth.grid_mesh(15, 11)
+        anim = synth.bump_animation(verts0, 14, n_bumps=4, sigma=0.15, seed=7)
+        mass = synth.lumped_vertex_masses(anim[0].astype(float), tris)
+        with contextlib.redirect_stdout(io.StringIO()):
+            ps, pc = mg.ref_pos_objects(anim, tris, mass, "average", "local", 6, "SPLOCS", dict(max_itrs=2, admm=3, lam=1.5, rho=8.0))
+            cap, _ = mg.run_ref_pos(pc, True)
+    prep = port.prepare_snapshots(anim, mass, "average")
+    assert np.array_equal(prep["snapTensor"], ps.snapTensor)
+    geo = port.GeodesicHeat(np.mean(anim.astype(float), axis=0), tris)
+    C, W, meas, picked, R = port.extract_k_components(prep["snapTensor"], 6, "local", geo)
+    assert np.array_equal(C, pc.comps) and np.array_equal(W, pc.weigs)
+    Wf, Cf, _, _ = port.splocs_glob_optimization(prep["snapTensor"], C, W, R, geo, 2, 3, 1.5, 8.0)
+    assert rel(Wf, cap["W"]) < 1e-12 and rel(Cf, cap["C"]) < 1e-12
