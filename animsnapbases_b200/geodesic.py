@@ -5,11 +5,15 @@ assembles the cotangent Laplacian `Lc`, the lumped areas `A`, the time step `t =
 per-corner geometric constants on the host with numpy/scipy.sparse -- geometry only, no snapshot data.  Every
 *query* then runs on the device through libasb kernels:
 
-    u   = (A - t Lc)^-1 delta_idx          batched Jacobi-PCG   (SPD)
+    u   = (A - t Lc)^-1 delta_idx          multifrontal Cholesky solve (mfsolve.py; asb_mf_forward / asb_mf_backward)
     X   = -grad u / |grad u|               per triangle
     div = integrated divergence            per-vertex gather over incident corners (deterministic)
-    phi = Lc^+ div                          batched Jacobi-PCG on -Lc (PSD, constant null space projected out)
+    phi = Lc^+ div                          multifrontal solve of -Lc grounded at one vertex (defined up to a constant)
     phi -= min(phi); support map            fused in asb_support_map
+
+A direct solver, like the reference's SuperLU factors (utils/support.py:169-171): u decays like exp(-d / sqrt(t)) over
+hundreds of orders of magnitude and only its gradient *direction* is used, so the far field needs componentwise
+relative accuracy, which a Krylov solver cannot give (it also under-reaches: k iterations see k hops).
 
 Several sources are solved at once (multi right-hand side); maps are memoised by vertex id because phi depends on
 the source vertex only (SPLOCS re-queries the same centres every outer iteration, posComponents.py:158-165).
@@ -55,15 +59,14 @@ def cotan_laplacian(verts, tris):
 
 
 class HeatGeodesics:
-    def __init__(self, ops, verts, tris, m: float = 10.0, tol: float = 1e-12, max_iter: int = 20000,
-                 check_every: int = 25):
+    def __init__(self, ops, verts, tris, m: float = 10.0, leaf_size: int = 64):
+        from .mfsolve import MultifrontalSolver
         self.ops = ops
         verts = np.asarray(verts, dtype=np.float64)
         tris = np.asarray(tris, dtype=np.int64)
         self.n = n = len(verts)
         self.T = len(tris)
         self.ldx = (n + 31) // 32 * 32
-        self.tol, self.max_iter, self.check_every = tol, max_iter, check_every
         e01 = verts[tris[:, 1]] - verts[tris[:, 0]]
         e12 = verts[tris[:, 2]] - verts[tris[:, 1]]
         e20 = verts[tris[:, 0]] - verts[tris[:, 2]]
@@ -97,70 +100,17 @@ class HeatGeodesics:
         h = np.mean([_veclen(e01), _veclen(e12), _veclen(e20)])
         self.t = m * h ** 2
         Lc, va = cotan_laplacian(verts, tris)
-        heat = (sparse.diags(va) - self.t * Lc).tocsr()
-        pois = (-Lc).tocsr()
-        heat.sort_indices()
-        pois.sort_indices()
-        self.heat = self._upload_csr(heat)
-        self.pois = self._upload_csr(pois)
-        dh = heat.diagonal()
-        dp = pois.diagonal()
-        dp = np.where(dp > 0, dp, 1.0)
-        self.heat_dinv = self._pad(1.0 / dh)
-        self.pois_dinv = self._pad(1.0 / dp)
+        self.heat = MultifrontalSolver(ops, (sparse.diags(va) - self.t * Lc).tocsr(), verts, leaf_size)
+        self.pois = MultifrontalSolver(ops, (-Lc).tocsr(), verts, leaf_size, ground=0)
         self.tri = ops.to_device(tris.astype(np.int32))
         self.gconst = ops.to_device(np.ascontiguousarray(gconst))
         self.dconst = ops.to_device(np.ascontiguousarray(dconst.reshape(self.T * 3, 8)))
         self.vc_ptr = ops.to_device(vc_ptr)
         self.vc_idx = ops.to_device(vc_idx)
-        self.stats = {"queries": 0, "cache_hits": 0, "solves": 0, "heat_iters": 0, "poisson_iters": 0}
+        self.stats = {"queries": 0, "cache_hits": 0, "solves": 0, "fronts": self.heat.stats["fronts"],
+                      "levels": self.heat.stats["levels"],
+                      "operator_bytes": self.heat.stats["operator_bytes"] + self.pois.stats["operator_bytes"]}
         self._cache = {}
-
-    def _pad(self, v):
-        out = np.zeros(self.ldx)
-        out[: self.n] = v
-        return self.ops.to_device(out)
-
-    def _upload_csr(self, m):
-        return (self.ops.to_device(m.indptr.astype(np.int32)), self.ops.to_device(m.indices.astype(np.int32)),
-                self.ops.to_device(m.data.astype(np.float64)))
-
-    # ------------------------------------------------------------------ batched PCG
-    def _pcg(self, csr, dinv, b, singular: bool, key: str):
-        """Solve A x = b for every row of b (B, ldx); returns x.  Jacobi preconditioner, device-resident scalars,
-        one host read of the residuals every `check_every` iterations."""
-        ops, n = self.ops, self.n
-        B = b.shape[0]
-        x = ops.zeros((B, self.ldx))
-        r = b.clone()
-        if singular:
-            ops.remove_mean(r, n)
-        z = ops.zeros((B, self.ldx))
-        ops.axpby(z, 1.0, r, dinv, 0.0, None, n)
-        p = z.clone()
-        Ap = ops.zeros((B, self.ldx))
-        rz = ops.zeros((B,))
-        rz_new = ops.zeros((B,))
-        pAp = ops.zeros((B,))
-        ops.batched_dot(r, z, n, rz)
-        rz0 = rz.clone()
-        it = 0
-        while it < self.max_iter:
-            for _ in range(self.check_every):
-                ops.spmv(csr, p, Ap)
-                ops.batched_dot(p, Ap, n, pAp)
-                ops.pcg_update_xr(x, r, z, p, Ap, dinv, rz, pAp, n)
-                ops.batched_dot(r, z, n, rz_new)
-                ops.pcg_update_p(p, z, rz_new, rz, n)
-                rz, rz_new = rz_new, rz
-                it += 1
-            ratio = float(torch.max(rz / rz0).item())     # host sync, once per `check_every` iterations
-            if not np.isfinite(ratio):
-                raise FloatingPointError("PCG broke down (non-finite residual)")
-            if ratio < self.tol * self.tol:
-                break
-        self.stats[key] += it
-        return x
 
     # ------------------------------------------------------------------ queries
     def distances(self, idx_dev):
@@ -170,12 +120,12 @@ class HeatGeodesics:
         B = idx_dev.numel()
         rhs = ops.empty((B, self.ldx))
         ops.delta_rhs(idx_dev, n, rhs)
-        u = self._pcg(self.heat, self.heat_dinv, rhs, False, "heat_iters")
+        u = self.heat.solve(rhs)
         Xt = ops.empty((B, self.T, 3))
         div = ops.zeros((B, self.ldx))
         ops.heat_divergence(u, self.tri, self.gconst, self.dconst, self.vc_ptr, self.vc_idx, n, Xt, div)
         # reference solves Lc phi = div; we solve (-Lc) psi = div  =>  phi = -psi
-        psi = self._pcg(self.pois, self.pois_dinv, div, True, "poisson_iters")
+        psi = self.pois.solve(div)
         phi = ops.empty((B, self.ldx))
         ops.axpby(phi, -1.0, psi, None, 0.0, None, n)
         self.stats["solves"] += B

@@ -294,6 +294,17 @@ class CudaOps:
         nrhs, ldx = x.shape
         self._call("asb_remove_mean", self._p(x), n, nrhs, ldx, self._p(self.workspace(8 * (66 * nrhs + 1024))))
 
+    def gather_rows(self, src, idx, out, n):
+        self._call("asb_gather_rows", self._p(src), self._p(idx), self._p(out), n, src.shape[0], src.stride(0), out.stride(0))
+
+    def mf_forward(self, desc, vals, src, slots, work, rhs, y, upd):
+        self._call("asb_mf_forward", self._p(desc), self._p(vals), self._p(src), slots, self._p(work), work.shape[0], self._p(rhs),
+                   self._p(y), self._p(upd), rhs.shape[0], rhs.stride(0), upd.stride(0))
+
+    def mf_backward(self, desc, vals, bnd, work, y, x):
+        self._call("asb_mf_backward", self._p(desc), self._p(vals), self._p(bnd), self._p(work), work.shape[0], self._p(y), self._p(x),
+                   y.shape[0], y.stride(0))
+
     def heat_divergence(self, u, tri, gconst, dconst, vc_ptr, vc_idx, n, Xt, div):
         nrhs, ldx = u.shape
         self._call("asb_heat_divergence", self._p(u), nrhs, ldx, self._p(tri), self._p(gconst), self._p(dconst), tri.shape[0],

@@ -198,6 +198,20 @@ int asb_axpby(double* y, double alpha, const double* a, const double* row_scale,
               int64_t nrhs, int64_t ldx, asb_stream_t stream);
 /* x[b] -= mean(x[b])  (projection onto the complement of the constant null space of the cotan Laplacian). */
 int asb_remove_mean(double* x, int64_t n, int64_t nrhs, int64_t ldx, void* ws, asb_stream_t stream);
+/* Multifrontal Cholesky solve (animsnapbases_b200/mfsolve.py): the direct-solver replacement of the reference's SuperLU
+ * `solve` calls (utils/support.py:182, :205).  desc: fronts x 8 int64 {own_start, n1, n2, mt_off, slot_off, upd_off, ldm,
+ * row2}; vals: dense per-front operators [L11^-1 ; -L21 L11^-1]; src: 2 x slots child->parent gather map (-1 = none);
+ * work: nwork x 2 int32 {front, first row/column} of ONE tree level.  Vectors are in elimination order.
+ * forward (call per level, deepest first):  y[own] = L11^-1 f1,  upd_t = f2 - L21 L11^-1 f1
+ * backward (call per level, root first):    x[own] = L11^-T (y[own] - L21^T x[bnd]) */
+int asb_mf_forward(const int64_t* desc, const double* vals, const int32_t* src, int64_t slots, const int32_t* work,
+                   int64_t nwork, const double* rhs, double* y, double* upd, int64_t nrhs, int64_t ldx, int64_t ldu,
+                   asb_stream_t stream);
+int asb_mf_backward(const int64_t* desc, const double* vals, const int32_t* bnd, const int32_t* work, int64_t nwork,
+                    const double* y, double* x, int64_t nrhs, int64_t ldx, asb_stream_t stream);
+/* out[b][i] = in[b][map[i]], i < n  (permutation to / from elimination order). */
+int asb_gather_rows(const double* in, const int32_t* map, double* out, int64_t n, int64_t nrhs, int64_t ldin, int64_t ldout,
+                    asb_stream_t stream);
 /* Heat-method step 2+3: per triangle unit gradient of u, integrated divergence gathered per vertex through a
  * vertex->corner CSR (deterministic, no atomics).  tri: T x 3 int32;  gconst: T x 9 (n x e12, n x e20, n x e01
  * scaled by 1/(2A));  dconst: T x 3 x 8 per-corner (cot1, e1[3], cot2, e2[3]) with the reference's

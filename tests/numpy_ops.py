@@ -339,6 +339,37 @@ class NumpyOps:
         for b in range(rhs.shape[0]):
             rhs.numpy()[b, int(idx[b])] = 1.0
 
+    # multifrontal solve (animsnapbases_b200/mfsolve.py) ---------------------------------------------
+    def gather_rows(self, src, idx, out, n):
+        out.numpy()[:, :n] = src.numpy()[:, idx.numpy()[:n]]
+
+    def mf_forward(self, desc, vals, src, slots, work, rhs, y, upd):
+        D, V, S = desc.numpy(), vals.numpy(), src.numpy()
+        r, yy, uu = rhs.numpy(), y.numpy(), upd.numpy()
+        for t in np.unique(work.numpy()[:, 0]):
+            s0, n1, n2, mo, so, uo, ldm, row2 = (int(v) for v in D[t])
+            f = np.zeros((r.shape[0], n1 + n2))
+            f[:, :n1] = r[:, s0:s0 + n1]
+            for ci in range(2):
+                sl = S[ci, so:so + n1 + n2]
+                ok = sl >= 0
+                f[:, ok] += uu[:, sl[ok]]
+            M = V[mo: mo + (row2 + n2) * ldm].reshape(row2 + n2, ldm)
+            yy[:, s0:s0 + n1] = f[:, :n1] @ M[:n1, :n1].T
+            if n2:
+                uu[:, uo:uo + n2] = f[:, n1:] + f[:, :n1] @ M[row2:row2 + n2, :n1].T
+
+    def mf_backward(self, desc, vals, bnd, work, y, x):
+        D, V, Bd = desc.numpy(), vals.numpy(), bnd.numpy()
+        yy, xx = y.numpy(), x.numpy()
+        for t in np.unique(work.numpy()[:, 0]):
+            s0, n1, n2, mo, so, uo, ldm, row2 = (int(v) for v in D[t])
+            M = V[mo: mo + (row2 + n2) * ldm].reshape(row2 + n2, ldm)
+            acc = yy[:, s0:s0 + n1] @ M[:n1, :n1]
+            if n2:
+                acc = acc + xx[:, Bd[uo:uo + n2]] @ M[row2:row2 + n2, :n1]
+            xx[:, s0:s0 + n1] = acc
+
     # alignment ------------------------------------------------------------------------------------
     def align(self, frames, rigid):
         v = frames.numpy().astype(np.float64)

@@ -369,8 +369,12 @@ def test_geodesic_kernels(cuda_ops):
     x[:, :n] = torch.from_numpy(rng.standard_normal((3, n)))
     xg = dev(cuda_ops, x)
     yr, yg = torch.zeros_like(x), cuda_ops.zeros((3, ldx))
-    REF.spmv(gr.heat, x, yr)
-    cuda_ops.spmv(gg.heat, xg, yg)
+    from animsnapbases_b200.geodesic import cotan_laplacian
+    Lc = cotan_laplacian(verts, tris)[0].tocsr()
+    Lc.sort_indices()
+    csr = (Lc.indptr.astype(np.int32), Lc.indices.astype(np.int32), Lc.data)
+    REF.spmv(tuple(REF.to_device(a) for a in csr), x, yr)
+    cuda_ops.spmv(tuple(cuda_ops.to_device(a) for a in csr), xg, yg)
     close(yg, yr, 1e-14, "spmv")
     dr, dg = torch.zeros(3, dtype=torch.float64), cuda_ops.zeros((3,))
     REF.batched_dot(x, yr, n, dr)
@@ -395,7 +399,45 @@ def test_geodesic_kernels(cuda_ops):
     orr, og = torch.zeros((3, ldx), dtype=torch.float64), cuda_ops.zeros((3, ldx))
     REF.support_map(pr, n, 0, 0, 2, 0, 0, n, orr)
     cuda_ops.support_map(pg, n, 0, 0, 2, 0, 0, n, og)
-    close(og, orr, 1e-9, "heat-method distances (PCG on device vs numpy PCG)")
+    close(og, orr, 1e-11, "heat-method distances (multifrontal solve on device vs numpy statement)")
+
+
+@pytest.mark.parametrize("nx,ny,leaf,ground", [(9, 7, 64, None), (60, 45, 16, None), (150, 120, 64, None), (60, 45, 16, 5),
+                                               (150, 120, 32, 0)])
+def test_multifrontal_solve(cuda_ops, nx, ny, leaf, ground):
+    """asb_mf_forward / asb_mf_backward (+ batched device factorisation) against SuperLU, the reference's solver
+    (utils/support.py:169-171): componentwise relative accuracy for the heat system, residual for the grounded Poisson."""
+    from scipy import sparse
+    from scipy.sparse.linalg import splu
+    from animsnapbases_b200 import synth
+    from animsnapbases_b200.geodesic import cotan_laplacian
+    from animsnapbases_b200.mfsolve import MultifrontalSolver
+    verts, tris = synth.grid_mesh(nx, ny)
+    verts = verts + (0.2 / max(nx, ny)) * np.random.default_rng(3).standard_normal(verts.shape)
+    n = len(verts)
+    Lc, va = cotan_laplacian(verts, tris)
+    h2 = float(np.mean(va))
+    A = (sparse.diags(va) - 10.0 * h2 * Lc).tocsc() if ground is None else (-Lc).tocsc()
+    mf = MultifrontalSolver(cuda_ops, A, verts, leaf_size=leaf, ground=ground)
+    ldx = mf.ldx
+    rng = np.random.default_rng(4)
+    B = 5
+    rhs = np.zeros((B, ldx))
+    if ground is None:
+        rhs[np.arange(B), rng.integers(0, n, B)] = 1.0              # heat sources
+        x = mf.solve(cuda_ops.to_device(rhs)).cpu().numpy()[:, :n]
+        lu = splu(A)
+        ref = np.stack([lu.solve(rhs[b, :n]) for b in range(B)])
+        assert ref.min() > 0
+        err = np.max(np.abs(x - ref) / ref)
+        assert err < 1e-11, f"componentwise relative error {err:.2e} (smallest value {ref.min():.1e})"
+    else:
+        d = rng.standard_normal((B, n))
+        rhs[:, :n] = d - d.mean(axis=1, keepdims=True)
+        x = mf.solve(cuda_ops.to_device(rhs)).cpu().numpy()[:, :n]
+        assert np.all(x[:, ground] == 0.0)
+        res = np.linalg.norm((A @ x.T).T - rhs[:, :n]) / np.linalg.norm(rhs)
+        assert res < 1e-11, res
 
 
 # ------------------------------------------------------------------------------------------------ alignment

@@ -7,6 +7,7 @@ import sys
 
 import numpy as np
 import pytest
+import torch
 
 from conftest import ROOT
 from numpy_ops import NumpyOps
@@ -88,3 +89,33 @@ def test_two_rank_gloo_row_sharding():
                        capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "RANK0 OK" in r.stdout and "RANK1 OK" in r.stdout
+
+
+@pytest.mark.parametrize("nx,leaf,ground", [(40, 16, None), (40, 16, 3), (7, 64, None)])
+def test_multifrontal_symbolic_and_numeric(nx, leaf, ground):
+    """Host side of animsnapbases_b200/mfsolve.py (ordering, symbolic maps, batched numeric factorisation with torch on the
+    CPU) driven through the numpy statement of the two solve kernels, against SuperLU."""
+    from scipy import sparse
+    from scipy.sparse.linalg import splu
+    from animsnapbases_b200 import synth
+    from animsnapbases_b200.geodesic import cotan_laplacian
+    from animsnapbases_b200.mfsolve import MultifrontalSolver
+    from numpy_ops import NumpyOps
+    verts, tris = synth.grid_mesh(nx, nx + 3)
+    n = len(verts)
+    Lc, va = cotan_laplacian(verts, tris)
+    A = (sparse.diags(va) - 10.0 * float(np.mean(va)) * Lc).tocsc() if ground is None else (-Lc).tocsc()
+    mf = MultifrontalSolver(NumpyOps(), A, verts, leaf_size=leaf, ground=ground)
+    rng = np.random.default_rng(0)
+    rhs = np.zeros((2, mf.ldx))
+    if ground is None:
+        rhs[[0, 1], [n // 3, n - 2]] = 1.0
+        x = mf.solve(torch.from_numpy(rhs)).numpy()[:, :n]
+        lu = splu(A)
+        ref = np.stack([lu.solve(rhs[b, :n]) for b in range(2)])
+        assert np.max(np.abs(x - ref) / ref) < 1e-12
+    else:
+        d = rng.standard_normal((2, n))
+        rhs[:, :n] = d - d.mean(axis=1, keepdims=True)
+        x = mf.solve(torch.from_numpy(rhs)).numpy()[:, :n]
+        assert np.linalg.norm((A @ x.T).T - rhs[:, :n]) / np.linalg.norm(rhs) < 1e-12

@@ -1,0 +1,125 @@
+#!/usr/bin/env python
+"""Per-kernel timing of the hot path at a given snapshot shape (CUDA events on the launching stream, inputs >> L2).
+Prints one JSON line per C-ABI entry point with its algorithmic bytes / flops and the achieved rate, next to a plain
+device copy (HBM ceiling) and cuBLAS DGEMM (fp64 tensor ceiling).  Used to pick the kernel to optimise next."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from animsnapbases_b200.ops import CudaOps, pad_ld  # noqa: E402
+
+
+def timed(fn, reps=3, warm=1):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    best = 1e30
+    for _ in range(reps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        best = min(best, a.elapsed_time(b))
+    return best * 1e-3
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--verts", type=int, default=1000000)
+    ap.add_argument("--frames", type=int, default=2000)
+    ap.add_argument("--comps", type=int, default=200)
+    ap.add_argument("--only", default="")
+    args = ap.parse_args()
+    ops = CudaOps("cuda:0")
+    N, F, K = args.verts, args.frames, args.comps
+    ld = pad_ld(N)
+    M = 3 * ld
+    S = 8.0 * F * M
+    only = set(args.only.split(",")) if args.only else None
+
+    def want(n):
+        return only is None or n in only
+
+    X = ops.empty((F, 3, ld))
+    for f0 in range(0, F, 50):
+        X[f0:f0 + 50].normal_()
+    Kp = (K + 3) // 4 * 4
+    W = ops.empty((F, Kp)).normal_()
+    C = ops.empty((K, 3, ld)).normal_()
+    out = []
+
+    def rec(name, secs, nbytes=None, flops=None, note=""):
+        r = {"kernel": name, "ms": secs * 1e3}
+        if nbytes:
+            r["GB/s"] = nbytes / secs / 1e9
+        if flops:
+            r["TFLOP/s"] = flops / secs / 1e12
+        if note:
+            r["note"] = note
+        print(json.dumps(r), flush=True)
+        out.append(r)
+
+    # ceilings
+    if want("copy"):
+        a = torch.empty(1 << 30, dtype=torch.float64, device=ops.device)
+        b = torch.empty_like(a)
+        rec("torch_copy_8GiB", timed(lambda: b.copy_(a)), nbytes=2.0 * a.numel() * 8)
+        rec("torch_sum_read_8GiB", timed(lambda: a.sum()), nbytes=1.0 * a.numel() * 8)
+        del a, b
+    if want("dgemm"):
+        a = torch.randn(8192, 8192, dtype=torch.float64, device=ops.device)
+        b = torch.randn(8192, 8192, dtype=torch.float64, device=ops.device)
+        rec("cublas_dgemm_8192", timed(lambda: torch.matmul(a, b), reps=5), flops=2.0 * 8192 ** 3)
+        del a, b
+        xs = X.view(F, M)[:, : min(M, 300000)]
+        rec("cublas_dgemm_WtX_K%dxF%dx%d" % (K, F, xs.shape[1]), timed(lambda: torch.matmul(W[:, :K].t(), xs)),
+            flops=2.0 * K * F * xs.shape[1])
+        rec("cublas_gram_XXt_F%dx%d" % (F, xs.shape[1]), timed(lambda: torch.matmul(xs, xs.t())), flops=2.0 * F * F * xs.shape[1],
+            note="full (non-symmetric) flop count")
+    # streaming
+    e = ops.empty((ld,))
+    g = ops.empty((3, ld))
+    if want("stream"):
+        rec("asb_vertex_energy", timed(lambda: ops.vertex_energy(X, N, out=e)), nbytes=S)
+        rec("asb_deflate_gemv", timed(lambda: ops.deflate_gemv(X, N, W, 0, g)), nbytes=S)
+        Wz = ops.zeros((F, Kp))
+        for nb in (4, 8, 16):
+            rec("asb_rank_update_nb%d" % nb, timed(lambda: ops.rank_update(X, N, Wz, C, 0, nb, e), reps=2), nbytes=2 * S)
+        mean = ops.zeros((3, ld))
+        rec("asb_center_stats", timed(lambda: ops.center_stats(X, mean, N)), nbytes=S)
+        rec("asb_center_apply", timed(lambda: ops.center_apply(X, mean, 1.0, N), reps=2), nbytes=2 * S)
+        val = ops.zeros((K,)); idx = ops.zeros((K,), torch.int64); sp = ops.zeros((K,))
+        rec("asb_component_centers", timed(lambda: ops.component_centers(C, None, K, N, 0, val, idx, sp)), nbytes=8.0 * K * M)
+    Xm, Cm = X.view(F, M), C.view(K, M)
+    if want("gemm"):
+        rec("asb_gemm_nt_XCt", timed(lambda: ops.gemm_nt(Xm, F, Cm, K, M)), flops=2.0 * F * K * M, nbytes=S + 8.0 * K * M)
+        rec("asb_gemm_nt_CCt_sym", timed(lambda: ops.gemm_nt(Cm, K, Cm, K, M, symmetric=True)), flops=1.0 * K * (K + 1) * M,
+            nbytes=8.0 * K * M)
+        Fp = (F + 1) // 2 * 2
+        A = ops.empty((K, Fp)).normal_()
+        B0 = ops.empty((K, 3, ld))
+        rec("asb_gemm_nn_B0", timed(lambda: ops.gemm_nn(A, K, F, Xm, M, 1.0, B0.view(K, M))), flops=2.0 * K * F * M,
+            nbytes=S + 8.0 * K * M)
+        del B0
+    if want("gram"):
+        G = ops.zeros((F, (F + 1) // 2 * 2))
+        rec("asb_gemm_nt_gram_sym", timed(lambda: ops.gemm_nt(Xm, F, Xm, F, M, symmetric=True, out=G), reps=1, warm=1),
+            flops=1.0 * F * (F + 1) * M, nbytes=S, note="symmetric-half flops")
+    if want("admm"):
+        B0 = ops.empty((K, 3, ld)).normal_()
+        U = ops.zeros((K, 3, ld))
+        Lam = ops.empty((K, ld)).uniform_(0, 2)
+        Hr = ops.zeros((K, Kp))
+        Hr[:, :K] = torch.eye(K, dtype=torch.float64, device=ops.device) * 0.5
+        rec("asb_admm_iter", timed(lambda: ops.admm_iter(Hr, B0, C, U, Lam, K, N, 0.1)), flops=2.0 * K * K * M,
+            nbytes=8.0 * K * M * 5 + 8.0 * K * ld)
+    json.dump(out, open(os.path.join("gpurun_out", "kbench_%dx%d.json" % (N, F)), "w"), indent=1)
+
+
+if __name__ == "__main__":
+    main()
