@@ -344,3 +344,114 @@ def deim(ops, comm, C, shard, K):
         print("ERROR!: zero residual!!")
         return None
     return Pt.cpu().numpy()
+
+
+# ====================================================================================== per-dimension Gram helpers
+def _plane(T, K, d):
+    """(K, ld) view of dimension d of a planar (K, 3, ld) tensor (row stride 3*ld)."""
+    return T[:, d, :]
+
+
+def weighted_row_grams(ops, comm, T, shard, K, row_scale):
+    """[G_x, G_y, G_z] with G_d = T_d diag(row_scale^2) T_d^T (K x K, host).  row_scale = sqrt(mass) gives U^T M U
+    (posComponents.py:305-313); None gives the plain Gram whose eigenvalues are the squared singular values (:344-356)."""
+    Ts = T
+    if row_scale is not None:
+        Ts = ops.ingest(ops.export_aos(T, row_scale, shard.n), None, shard.ld)
+    ld = T.shape[2]
+    out = []
+    for d in range(3):
+        A = _plane(Ts, K, d)
+        G = ops.gemm_nt(A, K, A, K, ld, symmetric=True)
+        comm.allreduce_sum(G)
+        out.append(G.cpu().numpy())
+    return out
+
+
+def row_lq(ops, comm, T, shard, K):
+    """T_d = L_d Q_d per dimension: Q (planar copy of T with orthonormal rows, CGS2) and the K x K factors L_d = T_d Q_d^T
+    (DMMA GEMM, all-reduced).  The small factors carry the singular values of T_d without squaring its condition number
+    (post-processed components contain the mean shape: sigma_1 / sigma_K ~ 1e8 is normal)."""
+    ld = T.shape[2]
+    Q = T.clone()
+    orthogonalize_rows(ops, comm, Q, shard, K)
+    Ls = []
+    for d in range(3):
+        L = ops.gemm_nt(_plane(T, K, d), K, _plane(Q, K, d), K, ld)
+        comm.allreduce_sum(L)
+        Ls.append(L)
+    return Q, Ls
+
+
+def row_singular_values(ops, comm, T, shard, K):
+    """Singular values of T[:, d, :] (K x N), descending, per dimension (host arrays)."""
+    _, Ls = row_lq(ops, comm, T, shard, K)
+    return [torch.linalg.svdvals(L).cpu().numpy() for L in Ls]
+
+
+def orth_rows(ops, comm, T, shard, K):
+    """`comps[:, :, l] = orth(comps[:, :, l].T).T` (posComponents.py:285-287): rows of T_d replaced by the right singular
+    vectors of T_d (descending singular values; sign per vector is LAPACK's choice in the reference).  T_d = L Q (CGS2),
+    L = U S Vh (replicated K x K SVD), new rows = Vh Q.  Returns the numerical rank per dimension (scipy orth tolerance)."""
+    ld = T.shape[2]
+    Kp = (K + 1) // 2 * 2
+    Q, Ls = row_lq(ops, comm, T, shard, K)
+    ranks = []
+    for d in range(3):
+        _, S, Vh = torch.linalg.svd(Ls[d])
+        sig = S.cpu().numpy()
+        tol = max(shard.n_global, K) * np.finfo(np.float64).eps * sig[0]
+        ranks.append(int((sig > tol).sum()))
+        A = ops.zeros((K, Kp))
+        A[:, :K] = Vh
+        ops.gemm_nn(A, K, K, _plane(Q, K, d), ld, 1.0, _plane(T, K, d))
+    return ranks
+
+
+def sparsity_and_rank(ops, comm, T, shard, K):
+    """Self-checks of posComponents.post_process_components (utils/utils.py:41-74): fraction of exact zeros and numerical
+    rank (numpy.linalg.matrix_rank tolerance) of comps[:, :, d], per dimension."""
+    n = shard.n
+    cnt = torch.stack([torch.count_nonzero(T[:, d, :n]) for d in range(3)]).to(F64)
+    comm.allreduce_sum(cnt)
+    sparsity = [1.0 - float(c) / (K * shard.n_global) for c in cnt.tolist()]
+    ranks = []
+    for sig in row_singular_values(ops, comm, T, shard, K):
+        ranks.append(int((sig > sig[0] * max(shard.n_global, K) * np.finfo(np.float64).eps).sum()))
+    return sparsity, ranks
+
+
+def gather_rows_host(comm, arr, shard, axis):
+    """Concatenate the row shards of a host array on every rank (outputs only)."""
+    parts = [None] * comm.world
+    comm.dist.all_gather_object(parts, arr)
+    return np.concatenate(parts, axis=axis)
+
+
+def reconstruction_errors(ops, comm, X, shard, C, W, ks):
+    """posComponents.test_convergence (posComponents.py:192-214): Frobenius, max-pointwise and per-axis relative errors
+    of X ~ W[:, :k] C[:k].  A SURVEY 8(f) 'next' row: the reconstruction GEMM is the DMMA kernel, the norms are still
+    torch reductions."""
+    Fr, _, ld = X.shape
+    M = 3 * ld
+    fro, mx, rx, ry, rz = [], [], [], [], []
+    rec = ops.empty((Fr, 3, ld))
+    xmax = X.max().reshape(1)
+    comm.allreduce_max(xmax)
+    xn = torch.stack([(X[:, d, :] ** 2).sum() for d in range(3)])
+    comm.allreduce_sum(xn)
+    for k in ks:
+        kk = (k + 1) // 2 * 2
+        A = ops.zeros((Fr, kk))
+        A[:, :k] = W[:, :k]
+        ops.gemm_nn(A, Fr, k, C.view(C.shape[0], M), M, 1.0, rec.view(Fr, M))
+        err = X - rec
+        e2 = torch.stack([(err[:, d, :] ** 2).sum() for d in range(3)])
+        comm.allreduce_sum(e2)
+        em = err.abs().max().reshape(1)
+        comm.allreduce_max(em)
+        fro.append(float(torch.sqrt(e2.sum()).item()))
+        mx.append(float((em / xmax).item()))
+        rel = torch.sqrt(e2 / xn).tolist()
+        rx.append(rel[0]); ry.append(rel[1]); rz.append(rel[2])
+    return fro, mx, rx, ry, rz

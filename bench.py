@@ -32,7 +32,7 @@ UNIT = "s"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--steps", type=int, default=1)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--grid", type=int, nargs=2, default=[1000, 1000], help="synthetic planar grid (nx ny) -> N = nx*ny vertices")
@@ -237,7 +237,8 @@ def main():
     if not args.no_e2e:
         host_in = torch.empty(anim_dev.shape, dtype=torch.float32, pin_memory=True)
         host_in.copy_(anim_dev)
-        del anim_dev
+        del anim_dev, st                                   # one resident snapshot tensor at a time (48 GB at 1M x 2000)
+        torch.cuda.empty_cache()
         host_C = torch.empty((K, 3, sh.ld), dtype=torch.float64, pin_memory=True)
         host_W = torch.empty((F, (K + 3) // 4 * 4), dtype=torch.float64, pin_memory=True)
         n_e2e = max(1, min(args.steps, 2))

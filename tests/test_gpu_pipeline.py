@@ -14,3 +14,10 @@ def test_position_pipeline(cuda_ops, name):
 
 def test_bar_pipeline(cuda_ops):
     assert pipeline_checks.check_bar(cuda_ops, engine.Comm(enabled=False))
+
+
+def test_pos_components_protocol(cuda_ops, tmp_path):
+    """The reference's main.py:71-100 protocol through libasb.so, against the reference's golden outputs."""
+    import api_checks
+    from animsnapbases_b200 import engine
+    assert api_checks.check_pos_protocol(cuda_ops, engine.Comm(enabled=False), tmp_path)

@@ -119,3 +119,9 @@ def test_multifrontal_symbolic_and_numeric(nx, leaf, ground):
         rhs[:, :n] = d - d.mean(axis=1, keepdims=True)
         x = mf.solve(torch.from_numpy(rhs)).numpy()[:, :n]
         assert np.linalg.norm((A @ x.T).T - rhs[:, :n]) / np.linalg.norm(rhs) < 1e-12
+
+
+def test_pos_components_protocol_host_logic(tmp_path):
+    """posSnapshots / posComponents drop-in protocol with the numpy statement of the kernels (host logic only)."""
+    import api_checks
+    assert api_checks.check_pos_protocol(NumpyOps(), engine.Comm(enabled=False), tmp_path)
