@@ -7,24 +7,9 @@
 // sm_100a has no fp64 kind of tcgen05.mma; fp64 tensor work is `mma.sync.aligned.m8n8k4.f64` (SASS DMMA.8x8x4).
 // Operand tiles are staged global -> shared with a 3-stage cp.async (LDGSTS) pipeline; shared tiles use padded
 // strides (stride mod 16 doubles == 4 or 12) so that every 8x4 / 4x8 fragment read is bank-conflict free.
-#include "common.cuh"
+#include "dmma.cuh"
 
 namespace asb {
-
-__device__ __forceinline__ void dmma(double& d0, double& d1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-                 : "+d"(d0), "+d"(d1)
-                 : "d"(a), "d"(b));
-}
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem, int src_bytes) {
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gmem), "r"(src_bytes));
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-    asm volatile("cp.async.wait_group %0;" ::"n"(N));
-}
 
 constexpr int BM = 128, BN = 128, BK = 16, STAGES = 3, GEMM_THREADS = 256;
 constexpr int A_LD = BK + 4;         // 20 doubles: rows 160 B apart -> conflict-free 8x4 fragment reads
@@ -217,122 +202,187 @@ gemm_nn_kernel(const double* __restrict__ A, int64_t lda, int64_t r, int64_t q, 
     }
 }
 
-// ------------------------------------------------------------------------------------------ fused ADMM iteration
-// CTA = 8 vertices (x 3 planes = 24 columns) x all K rows. 4 warps = 4 row groups of MTW m-tiles; each warp owns the
-// x, y, z accumulators of the same (k, n) so the group-lasso prox is thread-local.
-constexpr int ADMM_BK = 8;
-constexpr int ADMM_ALD = ADMM_BK + 4;  // 12
-constexpr int ADMM_DLD = 24 + 4;       // 28
-template <int MTW>
-__global__ void __launch_bounds__(128)
-admm_iter_kernel(const double* __restrict__ Hr, int64_t ldh, const double* __restrict__ B0, double* __restrict__ Z,
-                 double* __restrict__ U, const double* __restrict__ Lambda, int64_t K, int64_t N, int64_t ld,
-                 double inv_rho) {
-    constexpr int KP = 4 * MTW * 8;  // padded rows
-    constexpr int ASTAGE = KP * ADMM_ALD;
-    extern __shared__ __align__(16) double smem[];
-    double* Ds = smem;                   // [KP][28]   (Z - U) tile, k-major
-    double* As = smem + KP * ADMM_DLD;   // STAGES x [KP][12]
-    const int64_t n0 = (int64_t)blockIdx.x * 8;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, lr = lane >> 2, lc = lane & 3;
-    const int64_t C3 = 3 * ld;
 
-    // stage D = Z - U (rows >= K are zero): KP rows x 3 planes x 4 double2
-    for (int t = threadIdx.x; t < KP * 12; t += 128) {
-        const int k = t / 12, rem = t % 12, d = rem >> 2, c2 = (rem & 3) * 2;
-        double2 v = make_double2(0.0, 0.0);
-        if (k < K) {
-            const int64_t off = (int64_t)k * C3 + d * ld + n0 + c2;
-            const double2 z = ld2(Z + off), u = ld2(U + off);
-            v.x = z.x - u.x;
-            v.y = z.y - u.y;
-        }
-        st2(Ds + k * ADMM_DLD + d * 8 + c2, v);
-    }
-    auto load_a = [&](int stage, int64_t k0) {
-        // KP rows x 4 chunks of 16 B
-        for (int q = threadIdx.x; q < KP * 4; q += 128) {
-            const int row = q >> 2, cc = (q & 3) * 2;
-            const bool ok = row < K && k0 + cc < K;
-            const double* src = ok ? Hr + (int64_t)row * ldh + k0 + cc : Hr;
-            cp_async16(As + stage * ASTAGE + row * ADMM_ALD + cc, src, ok ? 16 : 0);
-        }
-    };
-    const int64_t nk = (K + ADMM_BK - 1) / ADMM_BK;
-#pragma unroll
-    for (int s = 0; s < STAGES - 1; ++s) {
-        if (s < nk) load_a(s, (int64_t)s * ADMM_BK);
-        cp_async_commit();
-    }
-    double acc[MTW][3][2];
-#pragma unroll
-    for (int i = 0; i < MTW; ++i)
-#pragma unroll
-        for (int d = 0; d < 3; ++d) acc[i][d][0] = acc[i][d][1] = 0.0;
+// ------------------------------------------------------------------------------------------ skinny variants
+// One operand has at most 256 rows (the K components / the K x F weight operator): it becomes the DMMA m-side and is
+// covered COMPLETELY by one CTA (no 128-row tile quantisation: K = 200 costs 25 m-tiles, not 32), dealt to WM = 4
+// row-warps at run time (7,6,6,6 -> sub-partition loads 13,13,12,12 with warp id = wm * 2 + wn).  The long operand is the
+// n-side, 64 rows/columns per CTA (2 column-warps x 4 n-tiles).  4-stage cp.async ring, BK = 16.
+constexpr int SK_BN = 64, SK_STAGES = 4, SK_WM = 4, SK_WN = 2, SK_NT = 4;
+constexpr int SK_BLD_NN = SK_BN + 4;  // B stored [k][n]: 68 (mod 16 == 4)
 
-    for (int64_t kt = 0; kt < nk; ++kt) {
-        cp_async_wait<STAGES - 2>();
-        __syncthreads();  // also orders the Ds stores before the first fragment read
-        const int64_t nx = kt + STAGES - 1;
-        if (nx < nk) load_a((int)(nx % STAGES), nx * ADMM_BK);
-        cp_async_commit();
-        const double* as = As + (int)(kt % STAGES) * ASTAGE;
+__device__ __forceinline__ void sk_load_small(double* sm, const double* __restrict__ g, int64_t ld, int rows8, int64_t nrows,
+                                              int64_t k0, int64_t klen) {
+    for (int q = threadIdx.x; q < rows8 * (BK / 2); q += GEMM_THREADS) {
+        const int row = q >> 3, cc = (q & 7) * 2;
+        const int64_t gk = k0 + cc;
+        const bool ok = row < nrows && gk < klen;
+        cp_async16(sm + row * A_LD + cc, ok ? g + (int64_t)row * ld + gk : g, ok ? 16 : 0);
+    }
+}
+
+template <int MT, bool NT_LAYOUT>
+__device__ __forceinline__ void sk_mma_stage(const double* __restrict__ As, const double* __restrict__ Bs,
+                                             double (&acc)[MT][SK_NT][2], int mt0, int mtn, int wn, int lane) {
+    const int lr = lane >> 2, lc = lane & 3;
+    const double* as = As + (mt0 * 8 + lr) * A_LD + lc;
+    const double* bs = NT_LAYOUT ? Bs + (wn * SK_NT * 8 + lr) * BNT_LD + lc : Bs + lc * SK_BLD_NN + wn * SK_NT * 8 + lr;
 #pragma unroll
-        for (int kk = 0; kk < ADMM_BK / 4; ++kk) {
-            const int krow = (int)kt * ADMM_BK + kk * 4 + lc;
-            double b[3];
+    for (int kk = 0; kk < BK / 4; ++kk) {
+        double b[SK_NT];
 #pragma unroll
-            for (int d = 0; d < 3; ++d) b[d] = Ds[krow * ADMM_DLD + d * 8 + lr];
+        for (int j = 0; j < SK_NT; ++j) b[j] = NT_LAYOUT ? bs[j * 8 * BNT_LD + kk * 4] : bs[kk * 4 * SK_BLD_NN + j * 8];
 #pragma unroll
-            for (int i = 0; i < MTW; ++i) {
-                const double a = as[(warp * MTW * 8 + i * 8 + lr) * ADMM_ALD + kk * 4 + lc];
+        for (int i = 0; i < MT; ++i) {
+            if (i < mtn) {  // warp-uniform
+                const double a = as[i * 8 * A_LD + kk * 4];
 #pragma unroll
-                for (int d = 0; d < 3; ++d) dmma(acc[i][d][0], acc[i][d][1], a, b[d]);
+                for (int j = 0; j < SK_NT; ++j) dmma(acc[i][j][0], acc[i][j][1], a, b[j]);
             }
         }
     }
-    cp_async_wait<0>();
-    __syncthreads();  // every warp has finished reading Z/U through Ds before anyone overwrites them
+}
 
-    const int64_t n = n0 + 2 * lc;
+// D (r x M) = alpha * diag(row_scale) * A (r x q) * B (q x M),  r <= 8 * 4 * MT.  grid.x = column tile of 64.
+template <int MT>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_nn_skinny_kernel(const double* __restrict__ A, int64_t lda, int r, int64_t q, const double* __restrict__ B, int64_t ldb,
+                      int64_t M, double alpha, const double* __restrict__ row_scale, double* __restrict__ D, int64_t ldd) {
+    extern __shared__ __align__(16) double smem[];
+    const int rows8 = (r + 7) & ~7;
+    const int astage = rows8 * A_LD, bstage = BK * SK_BLD_NN;
+    double* As = smem;
+    double* Bs = smem + SK_STAGES * astage;
+    const int64_t col0 = (int64_t)blockIdx.x * SK_BN;
+    const int64_t nk = (q + BK - 1) / BK;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wm = warp / SK_WN, wn = warp % SK_WN;
+    int mt0, mtn;
+    mtile_range(rows8 >> 3, SK_WM, wm, mt0, mtn);
+    double acc[MT][SK_NT][2];
 #pragma unroll
-    for (int i = 0; i < MTW; ++i) {
-        const int64_t k = (int64_t)warp * MTW * 8 + i * 8 + lr;
-        if (k >= K || n >= ld) continue;
-        const int64_t base = k * C3 + n;
-        double2 v[3], un[3];
+    for (int i = 0; i < MT; ++i)
 #pragma unroll
-        for (int d = 0; d < 3; ++d) {
-            const double2 b0 = ld2(B0 + base + d * ld);
-            const double2 u = ld2(U + base + d * ld);
-            v[d].x = (b0.x + acc[i][d][0]) + u.x;  // V = C + U
-            v[d].y = (b0.y + acc[i][d][1]) + u.y;
-        }
-        const double2 lam = ld2(Lambda + k * ld + n);
-        double sh[2];
-        {
-            const double len = sqrt(__dadd_rn(__dadd_rn(__dmul_rn(v[0].x, v[0].x), __dmul_rn(v[1].x, v[1].x)), __dmul_rn(v[2].x, v[2].x)));
-            const double t = 1.0 - __ddiv_rn(__dmul_rn(inv_rho, lam.x), len);
-            sh[0] = (t != t) ? t : fmax(0.0, t);  // np.maximum propagates the 0/0 NaN (posComponents.py:253-256)
-        }
-        {
-            const double len = sqrt(__dadd_rn(__dadd_rn(__dmul_rn(v[0].y, v[0].y), __dmul_rn(v[1].y, v[1].y)), __dmul_rn(v[2].y, v[2].y)));
-            const double t = 1.0 - __ddiv_rn(__dmul_rn(inv_rho, lam.y), len);
-            sh[1] = (t != t) ? t : fmax(0.0, t);
-        }
-        const bool ok0 = n < N, ok1 = n + 1 < N;
+        for (int j = 0; j < SK_NT; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+    auto load_b = [&](double* sm, int64_t k0) {  // BK x 64 tile of B -> [k][SK_BLD_NN]
 #pragma unroll
-        for (int d = 0; d < 3; ++d) {
-            double2 z, u2;
-            z.x = ok0 ? v[d].x * sh[0] : 0.0;
-            z.y = ok1 ? v[d].y * sh[1] : 0.0;
-            u2.x = ok0 ? v[d].x - z.x : 0.0;
-            u2.y = ok1 ? v[d].y - z.y : 0.0;
-            un[d] = u2;
-            st2(Z + base + d * ld, z);
+        for (int t = 0; t < (BK * SK_BN / 2) / GEMM_THREADS; ++t) {
+            const int qq = threadIdx.x + t * GEMM_THREADS;
+            const int row = qq >> 5, cc = (qq & 31) * 2;
+            const int64_t gk = k0 + row, gc = col0 + cc;
+            const bool ok = gk < q && gc < M;
+            cp_async16(sm + row * SK_BLD_NN + cc, ok ? B + gk * ldb + gc : B, ok ? 16 : 0);
         }
+    };
 #pragma unroll
-        for (int d = 0; d < 3; ++d) st2(U + base + d * ld, un[d]);
+    for (int s = 0; s < SK_STAGES - 1; ++s) {
+        if (s < nk) {
+            sk_load_small(As + s * astage, A, lda, rows8, r, (int64_t)s * BK, q);
+            load_b(Bs + s * bstage, (int64_t)s * BK);
+        }
+        cp_async_commit();
+    }
+    for (int64_t kt = 0; kt < nk; ++kt) {
+        cp_async_wait<SK_STAGES - 2>();
+        __syncthreads();
+        const int64_t nx = kt + SK_STAGES - 1;
+        if (nx < nk) {
+            const int s = (int)(nx % SK_STAGES);
+            sk_load_small(As + s * astage, A, lda, rows8, r, nx * BK, q);
+            load_b(Bs + s * bstage, nx * BK);
+        }
+        cp_async_commit();
+        const int s = (int)(kt % SK_STAGES);
+        sk_mma_stage<MT, false>(As + s * astage, Bs + s * bstage, acc, mt0, mtn, wn, lane);
+    }
+    cp_async_wait<0>();
+    const int lr = lane >> 2, lc = lane & 3;
+#pragma unroll
+    for (int i = 0; i < MT; ++i) {
+        const int row = (mt0 + i) * 8 + lr;
+        if (i >= mtn || row >= r) continue;
+        const double sc = row_scale ? alpha * row_scale[row] : alpha;
+#pragma unroll
+        for (int j = 0; j < SK_NT; ++j) {
+            const int64_t c = col0 + wn * SK_NT * 8 + j * 8 + 2 * lc;
+            if (c < M) st2(D + (int64_t)row * ldd + c, make_double2(sc * acc[i][j][0], sc * acc[i][j][1]));
+        }
+    }
+}
+
+// part[slab][...] = S L^T over one slab of the long axis;  S: rs x M (rs <= 8 * 4 * MT, the m-side), L: rl x M, 64 rows of
+// L per CTA.  Output element (s, l) goes to part[l * ldo + s] (transpose_out) or part[s * ldo + l].
+// grid.x = L tile (fastest: CTAs sharing a slab of S run together -> S is read from HBM once), grid.y = slab.
+template <int MT>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_nt_skinny_kernel(const double* __restrict__ Sm, int64_t lds, int rs, const double* __restrict__ L, int64_t ldl,
+                      int64_t rl, int64_t M, int64_t slab_len, int transpose_out, double* __restrict__ out, int64_t ldo,
+                      int64_t slab_stride) {
+    extern __shared__ __align__(16) double smem[];
+    const int rows8 = (rs + 7) & ~7;
+    const int astage = rows8 * A_LD, bstage = SK_BN * BNT_LD;
+    double* As = smem;
+    double* Bs = smem + SK_STAGES * astage;
+    const int64_t l0 = (int64_t)blockIdx.x * SK_BN;
+    const int64_t m0 = (int64_t)blockIdx.y * slab_len;
+    const int64_t m1 = min(M, m0 + slab_len);
+    const int64_t nk = (m1 - m0 + BK - 1) / BK;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wm = warp / SK_WN, wn = warp % SK_WN;
+    int mt0, mtn;
+    mtile_range(rows8 >> 3, SK_WM, wm, mt0, mtn);
+    double acc[MT][SK_NT][2];
+#pragma unroll
+    for (int i = 0; i < MT; ++i)
+#pragma unroll
+        for (int j = 0; j < SK_NT; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+    auto load_l = [&](double* sm, int64_t k0) {  // 64 rows of L x BK -> [row][BNT_LD]
+#pragma unroll
+        for (int t = 0; t < (SK_BN * BK / 2) / GEMM_THREADS; ++t) {
+            const int qq = threadIdx.x + t * GEMM_THREADS;
+            const int row = qq >> 3, cc = (qq & 7) * 2;
+            const int64_t gr = l0 + row, gk = k0 + cc;
+            const bool ok = gr < rl && gk < m1;
+            cp_async16(sm + row * BNT_LD + cc, ok ? L + gr * ldl + gk : L, ok ? 16 : 0);
+        }
+    };
+#pragma unroll
+    for (int s = 0; s < SK_STAGES - 1; ++s) {
+        if (s < nk) {
+            sk_load_small(As + s * astage, Sm, lds, rows8, rs, m0 + (int64_t)s * BK, m1);
+            load_l(Bs + s * bstage, m0 + (int64_t)s * BK);
+        }
+        cp_async_commit();
+    }
+    for (int64_t kt = 0; kt < nk; ++kt) {
+        cp_async_wait<SK_STAGES - 2>();
+        __syncthreads();
+        const int64_t nx = kt + SK_STAGES - 1;
+        if (nx < nk) {
+            const int s = (int)(nx % SK_STAGES);
+            sk_load_small(As + s * astage, Sm, lds, rows8, rs, m0 + nx * BK, m1);
+            load_l(Bs + s * bstage, m0 + nx * BK);
+        }
+        cp_async_commit();
+        const int s = (int)(kt % SK_STAGES);
+        sk_mma_stage<MT, true>(As + s * astage, Bs + s * bstage, acc, mt0, mtn, wn, lane);
+    }
+    cp_async_wait<0>();
+    double* o = out + (int64_t)blockIdx.y * slab_stride;
+    const int lr = lane >> 2, lc = lane & 3;
+#pragma unroll
+    for (int i = 0; i < MT; ++i) {
+        const int srow = (mt0 + i) * 8 + lr;
+        if (i >= mtn || srow >= rs) continue;
+#pragma unroll
+        for (int j = 0; j < SK_NT; ++j) {
+            const int64_t l = l0 + wn * SK_NT * 8 + j * 8 + 2 * lc;
+            if (transpose_out) {
+                if (l < rl) o[l * ldo + srow] = acc[i][j][0];
+                if (l + 1 < rl) o[(l + 1) * ldo + srow] = acc[i][j][1];
+            } else {
+                if (l < rl) o[(int64_t)srow * ldo + l] = acc[i][j][0];
+                if (l + 1 < rl) o[(int64_t)srow * ldo + l + 1] = acc[i][j][1];
+            }
+        }
     }
 }
 
@@ -340,27 +390,70 @@ admm_iter_kernel(const double* __restrict__ Hr, int64_t ldh, const double* __res
 
 using namespace asb;
 
-static int nt_plan(int64_t ra, int64_t rb, int64_t M, int symmetric, int64_t* tiles, int64_t* slabs, int64_t* slab_len,
-                   int* tiles_j) {
-    const int64_t ti = cdiv(ra, BM), tj = cdiv(rb, BN);
-    *tiles_j = (int)tj;
-    *tiles = symmetric ? ti * (ti + 1) / 2 : ti * tj;
-    int64_t s = cdiv(2LL * sm_count(), *tiles);
-    const int64_t max_by_len = std::max<int64_t>(1, M / (8 * BK));  // at least 8 k-tiles per slab
-    s = std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(s, 64), max_by_len));
-    int64_t len = cdiv(cdiv(M, s), BK) * BK;
-    *slab_len = len;
-    *slabs = cdiv(M, len);
-    return 0;
+struct NtPlan {
+    bool skinny;       // one operand <= 256 rows: gemm_nt_skinny_kernel
+    bool swap;         // skinny: A is the small (m-side) operand -> output written untransposed
+    int64_t tiles, slabs, slab_len;
+    int tiles_j;
+};
+
+// Slab count: fill whole waves of the SM count (a 2.2-wave grid runs as long as a 3-wave one), prefer fewer slabs among
+// equally efficient choices, keep >= 8 k-tiles per slab and <= 64 partial outputs.
+static int64_t pick_slabs(int64_t tiles, int64_t M) {
+    const int64_t sms = sm_count();
+    const int64_t max_by_len = std::max<int64_t>(1, M / (8 * BK));
+    const int64_t smax = std::max<int64_t>(1, std::min<int64_t>(64, max_by_len));
+    int64_t best = 1;
+    double best_eff = -1.0;
+    for (int64_t s = 1; s <= smax; ++s) {
+        const int64_t ctas = tiles * s;
+        double eff = (double)ctas / (double)(cdiv(ctas, sms) * sms);
+        if (ctas >= 2 * sms) eff += 0.004;  // >= 2 waves: the tail of uneven CTAs is amortised
+        if (eff > best_eff + 0.005) { best_eff = eff; best = s; }
+    }
+    return best;
 }
 
-template <int MTW>
-static int launch_admm(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda,
-                       int64_t K, int64_t N, int64_t ld, double inv_rho, cudaStream_t st) {
-    constexpr int KP = 4 * MTW * 8;
-    const size_t smem = (size_t)(KP * ADMM_DLD + STAGES * KP * ADMM_ALD) * sizeof(double);
-    ASB_CUDA(cudaFuncSetAttribute(admm_iter_kernel<MTW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    admm_iter_kernel<MTW><<<(unsigned)(ld / 8), 128, smem, st>>>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho);
+static NtPlan nt_plan(int64_t ra, int64_t rb, int64_t M, int symmetric) {
+    NtPlan p{};
+    const int64_t small = std::min(ra, rb);
+    p.skinny = small <= 256;
+    if (p.skinny) {
+        p.swap = ra <= rb;  // A small: m-side = A, n-side = B
+        p.tiles = cdiv(p.swap ? rb : ra, SK_BN);
+        p.tiles_j = 1;
+    } else {
+        const int64_t ti = cdiv(ra, BM), tj = cdiv(rb, BN);
+        p.tiles_j = (int)tj;
+        p.tiles = symmetric ? ti * (ti + 1) / 2 : ti * tj;
+    }
+    const int64_t s = pick_slabs(p.tiles, M);
+    p.slab_len = cdiv(cdiv(M, s), BK) * BK;
+    p.slabs = cdiv(M, p.slab_len);
+    return p;
+}
+
+template <int MT>
+static int launch_nt_skinny(const double* Sm, int64_t lds, int64_t rs, const double* L, int64_t ldl, int64_t rl, int64_t M,
+                            const NtPlan& p, int transpose_out, double* part, int64_t ldo, int64_t slab_stride,
+                            cudaStream_t st) {
+    const int rows8 = (int)((rs + 7) & ~7LL);
+    const size_t smem = (size_t)SK_STAGES * (rows8 * A_LD + SK_BN * BNT_LD) * sizeof(double);
+    ASB_CUDA(cudaFuncSetAttribute(gemm_nt_skinny_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gemm_nt_skinny_kernel<MT><<<dim3((unsigned)p.tiles, (unsigned)p.slabs), GEMM_THREADS, smem, st>>>(
+        Sm, lds, (int)rs, L, ldl, rl, M, p.slab_len, transpose_out, part, ldo, slab_stride);
+    ASB_LAUNCH_CHECK();
+    return ASB_OK;
+}
+
+template <int MT>
+static int launch_nn_skinny(const double* A, int64_t lda, int64_t r, int64_t q, const double* B, int64_t ldb, int64_t M,
+                            double alpha, const double* row_scale, double* D, int64_t ldd, cudaStream_t st) {
+    const int rows8 = (int)((r + 7) & ~7LL);
+    const size_t smem = (size_t)SK_STAGES * (rows8 * A_LD + BK * SK_BLD_NN) * sizeof(double);
+    ASB_CUDA(cudaFuncSetAttribute(gemm_nn_skinny_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gemm_nn_skinny_kernel<MT><<<(unsigned)cdiv(M, SK_BN), GEMM_THREADS, smem, st>>>(A, lda, (int)r, q, B, ldb, M, alpha,
+                                                                                  row_scale, D, ldd);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
 }
@@ -368,10 +461,8 @@ static int launch_admm(const double* Hr, int64_t ldh, const double* B0, double* 
 extern "C" {
 
 int64_t asb_gemm_nt_workspace_bytes(int64_t ra, int64_t rb, int64_t M, int symmetric) {
-    int64_t tiles, slabs, len;
-    int tj;
-    nt_plan(ra, rb, M, symmetric, &tiles, &slabs, &len, &tj);
-    return slabs * ra * rb * (int64_t)sizeof(double);
+    const NtPlan p = nt_plan(ra, rb, M, symmetric);
+    return p.slabs * ra * rb * (int64_t)sizeof(double);
 }
 
 int asb_gemm_nt(const double* A, int64_t lda, int64_t ra, const double* B, int64_t ldb, int64_t rb, int64_t M, double* D,
@@ -380,21 +471,34 @@ int asb_gemm_nt(const double* A, int64_t lda, int64_t ra, const double* B, int64
     ASB_REQUIRE(lda % 2 == 0 && ldb % 2 == 0 && M % 2 == 0, "gemm_nt: leading dimensions and M must be even");
     ASB_REQUIRE(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0), "gemm_nt: operands must be 16-byte aligned");
     ASB_REQUIRE(!symmetric || (A == B && ra == rb), "gemm_nt: symmetric needs A == B");
-    int64_t tiles, slabs, slab_len;
-    int tiles_j;
-    nt_plan(ra, rb, M, symmetric, &tiles, &slabs, &slab_len, &tiles_j);
-    const size_t smem = (size_t)STAGES * (A_STAGE + BNT_STAGE) * sizeof(double);
-    static bool attr = false;
-    if (!attr) {
-        ASB_CUDA(cudaFuncSetAttribute(gemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr = true;
-    }
+    const NtPlan p = nt_plan(ra, rb, M, symmetric);
     double* part = reinterpret_cast<double*>(ws);
     const int64_t slab_stride = ra * rb;
-    gemm_nt_kernel<<<dim3((unsigned)tiles, (unsigned)slabs), GEMM_THREADS, smem, S(stream)>>>(
-        A, lda, ra, B, ldb, rb, M, slab_len, symmetric, tiles_j, part, rb, slab_stride);
-    ASB_LAUNCH_CHECK();
-    gemm_nt_reduce_kernel<<<(unsigned)cdiv(ra * rb, 256), 256, 0, S(stream)>>>(part, slabs, slab_stride, ra, rb, rb,
+    if (p.skinny) {
+        // part[slab][i][j], i over A rows, j over B rows.  m-side = the small operand.
+        const double* Sm = p.swap ? A : B;
+        const double* L = p.swap ? B : A;
+        const int64_t lds = p.swap ? lda : ldb, ldl = p.swap ? ldb : lda, rs = p.swap ? ra : rb, rl = p.swap ? rb : ra;
+        const int tr = p.swap ? 0 : 1;  // element (s, l): swap -> part[s][l], else part[l][s]
+        int rc;
+        if (rs <= 64) rc = launch_nt_skinny<2>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream));
+        else if (rs <= 128) rc = launch_nt_skinny<4>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream));
+        else if (rs <= 224) rc = launch_nt_skinny<7>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream));
+        else rc = launch_nt_skinny<8>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream));
+        if (rc != ASB_OK) return rc;
+        symmetric = 0;  // the skinny kernel computes every tile
+    } else {
+        const size_t smem = (size_t)STAGES * (A_STAGE + BNT_STAGE) * sizeof(double);
+        static bool attr = false;
+        if (!attr) {
+            ASB_CUDA(cudaFuncSetAttribute(gemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr = true;
+        }
+        gemm_nt_kernel<<<dim3((unsigned)p.tiles, (unsigned)p.slabs), GEMM_THREADS, smem, S(stream)>>>(
+            A, lda, ra, B, ldb, rb, M, p.slab_len, symmetric, p.tiles_j, part, rb, slab_stride);
+        ASB_LAUNCH_CHECK();
+    }
+    gemm_nt_reduce_kernel<<<(unsigned)cdiv(ra * rb, 256), 256, 0, S(stream)>>>(part, p.slabs, slab_stride, ra, rb, rb,
                                                                              symmetric, D, ldd);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
@@ -407,6 +511,12 @@ int asb_gemm_nn(const double* A, int64_t lda, int64_t r, int64_t q, const double
                 "gemm_nn: leading dimensions and M must be even (A zero-padded to an even row length)");
     ASB_REQUIRE(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && ((uintptr_t)D % 16 == 0),
                 "gemm_nn: operands must be 16-byte aligned");
+    if (r <= 256) {
+        if (r <= 64) return launch_nn_skinny<2>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
+        if (r <= 128) return launch_nn_skinny<4>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
+        if (r <= 224) return launch_nn_skinny<7>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
+        return launch_nn_skinny<8>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
+    }
     ASB_REQUIRE(cdiv(M, BN) < 65536, "gemm_nn: M too large for one launch");
     const size_t smem = (size_t)STAGES * (A_STAGE + BNN_STAGE) * sizeof(double);
     static bool attr = false;
@@ -418,17 +528,6 @@ int asb_gemm_nn(const double* A, int64_t lda, int64_t r, int64_t q, const double
         A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
-}
-
-int asb_admm_iter(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda, int64_t K,
-                  int64_t N, int64_t ld, double inv_rho, asb_stream_t stream) {
-    ASB_REQUIRE(Hr && B0 && Z && U && Lambda && K > 0 && K <= 256 && N > 0 && ld >= N && ld % 32 == 0,
-                "admm_iter: bad arguments (K <= 256)");
-    ASB_REQUIRE(ldh % 2 == 0 && ((uintptr_t)Hr % 16 == 0), "admm_iter: Hr must be 16-byte aligned with even ldh");
-    if (K <= 64) return launch_admm<2>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, S(stream));
-    if (K <= 128) return launch_admm<4>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, S(stream));
-    if (K <= 224) return launch_admm<7>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, S(stream));
-    return launch_admm<8>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, S(stream));
 }
 
 }  // extern "C"

@@ -230,8 +230,7 @@ def splocs(ops, comm, X, shard, C, W, K, geodesic, num_iters, num_admm, lam, rho
         ops.small_gemm(0, 1, K, F, K, 1.0, Hinv, W, Aw)                 # Aw = H^-1 W^T   (K x F)
         ops.gemm_nn(Aw, K, F, Xm, M, 1.0, B0.view(K, M))                # B0 = H^-1 (W^T X)
         ops.axpby(Hr.view(1, -1), rho, Hinv.view(1, -1), None, 0.0, None, K * Kp)
-        for _ in range(num_admm):
-            ops.admm_iter(Hr, B0, C, U, Lambda, K, N, 1.0 / rho)
+        ops.admm_solve(Hr, B0, C, U, Lambda, K, N, 1.0 / rho, num_admm)
         P, Q = grams()
         centres(True)
         # energy = |X - W C|^2 + sum Lambda |c|  via  |X|^2 - 2 <W, P> + <W Q, W>

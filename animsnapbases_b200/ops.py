@@ -213,6 +213,12 @@ class CudaOps:
         self._call("asb_admm_iter", self._p(Hr), Hr.stride(0), self._p(B0), self._p(Z), self._p(U), self._p(Lambda), K, N, ld,
                    float(inv_rho))
 
+    def admm_solve(self, Hr, B0, Z, U, Lambda, K, N, inv_rho, iters):
+        """`iters` fused ADMM iterations in one launch (Z, U in place)."""
+        ld = Z.shape[2]
+        self._call("asb_admm_solve", self._p(Hr), Hr.stride(0), self._p(B0), self._p(Z), self._p(U), self._p(Lambda), K, N, ld,
+                   float(inv_rho), int(iters))
+
     # ------------------------------------------------------------------ small dense
     def gram_small(self, W, F, K, diag_add, G):
         self._call("asb_gram_small", self._p(W), W.stride(0), F, K, float(diag_add), self._p(G), G.stride(0))

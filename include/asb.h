@@ -122,10 +122,15 @@ int asb_gemm_nt(const double* A, int64_t lda, int64_t ra, const double* B, int64
  * c = W^T X (posComponents.py:171), back-projection U^T = S^-1 V^T X (constraintsComponents.py:313). */
 int asb_gemm_nn(const double* A, int64_t lda, int64_t r, int64_t q, const double* B, int64_t ldb, int64_t M,
                 double alpha, const double* row_scale, double* D, int64_t ldd, asb_stream_t stream);
-/* One ADMM iteration, fused (posComponents.py:175-178, :252-256), in place on Z and U:
+/* The ADMM inner loop of one SPLOCS outer step (posComponents.py:175-178, :252-256), `iters` iterations fused in ONE
+ * launch, in place on Z and U:
  *   C = B0 + Hr (Z - U)          Hr = rho * (W^T W + rho I)^-1  (K x K, ldh)
  *   V = C + U;  Z' = V * max(0, 1 - inv_rho * Lambda[k][n] / |V[k][:, n]|);  U' = V - Z'
- * B0, Z, U: K x 3*ld planar; Lambda: K x ld.  K <= 256. */
+ * The iteration only couples the K entries of one vertex, so each CTA keeps its vertex tile (Z - U, U) in shared
+ * memory for all iterations: Z and U cross HBM once per call.  B0, Z, U: K x 3*ld planar; Lambda: K x ld.  K <= 256. */
+int asb_admm_solve(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda,
+                   int64_t K, int64_t N, int64_t ld, double inv_rho, int64_t iters, asb_stream_t stream);
+/* One iteration of the above (asb_admm_solve with iters = 1). */
 int asb_admm_iter(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda,
                   int64_t K, int64_t N, int64_t ld, double inv_rho, asb_stream_t stream);
 

@@ -184,6 +184,10 @@ class NumpyOps:
         z[:] = Zn
         u[:] = Un
 
+    def admm_solve(self, Hr, B0, Z, U, Lambda, K, N, inv_rho, iters):
+        for _ in range(int(iters)):
+            self.admm_iter(Hr, B0, Z, U, Lambda, K, N, inv_rho)
+
     # small dense ----------------------------------------------------------------------------------
     def gram_small(self, W, F, K, diag_add, G):
         w = W.numpy()[:F, :K]

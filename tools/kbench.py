@@ -118,6 +118,8 @@ def main():
         Hr[:, :K] = torch.eye(K, dtype=torch.float64, device=ops.device) * 0.5
         rec("asb_admm_iter", timed(lambda: ops.admm_iter(Hr, B0, C, U, Lam, K, N, 0.1)), flops=2.0 * K * K * M,
             nbytes=8.0 * K * M * 5 + 8.0 * K * ld)
+        rec("asb_admm_solve_x10", timed(lambda: ops.admm_solve(Hr, B0, C, U, Lam, K, N, 0.1, 10), reps=2), flops=20.0 * K * K * M,
+            nbytes=8.0 * K * M * 5 + 8.0 * K * ld)
     json.dump(out, open(os.path.join("gpurun_out", "kbench_%dx%d.json" % (N, F)), "w"), indent=1)
 
 
