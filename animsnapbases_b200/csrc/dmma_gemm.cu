@@ -8,6 +8,7 @@
 // Operand tiles are staged global -> shared with a 3-stage cp.async (LDGSTS) pipeline; shared tiles use padded
 // strides (stride mod 16 doubles == 4 or 12) so that every 8x4 / 4x8 fragment read is bank-conflict free.
 #include "dmma.cuh"
+#include "dmma_skinny.cuh"
 
 namespace asb {
 
@@ -143,7 +144,8 @@ __global__ void gemm_nt_reduce_kernel(const double* __restrict__ part, int64_t s
     if (t >= ra * rb) return;
     const int64_t i = t / rb, j = t % rb;
     int64_t si = i, sj = j;
-    if (symmetric && ((j / BN) < (i / BM))) { si = j; sj = i; }  // tile (ti > tj) was not computed
+    if (symmetric == 1 && ((j / BN) < (i / BM))) { si = j; sj = i; }  // tile (ti > tj) was not computed
+    if (symmetric == 2 && j < i) { si = j; sj = i; }                   // every tile computed: mirror element-wise
     double s = 0.0;
     for (int64_t k = 0; k < slabs; ++k) s += part[k * slab_stride + si * ldp + sj];
     D[i * ldd + j] = s;
@@ -203,189 +205,6 @@ gemm_nn_kernel(const double* __restrict__ A, int64_t lda, int64_t r, int64_t q, 
 }
 
 
-// ------------------------------------------------------------------------------------------ skinny variants
-// One operand has at most 256 rows (the K components / the K x F weight operator): it becomes the DMMA m-side and is
-// covered COMPLETELY by one CTA (no 128-row tile quantisation: K = 200 costs 25 m-tiles, not 32), dealt to WM = 4
-// row-warps at run time (7,6,6,6 -> sub-partition loads 13,13,12,12 with warp id = wm * 2 + wn).  The long operand is the
-// n-side, 64 rows/columns per CTA (2 column-warps x 4 n-tiles).  4-stage cp.async ring, BK = 16.
-constexpr int SK_BN = 64, SK_STAGES = 4, SK_WM = 4, SK_WN = 2, SK_NT = 4;
-constexpr int SK_BLD_NN = SK_BN + 4;  // B stored [k][n]: 68 (mod 16 == 4)
-
-__device__ __forceinline__ void sk_load_small(double* sm, const double* __restrict__ g, int64_t ld, int rows8, int64_t nrows,
-                                              int64_t k0, int64_t klen) {
-    for (int q = threadIdx.x; q < rows8 * (BK / 2); q += GEMM_THREADS) {
-        const int row = q >> 3, cc = (q & 7) * 2;
-        const int64_t gk = k0 + cc;
-        const bool ok = row < nrows && gk < klen;
-        cp_async16(sm + row * A_LD + cc, ok ? g + (int64_t)row * ld + gk : g, ok ? 16 : 0);
-    }
-}
-
-template <int MT, bool NT_LAYOUT>
-__device__ __forceinline__ void sk_mma_stage(const double* __restrict__ As, const double* __restrict__ Bs,
-                                             double (&acc)[MT][SK_NT][2], int mt0, int mtn, int wn, int lane) {
-    const int lr = lane >> 2, lc = lane & 3;
-    const double* as = As + (mt0 * 8 + lr) * A_LD + lc;
-    const double* bs = NT_LAYOUT ? Bs + (wn * SK_NT * 8 + lr) * BNT_LD + lc : Bs + lc * SK_BLD_NN + wn * SK_NT * 8 + lr;
-#pragma unroll
-    for (int kk = 0; kk < BK / 4; ++kk) {
-        double b[SK_NT];
-#pragma unroll
-        for (int j = 0; j < SK_NT; ++j) b[j] = NT_LAYOUT ? bs[j * 8 * BNT_LD + kk * 4] : bs[kk * 4 * SK_BLD_NN + j * 8];
-#pragma unroll
-        for (int i = 0; i < MT; ++i) {
-            if (i < mtn) {  // warp-uniform
-                const double a = as[i * 8 * A_LD + kk * 4];
-#pragma unroll
-                for (int j = 0; j < SK_NT; ++j) dmma(acc[i][j][0], acc[i][j][1], a, b[j]);
-            }
-        }
-    }
-}
-
-// D (r x M) = alpha * diag(row_scale) * A (r x q) * B (q x M),  r <= 8 * 4 * MT.  grid.x = column tile of 64.
-template <int MT>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_nn_skinny_kernel(const double* __restrict__ A, int64_t lda, int r, int64_t q, const double* __restrict__ B, int64_t ldb,
-                      int64_t M, double alpha, const double* __restrict__ row_scale, double* __restrict__ D, int64_t ldd) {
-    extern __shared__ __align__(16) double smem[];
-    const int rows8 = (r + 7) & ~7;
-    const int astage = rows8 * A_LD, bstage = BK * SK_BLD_NN;
-    double* As = smem;
-    double* Bs = smem + SK_STAGES * astage;
-    const int64_t col0 = (int64_t)blockIdx.x * SK_BN;
-    const int64_t nk = (q + BK - 1) / BK;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wm = warp / SK_WN, wn = warp % SK_WN;
-    int mt0, mtn;
-    mtile_range(rows8 >> 3, SK_WM, wm, mt0, mtn);
-    double acc[MT][SK_NT][2];
-#pragma unroll
-    for (int i = 0; i < MT; ++i)
-#pragma unroll
-        for (int j = 0; j < SK_NT; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
-    auto load_b = [&](double* sm, int64_t k0) {  // BK x 64 tile of B -> [k][SK_BLD_NN]
-#pragma unroll
-        for (int t = 0; t < (BK * SK_BN / 2) / GEMM_THREADS; ++t) {
-            const int qq = threadIdx.x + t * GEMM_THREADS;
-            const int row = qq >> 5, cc = (qq & 31) * 2;
-            const int64_t gk = k0 + row, gc = col0 + cc;
-            const bool ok = gk < q && gc < M;
-            cp_async16(sm + row * SK_BLD_NN + cc, ok ? B + gk * ldb + gc : B, ok ? 16 : 0);
-        }
-    };
-#pragma unroll
-    for (int s = 0; s < SK_STAGES - 1; ++s) {
-        if (s < nk) {
-            sk_load_small(As + s * astage, A, lda, rows8, r, (int64_t)s * BK, q);
-            load_b(Bs + s * bstage, (int64_t)s * BK);
-        }
-        cp_async_commit();
-    }
-    for (int64_t kt = 0; kt < nk; ++kt) {
-        cp_async_wait<SK_STAGES - 2>();
-        __syncthreads();
-        const int64_t nx = kt + SK_STAGES - 1;
-        if (nx < nk) {
-            const int s = (int)(nx % SK_STAGES);
-            sk_load_small(As + s * astage, A, lda, rows8, r, nx * BK, q);
-            load_b(Bs + s * bstage, nx * BK);
-        }
-        cp_async_commit();
-        const int s = (int)(kt % SK_STAGES);
-        sk_mma_stage<MT, false>(As + s * astage, Bs + s * bstage, acc, mt0, mtn, wn, lane);
-    }
-    cp_async_wait<0>();
-    const int lr = lane >> 2, lc = lane & 3;
-#pragma unroll
-    for (int i = 0; i < MT; ++i) {
-        const int row = (mt0 + i) * 8 + lr;
-        if (i >= mtn || row >= r) continue;
-        const double sc = row_scale ? alpha * row_scale[row] : alpha;
-#pragma unroll
-        for (int j = 0; j < SK_NT; ++j) {
-            const int64_t c = col0 + wn * SK_NT * 8 + j * 8 + 2 * lc;
-            if (c < M) st2(D + (int64_t)row * ldd + c, make_double2(sc * acc[i][j][0], sc * acc[i][j][1]));
-        }
-    }
-}
-
-// part[slab][...] = S L^T over one slab of the long axis;  S: rs x M (rs <= 8 * 4 * MT, the m-side), L: rl x M, 64 rows of
-// L per CTA.  Output element (s, l) goes to part[l * ldo + s] (transpose_out) or part[s * ldo + l].
-// grid.x = L tile (fastest: CTAs sharing a slab of S run together -> S is read from HBM once), grid.y = slab.
-template <int MT>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_nt_skinny_kernel(const double* __restrict__ Sm, int64_t lds, int rs, const double* __restrict__ L, int64_t ldl,
-                      int64_t rl, int64_t M, int64_t slab_len, int transpose_out, double* __restrict__ out, int64_t ldo,
-                      int64_t slab_stride) {
-    extern __shared__ __align__(16) double smem[];
-    const int rows8 = (rs + 7) & ~7;
-    const int astage = rows8 * A_LD, bstage = SK_BN * BNT_LD;
-    double* As = smem;
-    double* Bs = smem + SK_STAGES * astage;
-    const int64_t l0 = (int64_t)blockIdx.x * SK_BN;
-    const int64_t m0 = (int64_t)blockIdx.y * slab_len;
-    const int64_t m1 = min(M, m0 + slab_len);
-    const int64_t nk = (m1 - m0 + BK - 1) / BK;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wm = warp / SK_WN, wn = warp % SK_WN;
-    int mt0, mtn;
-    mtile_range(rows8 >> 3, SK_WM, wm, mt0, mtn);
-    double acc[MT][SK_NT][2];
-#pragma unroll
-    for (int i = 0; i < MT; ++i)
-#pragma unroll
-        for (int j = 0; j < SK_NT; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
-    auto load_l = [&](double* sm, int64_t k0) {  // 64 rows of L x BK -> [row][BNT_LD]
-#pragma unroll
-        for (int t = 0; t < (SK_BN * BK / 2) / GEMM_THREADS; ++t) {
-            const int qq = threadIdx.x + t * GEMM_THREADS;
-            const int row = qq >> 3, cc = (qq & 7) * 2;
-            const int64_t gr = l0 + row, gk = k0 + cc;
-            const bool ok = gr < rl && gk < m1;
-            cp_async16(sm + row * BNT_LD + cc, ok ? L + gr * ldl + gk : L, ok ? 16 : 0);
-        }
-    };
-#pragma unroll
-    for (int s = 0; s < SK_STAGES - 1; ++s) {
-        if (s < nk) {
-            sk_load_small(As + s * astage, Sm, lds, rows8, rs, m0 + (int64_t)s * BK, m1);
-            load_l(Bs + s * bstage, m0 + (int64_t)s * BK);
-        }
-        cp_async_commit();
-    }
-    for (int64_t kt = 0; kt < nk; ++kt) {
-        cp_async_wait<SK_STAGES - 2>();
-        __syncthreads();
-        const int64_t nx = kt + SK_STAGES - 1;
-        if (nx < nk) {
-            const int s = (int)(nx % SK_STAGES);
-            sk_load_small(As + s * astage, Sm, lds, rows8, rs, m0 + nx * BK, m1);
-            load_l(Bs + s * bstage, m0 + nx * BK);
-        }
-        cp_async_commit();
-        const int s = (int)(kt % SK_STAGES);
-        sk_mma_stage<MT, true>(As + s * astage, Bs + s * bstage, acc, mt0, mtn, wn, lane);
-    }
-    cp_async_wait<0>();
-    double* o = out + (int64_t)blockIdx.y * slab_stride;
-    const int lr = lane >> 2, lc = lane & 3;
-#pragma unroll
-    for (int i = 0; i < MT; ++i) {
-        const int srow = (mt0 + i) * 8 + lr;
-        if (i >= mtn || srow >= rs) continue;
-#pragma unroll
-        for (int j = 0; j < SK_NT; ++j) {
-            const int64_t l = l0 + wn * SK_NT * 8 + j * 8 + 2 * lc;
-            if (transpose_out) {
-                if (l < rl) o[l * ldo + srow] = acc[i][j][0];
-                if (l + 1 < rl) o[(l + 1) * ldo + srow] = acc[i][j][1];
-            } else {
-                if (l < rl) o[(int64_t)srow * ldo + l] = acc[i][j][0];
-                if (l + 1 < rl) o[(int64_t)srow * ldo + l + 1] = acc[i][j][1];
-            }
-        }
-    }
-}
-
 }  // namespace asb
 
 using namespace asb;
@@ -438,9 +257,9 @@ static int launch_nt_skinny(const double* Sm, int64_t lds, int64_t rs, const dou
                             const NtPlan& p, int transpose_out, double* part, int64_t ldo, int64_t slab_stride,
                             cudaStream_t st) {
     const int rows8 = (int)((rs + 7) & ~7LL);
-    const size_t smem = (size_t)SK_STAGES * (rows8 * A_LD + SK_BN * BNT_LD) * sizeof(double);
+    const size_t smem = (size_t)SK_STAGES * (rows8 * SK_ALD + SK_BN * SK_ALD) * sizeof(double);
     ASB_CUDA(cudaFuncSetAttribute(gemm_nt_skinny_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gemm_nt_skinny_kernel<MT><<<dim3((unsigned)p.tiles, (unsigned)p.slabs), GEMM_THREADS, smem, st>>>(
+    gemm_nt_skinny_kernel<MT><<<dim3((unsigned)p.tiles, (unsigned)p.slabs), SK_THREADS, smem, st>>>(
         Sm, lds, (int)rs, L, ldl, rl, M, p.slab_len, transpose_out, part, ldo, slab_stride);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
@@ -450,7 +269,7 @@ template <int MT>
 static int launch_nn_skinny(const double* A, int64_t lda, int64_t r, int64_t q, const double* B, int64_t ldb, int64_t M,
                             double alpha, const double* row_scale, double* D, int64_t ldd, cudaStream_t st) {
     const int rows8 = (int)((r + 7) & ~7LL);
-    const size_t smem = (size_t)SK_STAGES * (rows8 * A_LD + BK * SK_BLD_NN) * sizeof(double);
+    const size_t smem = (size_t)SK_STAGES * (rows8 * SK_ALD + SK_BK * SK_BLD_NN) * sizeof(double);
     ASB_CUDA(cudaFuncSetAttribute(gemm_nn_skinny_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     gemm_nn_skinny_kernel<MT><<<(unsigned)cdiv(M, SK_BN), GEMM_THREADS, smem, st>>>(A, lda, (int)r, q, B, ldb, M, alpha,
                                                                                   row_scale, D, ldd);
@@ -481,12 +300,14 @@ int asb_gemm_nt(const double* A, int64_t lda, int64_t ra, const double* B, int64
         const int64_t lds = p.swap ? lda : ldb, ldl = p.swap ? ldb : lda, rs = p.swap ? ra : rb, rl = p.swap ? rb : ra;
         const int tr = p.swap ? 0 : 1;  // element (s, l): swap -> part[s][l], else part[l][s]
         int rc;
-        if (rs <= 64) rc = launch_nt_skinny<2>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream));
-        else if (rs <= 128) rc = launch_nt_skinny<4>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream));
-        else if (rs <= 224) rc = launch_nt_skinny<7>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream));
-        else rc = launch_nt_skinny<8>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream));
+        switch ((int)cdiv(cdiv(rs, 8), SK_WM)) {  // m-tiles per row-warp
+#define ASB_NT_CASE(MT) case MT: rc = launch_nt_skinny<MT>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream)); break;
+            ASB_NT_CASE(1) ASB_NT_CASE(2) ASB_NT_CASE(3) ASB_NT_CASE(4) ASB_NT_CASE(5) ASB_NT_CASE(6) ASB_NT_CASE(7)
+            default: rc = launch_nt_skinny<8>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream));
+#undef ASB_NT_CASE
+        }
         if (rc != ASB_OK) return rc;
-        symmetric = 0;  // the skinny kernel computes every tile
+        symmetric = symmetric ? 2 : 0;  // the skinny kernel computes every tile; the Gram is mirrored element-wise
     } else {
         const size_t smem = (size_t)STAGES * (A_STAGE + BNT_STAGE) * sizeof(double);
         static bool attr = false;
@@ -512,10 +333,12 @@ int asb_gemm_nn(const double* A, int64_t lda, int64_t r, int64_t q, const double
     ASB_REQUIRE(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && ((uintptr_t)D % 16 == 0),
                 "gemm_nn: operands must be 16-byte aligned");
     if (r <= 256) {
-        if (r <= 64) return launch_nn_skinny<2>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
-        if (r <= 128) return launch_nn_skinny<4>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
-        if (r <= 224) return launch_nn_skinny<7>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
-        return launch_nn_skinny<8>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
+        switch ((int)cdiv(cdiv(r, 8), SK_WM)) {
+#define ASB_NN_CASE(MT) case MT: return launch_nn_skinny<MT>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
+            ASB_NN_CASE(1) ASB_NN_CASE(2) ASB_NN_CASE(3) ASB_NN_CASE(4) ASB_NN_CASE(5) ASB_NN_CASE(6) ASB_NN_CASE(7)
+            default: return launch_nn_skinny<8>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
+#undef ASB_NN_CASE
+        }
     }
     ASB_REQUIRE(cdiv(M, BN) < 65536, "gemm_nn: M too large for one launch");
     const size_t smem = (size_t)STAGES * (A_STAGE + BNN_STAGE) * sizeof(double);

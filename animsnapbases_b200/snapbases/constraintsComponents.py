@@ -1,0 +1,238 @@
+"""constraintsComponents -- B200 mirror of snapbases/constraintsComponents.py:26-860 (reference), hot-path part.
+
+Same protocol as main.py:106-142 drives:  `.nonlinearSnapshots.config()`, `.config(...)`,
+`.nonlinearSnapshots.snapshots_prepare()`, `.compute_components_store_singvalues()`, `.post_process_components()`,
+`.deim()`, `.store_components_n_interpol_points()` / `.store_components_gradually_to_files(...)`.
+Device work goes through animsnapbases_b200.engine -> libasb.so:
+
+  pod_vectorized  (:298-320)  Gram X X^T on the DMMA pipe -> F x F eigensolve -> back-projection GEMM      engine.pod
+  post-process    (:415-446)  unscale + mean, per-dimension economic QR (CGS2), M^-1/2 row scaling         engine.orthogonalize_rows
+  deim            (:797-860)  greedy point selection, one index set for x/y/z, bit-exact first-max argmax   engine.deim
+
+Basis types 'pca_blocks' / 'pca_blocks_with_St' / 'pod' and the block / geometric DEIM variants are SURVEY 8(a) rows a10,
+a11, a14 (after the pod_vectorized + deim path); they raise NotImplementedError here rather than fall back to the CPU.
+The plotting / polyscope methods of the reference (:865-1156) are out of scope (graphics: unavailable on this box).
+"""
+from __future__ import annotations
+
+import csv
+import os
+
+import numpy as np
+
+from .. import engine, hostio, runtime
+from ..hostio import log_time
+from .nonlinear_snapshots import nonlinearSnapshots
+
+
+class constraintsComponents:  # Components == bases
+    def __init__(self, param):
+        self.basesType = ""
+        self.numComp = 0
+        self.support = ""
+        self.storeSingVal = False
+        self.nonlinearSnapshots = nonlinearSnapshots(param)
+        self.param = param
+        self.weigs = None
+        self.ortho_comps = None
+        self.largeDeforPoints = None
+        self.largeDeforBlocks = None
+        self.measures_at_largeDeforVerts = None
+        self.fileNameBases = ""
+        self.fileName_geom_points = ""
+        self.file_name_sing = ""
+        self.geom_interpol_verts = []
+        self.geom_alpha = None
+        self.geom_alpha_ranges = None
+        self.geom_Pt = None
+        self.geom_ep_idxs = None
+        self.St = None
+        self.singular_values = None
+        self._C = None               # device (K, 3, ld) planar components of this rank's row shard
+        self._host = {}
+
+    # ------------------------------------------------------------------ host view (reference attribute name)
+    @property
+    def comps(self):
+        if self._C is None:
+            return None
+        if "comps" not in self._host:
+            ops, _ = runtime.get()
+            self._host["comps"] = ops.export_aos(self._C, None, self.nonlinearSnapshots.shard.n).cpu().numpy()
+        return self._host["comps"]
+
+    def config(self, fileNameBases="p_nl_", fileName_geom_points="p_nl_interpol_points_",
+               file_name_sing="_constrprojBases_pcaExtraction_singValues"):
+        p = self.param
+        self.basesType = p.constProj_bases_interpolation_type
+        self.support = p.constProj_support
+        self.storeSingVal = p.constProj_store_sing_val
+        self.fileNameBases = fileNameBases
+        self.fileName_geom_points = fileName_geom_points
+        self.file_name_sing = file_name_sing
+        # the differential operator St is only used by the geometric / St variants (a11, a14): load it when present
+        st_file = getattr(p, "constProj_weightedSt", None)
+        if st_file and os.path.exists(st_file):
+            data = np.load(st_file, allow_pickle=True)
+            St = data[getattr(p, "costProj_St_key", data.files[0])]
+            if isinstance(St, np.ndarray) and St.dtype == object:
+                St = St.item()
+            self.St = St
+
+    @staticmethod
+    def project_weight(x):
+        x = np.maximum(0., x)
+        m = x.max()
+        return x if m == 0 else x / m
+
+    # ------------------------------------------------------------------ basis build
+    @log_time("")
+    def compute_components_store_singvalues(self):
+        p = self.param
+        kind = p.constProj_basis_type
+        if kind in ("pca_blocks", "pca_blocks_with_St"):
+            headerSing = ['component', 'idx', 'residual_matrix_norm'] + \
+                         ['singVal' + str(i) for i in range(self.nonlinearSnapshots.constraintsSize)]
+        else:
+            headerSing = ['component', 'singVal']
+        if kind not in ("pod", "pod_vectorized", "pca_blocks", "pca_blocks_with_St"):
+            raise ValueError("Uknown basis type: ", kind)
+        if kind != "pod_vectorized":
+            raise NotImplementedError(f"constProj_basis_type '{kind}' is not built on the device yet (SURVEY 8(a) a10/a11); "
+                                      "there is no CPU fallback")
+        _, comm = runtime.get()
+        file_name = os.path.join(p.constProj_output_directory, p.name + "_" + p.constProj_name + self.file_name_sing)
+        if self.storeSingVal and comm.rank == 0:
+            with open(file_name + '.csv', 'w', encoding='UTF8') as singFile:
+                writer = csv.writer(singFile)
+                writer.writerow(headerSing)
+                self.compute_pod_for_vectorized_nonlinear_snapshots_tensor(writer)
+        else:
+            self.compute_pod_for_vectorized_nonlinear_snapshots_tensor(None)
+
+    @log_time("")
+    def compute_pod_for_vectorized_nonlinear_snapshots_tensor(self, writer=None):
+        """Thin SVD of the (3 e p) x F snapshot matrix (:298-320) through its F x F Gram."""
+        ops, comm = runtime.get()
+        snaps = self.nonlinearSnapshots
+        F = snaps.state.X.shape[0]
+        k_desired = min(int(self.param.deim_desired_num_components), F)
+        C, sig = engine.pod(ops, comm, snaps.state.X, snaps.shard, k_desired)
+        self.singular_values = sig
+        if writer is not None:
+            for ai, bi in zip(range(1, sig.shape[0] + 1), sig):
+                writer.writerow([ai, bi])
+        self._C, self._host = C, {}
+        self.numComp = C.shape[0]
+
+    # ------------------------------------------------------------------ post-processing
+    @log_time("")
+    def post_process_components(self):
+        ops, comm = runtime.get()
+        p, snaps, sh = self.param, self.nonlinearSnapshots, self.nonlinearSnapshots.shard
+        C, X = self._C, snaps.state.X
+        if p.constProj_standarize:
+            ops.unstandardize(C, snaps.state.mean, snaps.pre_scale_factor, sh.n)   # comps /= scale; comps += mean
+            ops.unstandardize(X, snaps.state.mean, snaps.pre_scale_factor, sh.n)   # the snapshots too (:426-430)
+        if p.constProj_orthogonal:
+            engine.orthogonalize_rows(ops, comm, C, sh, self.numComp)              # economic QR per dimension
+        if p.constProj_massWeight:
+            assert C.shape[0] == self.numComp and snaps.invMassL.shape[0] == sh.n_global
+            self._C = ops.ingest(ops.export_aos(C, snaps.state.invMassL, sh.n), None, sh.ld)
+            snaps.state.X = ops.ingest(ops.export_aos(X, snaps.state.invMassL, sh.n), None, sh.ld)
+        self._host = {}
+        snaps.invalidate_host_views()
+        print("Post-processing, Undo standardization: ", p.constProj_standarize, ". Orthogonal-ized", p.constProj_orthogonal,
+              ". Mass weighting", p.constProj_massWeight, ", and bases shape",
+              (self.numComp, sh.n_global, 3))
+
+    # ------------------------------------------------------------------ DEIM
+    @log_time("")
+    def deim(self):
+        """Classical DEIM (:797-860): geom_Pt row ids, geom_alpha = Pt // p, geom_alpha_ranges = 1..K."""
+        ops, comm = runtime.get()
+        snaps = self.nonlinearSnapshots
+        p, K = snaps.constraintsSize, self.numComp
+        Pt = engine.deim(ops, comm, self._C, snaps.shard, K)
+        if Pt is None:                       # zero residual: the reference prints and returns (:832-834)
+            return
+        self.geom_Pt = np.array(Pt)
+        self.geom_alpha = self.geom_Pt // p
+        self.geom_ep_idxs = np.array(set(int(i) for i in Pt))       # 0-d object array, as the reference stores it (:856)
+        self.geom_alpha_ranges = np.arange(1, K + 1)
+        self.geom_interpol_verts = np.array(self.geom_interpol_verts)
+        for k in range(K):
+            print(k, int(self.geom_alpha[k]))
+        print("Regular Deim interpolation, used", self.geom_alpha.shape[0], "constrained elements")
+
+    def deim_blocksForm(self):
+        raise NotImplementedError("block DEIM (constraintsComponents.py:733-795) is not built on the device yet (SURVEY a14)")
+
+    def geom_block_form_utilizing_differential_operator(self, error_in_pos_space=True):
+        raise NotImplementedError("geometric DEIM (constraintsComponents.py:619-731) is not built on the device yet (SURVEY a14)")
+
+    # ------------------------------------------------------------------ checks
+    @log_time("")
+    def test_basesSingVals(self):
+        """(Kp, 3): singular values of comps[:, :, d] normalised by the largest, per dimension (:555-569)."""
+        ops, comm = runtime.get()
+        s = np.empty((self.numComp, 3))
+        for d, sig in enumerate(engine.row_singular_values(ops, comm, self._C, self.nonlinearSnapshots.shard, self.numComp)):
+            s[:, d] = sig / sig.max()
+        return s
+
+    @staticmethod
+    def frobenius_error(f, f_reconstructed):
+        return np.linalg.norm(f - f_reconstructed)
+
+    @staticmethod
+    def relative_error_per_component(f, f_reconstructed):
+        return [np.linalg.norm(f[:, :, i] - f_reconstructed[:, :, i]) / np.linalg.norm(f[:, :, i]) for i in range(3)]
+
+    @staticmethod
+    def max_pointwise_error(f, f_reconstructed):
+        return np.max(np.abs(f - f_reconstructed)) / np.max(f)
+
+    # ------------------------------------------------------------------ outputs
+    def _gathered_comps(self):
+        _, comm = runtime.get()
+        c = self.comps
+        if comm.world > 1:
+            c = engine.gather_rows_host(comm, c, self.nonlinearSnapshots.shard, axis=1)
+        return c
+
+    @log_time("")
+    def store_components_gradually_to_files(self, start, end, step, fileType):
+        """'.bin' or '.npy', one file per k (:572-593): bases (k*p components), interpolation elements, vertices."""
+        print('Storing bases ...', end='', flush=True)
+        ops, comm = runtime.get()
+        snaps = self.nonlinearSnapshots
+        p = snaps.constraintsSize
+        out = self.param.constProj_output_directory
+        basesFile = os.path.join(out, self.fileNameBases)
+        pointsFile = os.path.join(out, self.fileName_geom_points)
+        vertsFile = os.path.join(out, "corrVerts")
+        numverts = snaps.num_constained_elements * p
+        packed = ops.pack_bin(self._C, self.numComp, snaps.shard.n).cpu().numpy()      # (3, K, ep): the .bin body order
+        if comm.world > 1:
+            packed = engine.gather_rows_host(comm, packed, snaps.shard, axis=2)
+        if comm.rank == 0:
+            for k in range(start, end + 1, step):
+                hostio.store_components_packed(basesFile, snaps.frs, k * p, numverts, 3, packed, fileType, 'Kp')
+                hostio.store_interpol_points_vector(pointsFile, snaps.frs, k,
+                                                    self.geom_alpha[:self.geom_alpha_ranges[k - 1]], fileType)
+                hostio.store_interpol_points_vector(vertsFile, snaps.frs, k, self.geom_interpol_verts[:k], fileType)
+        print('done.')
+
+    @log_time("")
+    def store_components_n_interpol_points(self):
+        """One .npz with the keys projective_dynamics/Simulators.py:179-188 reads (:596-611)."""
+        print('Storing bases and interpolation points to one file ...', end='', flush=True)
+        _, comm = runtime.get()
+        comps = self._gathered_comps()
+        if comm.rank == 0:
+            np.savez(os.path.join(self.param.constProj_output_directory,
+                                  "components_interpol_alphas_interpol_verts_interpol_alpha_ranges.npz"),
+                     components=comps, interpol_alphas=self.geom_alpha, Pt=self.geom_Pt,
+                     interpol_verts=self.geom_interpol_verts, interpol_alpha_ranges=self.geom_alpha_ranges)
+        print("done!")

@@ -170,7 +170,8 @@ def test_gemv_large_is_one_slab(cuda_ops):
 
 
 # ------------------------------------------------------------------------------------------------ DMMA contractions
-@pytest.mark.parametrize("ra,rb,M", [(5, 7, 96), (130, 70, 3 * 352), (200, 200, 3 * 4000), (257, 129, 6400)])
+@pytest.mark.parametrize("ra,rb,M", [(5, 7, 96), (130, 70, 3 * 352), (200, 200, 3 * 4000), (257, 129, 6400), (300, 200, 3 * 2400),
+                                     (201, 333, 3 * 1024), (1000, 256, 3 * 640), (300, 290, 3 * 800)])
 def test_gemm_nt(cuda_ops, ra, rb, M):
     rng = np.random.default_rng(7)
     A = torch.from_numpy(rng.standard_normal((ra, M)))
@@ -189,7 +190,8 @@ def test_gemm_nt_symmetric(cuda_ops, r, M):
     assert torch.equal(D, D.T.contiguous()), "Gram must be exactly symmetric"
 
 
-@pytest.mark.parametrize("r,q,M", [(10, 24, 3 * 64), (200, 200, 3 * 1056), (70, 71, 3 * 320), (24, 24, 3 * 1824)])
+@pytest.mark.parametrize("r,q,M", [(10, 24, 3 * 64), (200, 200, 3 * 1056), (70, 71, 3 * 320), (24, 24, 3 * 1824), (200, 333, 3 * 2080),
+                                   (256, 100, 3 * 352), (129, 50, 3 * 96), (300, 64, 3 * 352)])
 def test_gemm_nn(cuda_ops, r, q, M):
     rng = np.random.default_rng(9)
     lda = (q + 1) // 2 * 2
@@ -223,6 +225,28 @@ def test_admm_iter(cuda_ops, K, N):
     close(Zg, Z, 1e-12, "admm Z")
     close(Ug, U, 1e-12, "admm U")
     assert float((Z[:, :, :N] == 0).double().mean()) > 0.01, "test must exercise the shrink-to-zero branch"
+    assert float(Zg[:, :, N:].abs().max().item()) == 0.0 and float(Ug[:, :, N:].abs().max().item()) == 0.0
+
+
+@pytest.mark.parametrize("K,N,iters", [(10, 100, 3), (64, 333, 4), (128, 200, 2), (200, 520, 10), (201, 77, 3), (256, 70, 2)])
+def test_admm_solve(cuda_ops, K, N, iters):
+    """All ADMM iterations of one outer step in one launch == the same number of single iterations of the numpy statement."""
+    rng = np.random.default_rng(12)
+    ld = (N + 31) // 32 * 32
+    Kp = (K + 3) // 4 * 4
+    Hr = torch.zeros((K, Kp), dtype=torch.float64)
+    H = rng.standard_normal((K, K)) * 0.03
+    Hr[:, :K] = torch.from_numpy(H @ H.T + 0.4 * np.eye(K))
+    B0, Z, U = planar(rng, K, N, ld), planar(rng, K, N, ld), planar(rng, K, N, ld, 0.3)
+    Lam = torch.zeros((K, ld), dtype=torch.float64)
+    Lam[:, :N] = torch.from_numpy(rng.random((K, N)) * 16.0)
+    Lam[:, : N // 3] = 0.0
+    Zg, Ug = dev(cuda_ops, Z), dev(cuda_ops, U)
+    REF.admm_solve(Hr, B0, Z, U, Lam, K, N, 0.1, iters)
+    cuda_ops.admm_solve(dev(cuda_ops, Hr), dev(cuda_ops, B0), Zg, Ug, dev(cuda_ops, Lam), K, N, 0.1, iters)
+    close(Zg, Z, 1e-11, "admm_solve Z")
+    close(Ug, U, 1e-11, "admm_solve U")
+    assert float((Z[:, :, :N] == 0).double().mean()) > 0.01
     assert float(Zg[:, :, N:].abs().max().item()) == 0.0 and float(Ug[:, :, N:].abs().max().item()) == 0.0
 
 

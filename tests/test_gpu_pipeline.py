@@ -21,3 +21,9 @@ def test_pos_components_protocol(cuda_ops, tmp_path):
     import api_checks
     from animsnapbases_b200 import engine
     assert api_checks.check_pos_protocol(cuda_ops, engine.Comm(enabled=False), tmp_path)
+
+
+@pytest.mark.gpu
+def test_constraints_components_protocol(cuda_ops, tmp_path):
+    import api_checks
+    assert api_checks.check_constraints_protocol(cuda_ops, engine.Comm(enabled=False), tmp_path)
