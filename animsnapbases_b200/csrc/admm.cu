@@ -103,11 +103,19 @@ __device__ __forceinline__ void admm_body(double* smem, const double* __restrict
 
         int cs = 0;
         for (int it = 0; it < iters; ++it) {
+            // accumulators start at B0 (C = B0 + Hr D): the L2 loads are all in flight before the first slab is consumed
             double acc[MTN][3][2];
 #pragma unroll
-            for (int i = 0; i < MTN; ++i)
+            for (int i = 0; i < MTN; ++i) {
+                const int k = (mt0 + i) * 8 + lr;
 #pragma unroll
-                for (int d = 0; d < 3; ++d) acc[i][d][0] = acc[i][d][1] = 0.0;
+                for (int d = 0; d < 3; ++d) {
+                    double2 b0 = make_double2(0.0, 0.0);
+                    if (live && k < K) b0 = ld2(B0 + (int64_t)k * C3 + (int64_t)d * ld + n);
+                    acc[i][d][0] = b0.x;
+                    acc[i][d][1] = b0.y;
+                }
+            }
 
             for (int s = 0; s < nslab; ++s) {
                 cp_async_wait<ADMM_STAGES - 2>();
@@ -141,6 +149,12 @@ __device__ __forceinline__ void admm_body(double* smem, const double* __restrict
 
             // ---- epilogue: prox + dual update on the thread's own entries
             const bool last = it == iters - 1;
+            double2 lam[MTN];
+#pragma unroll
+            for (int i = 0; i < MTN; ++i) {
+                const int k = (mt0 + i) * 8 + lr;
+                lam[i] = (live && k < K) ? ld2(Lambda + (int64_t)k * ld + n) : make_double2(0.0, 0.0);
+            }
 #pragma unroll
             for (int i = 0; i < MTN; ++i) {
                 const int k = (mt0 + i) * 8 + lr;
@@ -149,24 +163,22 @@ __device__ __forceinline__ void admm_body(double* smem, const double* __restrict
                 double2 v[3];
 #pragma unroll
                 for (int d = 0; d < 3; ++d) {
-                    const double2 b0 = ld2(B0 + base + (int64_t)d * ld);
-                    v[d].x = (b0.x + acc[i][d][0]) + u[i][d][0];  // V = C + U
-                    v[d].y = (b0.y + acc[i][d][1]) + u[i][d][1];
+                    v[d].x = acc[i][d][0] + u[i][d][0];  // V = C + U
+                    v[d].y = acc[i][d][1] + u[i][d][1];
                 }
-                const double2 lam = ld2(Lambda + (int64_t)k * ld + n);
                 // shrink = max(0, 1 - (lambda / rho) / |v|): NaN where lambda = 0 and v = 0 (0 * inf), like the reference's 0/0
                 // (np.maximum propagates it, posComponents.py:253-256); 0 where v = 0 and lambda > 0 (1 - inf).
                 double sh[2];
                 {
                     const double s2 = __dadd_rn(__dadd_rn(__dmul_rn(v[0].x, v[0].x), __dmul_rn(v[1].x, v[1].x)),
                                                 __dmul_rn(v[2].x, v[2].x));
-                    const double t = 1.0 - __dmul_rn(__dmul_rn(inv_rho, lam.x), rsqrt(s2));
+                    const double t = 1.0 - __dmul_rn(__dmul_rn(inv_rho, lam[i].x), rsqrt(s2));
                     sh[0] = (t != t) ? t : fmax(0.0, t);
                 }
                 {
                     const double s2 = __dadd_rn(__dadd_rn(__dmul_rn(v[0].y, v[0].y), __dmul_rn(v[1].y, v[1].y)),
                                                 __dmul_rn(v[2].y, v[2].y));
-                    const double t = 1.0 - __dmul_rn(__dmul_rn(inv_rho, lam.y), rsqrt(s2));
+                    const double t = 1.0 - __dmul_rn(__dmul_rn(inv_rho, lam[i].y), rsqrt(s2));
                     sh[1] = (t != t) ? t : fmax(0.0, t);
                 }
 #pragma unroll

@@ -296,13 +296,14 @@ __global__ void centers_stage2_kernel(const double* __restrict__ pv, const long 
 
 // ------------------------------------------------------------------------------------------ k19 DEIM
 __global__ void deim_gather_kernel(const double* __restrict__ C, int64_t ld, int64_t N, int64_t row0,
-                                   const int64_t* __restrict__ Pt, int64_t k, double* __restrict__ Vp, int64_t ldv) {
-    // Vp[d][j][l] = C[l][d][Pt[j]-row0], j < k, l <= k
+                                   const int64_t* __restrict__ Pt, int64_t k, int64_t rhs, double* __restrict__ Vp,
+                                   int64_t ldv) {
+    // Vp[d][j][l] = C[l < k ? l : rhs][d][Pt[j]-row0], j < k, l <= k
     const int64_t total = 3 * k * (k + 1);
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         const int64_t l = t % (k + 1), j = (t / (k + 1)) % k, d = t / ((k + 1) * k);
         const int64_t row = Pt[j] - row0;
-        if (row >= 0 && row < N) Vp[(d * ldv + j) * ldv + l] = C[(l * 3 + d) * ld + row];
+        if (row >= 0 && row < N) Vp[(d * ldv + j) * ldv + l] = C[((l < k ? l : rhs) * 3 + d) * ld + row];
     }
 }
 
@@ -364,7 +365,8 @@ __global__ void __launch_bounds__(256) deim_solve_kernel(const double* __restric
 
 // e[n] = |sum_l a[d][l] C[l][d][n] - C[k][d][n]|^2 summed over d; block partial max|r|
 __global__ void __launch_bounds__(256) deim_residual_kernel(const double* __restrict__ C, int64_t ld, int64_t N,
-                                                           int64_t k, const double* __restrict__ a, int64_t lda_a,
+                                                           int64_t k, int64_t target, int accumulate,
+                                                           const double* __restrict__ a, int64_t lda_a,
                                                            double* __restrict__ e, double* __restrict__ pmax) {
     extern __shared__ double sa[];  // 3 x k
     __shared__ double sh[33];
@@ -383,14 +385,15 @@ __global__ void __launch_bounds__(256) deim_residual_kernel(const double* __rest
                 s1 = fma(sa[d * k + l + 1], C[((l + 1) * 3 + d) * ld + n], s1);
             }
             if (l < k) s0 = fma(sa[d * k + l], C[(l * 3 + d) * ld + n], s0);
-            const double v = C[(k * 3 + d) * ld + n];
+            const double v = C[(target * 3 + d) * ld + n];
             r[d] = k == 0 ? v : (s0 + s1) - v;
             m = fmax(m, fabs(r[d]));
         }
-        e[n] = __dadd_rn(__dadd_rn(__dmul_rn(r[0], r[0]), __dmul_rn(r[1], r[1])), __dmul_rn(r[2], r[2]));
+        const double en = __dadd_rn(__dadd_rn(__dmul_rn(r[0], r[0]), __dmul_rn(r[1], r[1])), __dmul_rn(r[2], r[2]));
+        e[n] = accumulate ? __dadd_rn(e[n], en) : en;
     }
     m = block_max(m, sh);
-    if (threadIdx.x == 0) pmax[blockIdx.x] = m;
+    if (threadIdx.x == 0) pmax[blockIdx.x] = accumulate ? fmax(pmax[blockIdx.x], m) : m;
 }
 __global__ void max_partials_kernel(const double* __restrict__ p, int64_t nb, double* __restrict__ out) {
     __shared__ double sh[33];
@@ -528,13 +531,19 @@ int asb_component_centers(const double* C, const double* Lambda, int64_t K, int6
     return ASB_OK;
 }
 
-int asb_deim_gather(const double* C, int64_t ld, int64_t N, int64_t row0, const int64_t* Pt, int64_t k, double* Vp,
-                    int64_t ldv, asb_stream_t stream) {
-    ASB_REQUIRE(C && Pt && Vp && k >= 1 && ldv >= k + 1, "deim_gather: bad arguments");
+int asb_deim_gather_rhs(const double* C, int64_t ld, int64_t N, int64_t row0, const int64_t* Pt, int64_t k, int64_t rhs,
+                        double* Vp, int64_t ldv, asb_stream_t stream) {
+    ASB_REQUIRE(C && Pt && Vp && k >= 1 && ldv >= k + 1 && rhs >= 0, "deim_gather: bad arguments");
     const int64_t total = 3 * k * (k + 1);
-    deim_gather_kernel<<<(unsigned)std::min<int64_t>(cdiv(total, 256), 1024), 256, 0, S(stream)>>>(C, ld, N, row0, Pt, k, Vp, ldv);
+    deim_gather_kernel<<<(unsigned)std::min<int64_t>(cdiv(total, 256), 1024), 256, 0, S(stream)>>>(C, ld, N, row0, Pt, k, rhs,
+                                                                                                Vp, ldv);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
+}
+
+int asb_deim_gather(const double* C, int64_t ld, int64_t N, int64_t row0, const int64_t* Pt, int64_t k, double* Vp,
+                    int64_t ldv, asb_stream_t stream) {
+    return asb_deim_gather_rhs(C, ld, N, row0, Pt, k, k, Vp, ldv, stream);
 }
 
 int asb_deim_solve(const double* Vp, int64_t ldv, int64_t k, double* a, int64_t lda_a, void* ws, int* info_dev,
@@ -545,17 +554,23 @@ int asb_deim_solve(const double* Vp, int64_t ldv, int64_t k, double* a, int64_t 
     return ASB_OK;
 }
 
-int asb_deim_residual(const double* C, int64_t ld, int64_t N, int64_t k, const double* a, int64_t lda_a, double* e,
-                      double* maxabs, void* ws, asb_stream_t stream) {
-    ASB_REQUIRE(C && e && maxabs && ws && N > 0 && k >= 0 && (k == 0 || a), "deim_residual: bad arguments");
+int asb_deim_residual_block(const double* C, int64_t ld, int64_t N, int64_t k, int64_t target, int accumulate,
+                            const double* a, int64_t lda_a, double* e, double* maxabs, void* ws, asb_stream_t stream) {
+    ASB_REQUIRE(C && e && maxabs && ws && N > 0 && k >= 0 && target >= 0 && (k == 0 || a), "deim_residual: bad arguments");
     ASB_REQUIRE(3 * k * 8 <= 48 * 1024, "deim_residual: k too large");
     const int64_t nb = cdiv(N, 256);
     double* pmax = reinterpret_cast<double*>(ws);
-    deim_residual_kernel<<<(unsigned)nb, 256, (size_t)(3 * std::max<int64_t>(k, 1) * 8), S(stream)>>>(C, ld, N, k, a, lda_a, e, pmax);
+    deim_residual_kernel<<<(unsigned)nb, 256, (size_t)(3 * std::max<int64_t>(k, 1) * 8), S(stream)>>>(
+        C, ld, N, k, target, accumulate, a, lda_a, e, pmax);
     ASB_LAUNCH_CHECK();
     max_partials_kernel<<<1, 256, 0, S(stream)>>>(pmax, nb, maxabs);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
+}
+
+int asb_deim_residual(const double* C, int64_t ld, int64_t N, int64_t k, const double* a, int64_t lda_a, double* e,
+                      double* maxabs, void* ws, asb_stream_t stream) {
+    return asb_deim_residual_block(C, ld, N, k, k, 0, a, lda_a, e, maxabs, ws, stream);
 }
 
 int asb_cgs_dots(const double* T, int64_t k, int64_t d, int64_t N, int64_t ld, double* h, void* ws, asb_stream_t stream) {

@@ -164,6 +164,15 @@ __global__ void sum_slabs_kernel(const double* __restrict__ part, double* __rest
     out[i] = s;
 }
 
+// out[j] = sum of `group` consecutive entries (fixed ascending order)
+__global__ void group_sum_kernel(const double* __restrict__ v, int64_t ng, int64_t group, double* __restrict__ out) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= ng) return;
+    double s = 0.0;
+    for (int64_t i = 0; i < group; ++i) s = __dadd_rn(s, v[j * group + i]);
+    out[j] = s;
+}
+
 __global__ void argmax_stage1_kernel(const double* __restrict__ v, int64_t n, int64_t chunk, double* __restrict__ pv,
                                      long long* __restrict__ pi) {
     __shared__ double shv[33];
@@ -464,6 +473,13 @@ int asb_vertex_energy(const double* R, double* e, int64_t F, int64_t N, int64_t 
         sum_slabs_kernel<<<(unsigned)cdiv(ld, 256), 256, 0, S(stream)>>>(part, e, ld, ns);
         ASB_LAUNCH_CHECK();
     }
+    return ASB_OK;
+}
+
+int asb_group_sum(const double* v, int64_t n, int64_t group, double* out, asb_stream_t stream) {
+    ASB_REQUIRE(v && out && n > 0 && group >= 1 && n % group == 0, "group_sum: n must be a multiple of the group size");
+    group_sum_kernel<<<(unsigned)cdiv(n / group, 256), 256, 0, S(stream)>>>(v, n / group, group, out);
+    ASB_LAUNCH_CHECK();
     return ASB_OK;
 }
 

@@ -170,6 +170,64 @@ def deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1
     return C, W, meas, picked, (R if keep_residual else None)
 
 
+def deflate_blocks(ops, comm, X, shard, p, num_blocks, block=8, keep_residual=False):
+    """Block deflation of snapbases/constraintsComponents.py:324-412 (global support) on a row shard: per block, the
+    element with the largest residual energy over its p constraint rows (:86-96), then p rank-1 steps at its rows
+    (each on the residual left by the previous one).  Same kernels and the same lazy rank-update blocking as `deflate`.
+    The shard must hold whole elements (Shard.make(..., multiple=lcm(32, p))).
+    Returns C (K p, 3, ld), W (F, Kp'), meas (K, 3 + p) rows [k, idx, |R|_F, sigma_0..sigma_{p-1}], element ids (K,),
+    row ids (K p,), R."""
+    F, _, ld = X.shape
+    N, row0 = shard.n, shard.row0
+    assert N % p == 0 and row0 % p == 0, "block deflation needs whole elements per shard"
+    K = num_blocks * p
+    Kp = (K + 3) // 4 * 4
+    R = X.clone()
+    W = ops.zeros((F, Kp))
+    C = ops.zeros((K, 3, ld))
+    meas = ops.zeros((K, 3))
+    elems = ops.zeros((num_blocks,), I64)
+    rows = ops.zeros((K,), I64)
+    e = ops.vertex_energy(R, N)
+    eg = ops.zeros((max(N // p, 1),))
+    g = ops.empty((3, ld))
+    traj = ops.zeros((3, F))
+    coef = ops.zeros((16,))
+    scal = ops.zeros((2,))
+    val = ops.zeros((1,))
+    idx = ops.zeros((1,), I64)
+    k0 = 0
+    for kb in range(num_blocks):
+        if N:
+            ops.group_sum(e, N, p, eg)
+            ops.argmax_first(eg, N // p, row0 // p, val, idx)
+        else:
+            val.fill_(-float("inf"))
+        comm.argmax_pairs(val, idx)
+        elems[kb:kb + 1].copy_(idx)
+        for i in range(p):
+            k = kb * p + i
+            rows[k:k + 1] = idx * p + i                       # index bookkeeping only
+            if comm.world > 1:
+                traj.zero_()
+            ops.gather_traj(R, N, rows[k:k + 1], row0, W, k0, C, k - k0, traj)
+            comm.allreduce_sum(traj)
+            ops.traj_rank1(traj, F, False, W, k, k0, coef, scal)
+            ops.deflate_gemv(R, N, W, k, g)
+            ops.deflate_finish(g, C, k, k0, coef, None, scal, e, N, meas[k])
+            if comm.world > 1:
+                comm.allreduce_sum(meas[k, 2:3])
+                meas[k, 1:2] = torch.sqrt(meas[k, 2:3])
+            if k - k0 + 1 == block or k == K - 1:
+                ops.rank_update(R, N, W, C, k0, k - k0 + 1, e)
+                k0 = k + 1
+    m = meas.cpu().numpy().reshape(num_blocks, p, 3)
+    el = elems.cpu().numpy()
+    table = np.concatenate([np.arange(num_blocks, dtype=float)[:, None], el[:, None].astype(float), m[:, p - 1, 1:2], m[:, :, 0]],
+                           axis=1)
+    return C, W, table, el, rows.cpu().numpy(), (R if keep_residual else None)
+
+
 # ====================================================================================== SPLOCS (k10-k14)
 def splocs(ops, comm, X, shard, C, W, K, geodesic, num_iters, num_admm, lam, rho, dmin=0.1, dmax=0.25, log=print):
     """SPLOCS global optimisation of snapbases/posComponents.py:132-189 in Gram form.
@@ -343,6 +401,51 @@ def deim(ops, comm, C, shard, K):
         print("ERROR!: zero residual!!")
         return None
     return Pt.cpu().numpy()
+
+
+def deim_blocks(ops, comm, C, shard, p):
+    """Block DEIM of snapbases/constraintsComponents.py:733-795: C (K p, 3, ld) planar basis, p rows per pick.
+    Step k solves V[Pt, :kp] a = v_t[Pt] for each of the p targets t of block k (per dimension), accumulates the row
+    energies of the p residuals, picks the first-max row, and appends all p rows of its element.
+    Returns dict(Pt (K p,), alpha (K,), alpha_ranges (K,), idxs (K,)) on the host, or None on a zero residual."""
+    N, row0 = shard.n, shard.row0
+    Kc = C.shape[0]
+    K = Kc // p
+    Kp = (Kc + 3) // 4 * 4
+    Pt = ops.zeros((Kc,), I64)
+    e = ops.zeros((C.shape[2],))
+    a = ops.zeros((3, Kp))
+    ldv = Kc + 1
+    Vp = ops.zeros((3, ldv, ldv))
+    maxabs = ops.zeros((K,))
+    info = ops.zeros((1,), I32)
+    val = ops.zeros((1,))
+    idx = ops.zeros((1,), I64)
+    idxs = ops.zeros((K,), I64)
+    steps = torch.arange(p, dtype=I64, device=Pt.device)
+    for k in range(K):
+        nb = k * p
+        for m in range(p):
+            if nb > 0:
+                if comm.world > 1:
+                    Vp.zero_()
+                ops.deim_gather_rhs(C, N, row0, Pt, nb, nb + m, Vp)
+                comm.allreduce_sum(Vp)
+                ops.deim_solve(Vp, nb, a, info)
+            ops.deim_residual_block(C, N, nb, nb + m, m > 0, a, e, maxabs[k:k + 1])
+        ops.argmax_first(e, N, row0, val, idx)
+        comm.argmax_pairs(val, idx)
+        idxs[k:k + 1].copy_(idx)
+        Pt[nb:nb + p] = (idx // p) * p + steps                # all p rows of the picked element (:781-783)
+    comm.allreduce_max(maxabs)
+    if int(info.item()) != 0:
+        raise FloatingPointError("block DEIM: singular interpolation matrix at step %d" % int(info.item()))
+    mx = maxabs.cpu().numpy()
+    if K > 1 and np.any(mx[1:] <= 1e-8):
+        print("ERROR!: zero residual!!")
+        return None
+    ix = idxs.cpu().numpy()
+    return dict(Pt=Pt.cpu().numpy(), alpha=ix // p, alpha_ranges=np.arange(1, K + 1), idxs=ix)
 
 
 # ====================================================================================== per-dimension Gram helpers

@@ -155,6 +155,9 @@ class CudaOps:
         self._call("asb_argmax_first", self._p(v), n, index_offset, self._p(out_val), self._p(out_idx),
                    self._p(self.ws_for(1, n)))
 
+    def group_sum(self, v, n, group, out):
+        self._call("asb_group_sum", self._p(v), n, group, self._p(out))
+
     def gather_traj(self, R, N, idx_dev, row0, W, k0, C, npend, traj):
         """W: (F, Kmax) weights, C: (Kmax, 3, ld) components; pending block = columns/rows [k0, k0+npend)."""
         F, _, ld = R.shape
@@ -263,6 +266,13 @@ class CudaOps:
     # ------------------------------------------------------------------ DEIM
     def deim_gather(self, C, N, row0, Pt, k, Vp):
         self._call("asb_deim_gather", self._p(C), C.shape[2], N, row0, self._p(Pt), k, self._p(Vp), Vp.shape[1])
+
+    def deim_gather_rhs(self, C, N, row0, Pt, k, rhs, Vp):
+        self._call("asb_deim_gather_rhs", self._p(C), C.shape[2], N, row0, self._p(Pt), k, rhs, self._p(Vp), Vp.shape[1])
+
+    def deim_residual_block(self, C, N, k, target, accumulate, a, e, maxabs):
+        self._call("asb_deim_residual_block", self._p(C), C.shape[2], N, k, target, int(accumulate), self._p(a), a.stride(0),
+                   self._p(e), self._p(maxabs), self._p(self.ws_for(1, C.shape[2])))
 
     def deim_solve(self, Vp, k, a, info):
         ws = self.workspace(3 * k * (k + 1) * 8 + 1024)

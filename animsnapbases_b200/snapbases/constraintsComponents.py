@@ -9,8 +9,11 @@ Device work goes through animsnapbases_b200.engine -> libasb.so:
   post-process    (:415-446)  unscale + mean, per-dimension economic QR (CGS2), M^-1/2 row scaling         engine.orthogonalize_rows
   deim            (:797-860)  greedy point selection, one index set for x/y/z, bit-exact first-max argmax   engine.deim
 
-Basis types 'pca_blocks' / 'pca_blocks_with_St' / 'pod' and the block / geometric DEIM variants are SURVEY 8(a) rows a10,
-a11, a14 (after the pod_vectorized + deim path); they raise NotImplementedError here rather than fall back to the CPU.
+  pca_blocks      (:324-412)  block deflation: element energy argmax + p rank-1 steps per block               engine.deflate_blocks
+  deim_blocksForm (:733-795)  block DEIM, p rows per pick                                                   engine.deim_blocks
+
+Basis types 'pca_blocks_with_St' / 'pod' and the geometric DEIM variant raise
+NotImplementedError here rather than fall back to the CPU.
 The plotting / polyscope methods of the reference (:865-1156) are out of scope (graphics: unavailable on this box).
 """
 from __future__ import annotations
@@ -33,7 +36,7 @@ class constraintsComponents:  # Components == bases
         self.storeSingVal = False
         self.nonlinearSnapshots = nonlinearSnapshots(param)
         self.param = param
-        self.weigs = None
+        self._W = None
         self.ortho_comps = None
         self.largeDeforPoints = None
         self.largeDeforBlocks = None
@@ -60,6 +63,15 @@ class constraintsComponents:  # Components == bases
             ops, _ = runtime.get()
             self._host["comps"] = ops.export_aos(self._C, None, self.nonlinearSnapshots.shard.n).cpu().numpy()
         return self._host["comps"]
+
+    @property
+    def weigs(self):
+        return None if self._W is None else self._W.cpu().numpy()[:, :self._C.shape[0]]
+
+    @property
+    def _rows(self):
+        """Number of component rows: numComp for POD, numComp * p for block bases."""
+        return 0 if self._C is None else self._C.shape[0]
 
     def config(self, fileNameBases="p_nl_", fileName_geom_points="p_nl_interpol_points_",
                file_name_sing="_constrprojBases_pcaExtraction_singValues"):
@@ -97,18 +109,40 @@ class constraintsComponents:  # Components == bases
             headerSing = ['component', 'singVal']
         if kind not in ("pod", "pod_vectorized", "pca_blocks", "pca_blocks_with_St"):
             raise ValueError("Uknown basis type: ", kind)
-        if kind != "pod_vectorized":
+        if kind not in ("pod_vectorized", "pca_blocks"):
             raise NotImplementedError(f"constProj_basis_type '{kind}' is not built on the device yet (SURVEY 8(a) a10/a11); "
                                       "there is no CPU fallback")
+        compute = self.compute_pod_for_vectorized_nonlinear_snapshots_tensor if kind == "pod_vectorized" \
+            else self.compute_nonlinearity_bases_blocks
         _, comm = runtime.get()
         file_name = os.path.join(p.constProj_output_directory, p.name + "_" + p.constProj_name + self.file_name_sing)
         if self.storeSingVal and comm.rank == 0:
             with open(file_name + '.csv', 'w', encoding='UTF8') as singFile:
                 writer = csv.writer(singFile)
                 writer.writerow(headerSing)
-                self.compute_pod_for_vectorized_nonlinear_snapshots_tensor(writer)
+                compute(writer)
         else:
-            self.compute_pod_for_vectorized_nonlinear_snapshots_tensor(None)
+            compute(None)
+
+    @log_time("")
+    def compute_nonlinearity_bases_blocks(self, writer=None):
+        """Block deflation (:324-412): K blocks of p rank-1 components; numComp counts BLOCKS, comps has K p rows."""
+        if self.support == 'local':
+            raise ValueError(' Local support is not yet available for nonlinearity')
+        ops, comm = runtime.get()
+        snaps = self.nonlinearSnapshots
+        p = snaps.constraintsSize
+        C, W, table, elems, rows, _ = engine.deflate_blocks(ops, comm, snaps.state.X, snaps.shard, p,
+                                                            int(self.param.deim_desired_num_components),
+                                                            block=int(getattr(self.param, "engine_deflation_block", 8)))
+        self._C, self._W, self._host = C, W, {}
+        self.measures_at_largeDeforVerts = table
+        self.largeDeforPoints, self.largeDeforBlocks = elems, rows
+        self.numComp = C.shape[0] // p
+        if writer is not None:
+            for r in table:
+                writer.writerow([int(r[0]), int(r[1])] + [float(v) for v in r[2:]])
+        print("bases shape", (C.shape[0], snaps.shard.n_global, 3), "number of components", self.numComp)
 
     @log_time("")
     def compute_pod_for_vectorized_nonlinear_snapshots_tensor(self, writer=None):
@@ -135,16 +169,16 @@ class constraintsComponents:  # Components == bases
             ops.unstandardize(C, snaps.state.mean, snaps.pre_scale_factor, sh.n)   # comps /= scale; comps += mean
             ops.unstandardize(X, snaps.state.mean, snaps.pre_scale_factor, sh.n)   # the snapshots too (:426-430)
         if p.constProj_orthogonal:
-            engine.orthogonalize_rows(ops, comm, C, sh, self.numComp)              # economic QR per dimension
+            engine.orthogonalize_rows(ops, comm, C, sh, self._rows)                # economic QR per dimension
         if p.constProj_massWeight:
-            assert C.shape[0] == self.numComp and snaps.invMassL.shape[0] == sh.n_global
+            assert snaps.invMassL.shape[0] == sh.n_global
             self._C = ops.ingest(ops.export_aos(C, snaps.state.invMassL, sh.n), None, sh.ld)
             snaps.state.X = ops.ingest(ops.export_aos(X, snaps.state.invMassL, sh.n), None, sh.ld)
         self._host = {}
         snaps.invalidate_host_views()
         print("Post-processing, Undo standardization: ", p.constProj_standarize, ". Orthogonal-ized", p.constProj_orthogonal,
               ". Mass weighting", p.constProj_massWeight, ", and bases shape",
-              (self.numComp, sh.n_global, 3))
+              (self._rows, sh.n_global, 3))
 
     # ------------------------------------------------------------------ DEIM
     @log_time("")
@@ -165,8 +199,20 @@ class constraintsComponents:  # Components == bases
             print(k, int(self.geom_alpha[k]))
         print("Regular Deim interpolation, used", self.geom_alpha.shape[0], "constrained elements")
 
+    @log_time("")
     def deim_blocksForm(self):
-        raise NotImplementedError("block DEIM (constraintsComponents.py:733-795) is not built on the device yet (SURVEY a14)")
+        """Block DEIM (:733-795): p rows per pick; geom_Pt has numComp * p row ids."""
+        ops, comm = runtime.get()
+        snaps = self.nonlinearSnapshots
+        out = engine.deim_blocks(ops, comm, self._C, snaps.shard, snaps.constraintsSize)
+        if out is None:
+            return
+        self.geom_Pt, self.geom_alpha, self.geom_alpha_ranges = out["Pt"], out["alpha"], out["alpha_ranges"]
+        self.geom_ep_idxs = np.array(set(int(i) for i in out["idxs"]))
+        self.geom_interpol_verts = np.array(self.geom_interpol_verts)
+        for k in range(self.geom_alpha.shape[0]):
+            print(k, int(self.geom_alpha[k]))
+        print("Regular Deim interpolation, used", self.geom_alpha.shape[0], "constrained elements")
 
     def geom_block_form_utilizing_differential_operator(self, error_in_pos_space=True):
         raise NotImplementedError("geometric DEIM (constraintsComponents.py:619-731) is not built on the device yet (SURVEY a14)")
@@ -176,8 +222,8 @@ class constraintsComponents:  # Components == bases
     def test_basesSingVals(self):
         """(Kp, 3): singular values of comps[:, :, d] normalised by the largest, per dimension (:555-569)."""
         ops, comm = runtime.get()
-        s = np.empty((self.numComp, 3))
-        for d, sig in enumerate(engine.row_singular_values(ops, comm, self._C, self.nonlinearSnapshots.shard, self.numComp)):
+        s = np.empty((self._rows, 3))
+        for d, sig in enumerate(engine.row_singular_values(ops, comm, self._C, self.nonlinearSnapshots.shard, self._rows)):
             s[:, d] = sig / sig.max()
         return s
 
@@ -213,7 +259,7 @@ class constraintsComponents:  # Components == bases
         pointsFile = os.path.join(out, self.fileName_geom_points)
         vertsFile = os.path.join(out, "corrVerts")
         numverts = snaps.num_constained_elements * p
-        packed = ops.pack_bin(self._C, self.numComp, snaps.shard.n).cpu().numpy()      # (3, K, ep): the .bin body order
+        packed = ops.pack_bin(self._C, self._rows, snaps.shard.n).cpu().numpy()        # (3, Kp, ep): the .bin body order
         if comm.world > 1:
             packed = engine.gather_rows_host(comm, packed, snaps.shard, axis=2)
         if comm.rank == 0:

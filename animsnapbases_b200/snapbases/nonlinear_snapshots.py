@@ -95,7 +95,8 @@ class nonlinearSnapshots:
             print('Error! unknown rest shape: ', self.rest_shape)
             sys.exit(1)
         ep = self._raw.shape[1]
-        self.shard = engine.Shard.make(ep, comm.world, comm.rank)
+        mult = int(np.lcm(32, max(int(self.constraintsSize), 1)))       # whole elements per shard (block deflation / DEIM)
+        self.shard = engine.Shard.make(ep, comm.world, comm.rank, multiple=mult)
         rows = slice(self.shard.row0, self.shard.row0 + self.shard.n)
         src = ops.to_device(np.ascontiguousarray(self._raw[:, rows]))
         rest = self.rest_shape if p.constProj_standarize else "first"

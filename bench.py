@@ -206,8 +206,8 @@ def main():
         build(st)
     sync_all()
     # ---- timed region (device-resident inputs)
-    timed = ["asb_deflate_gemv", "asb_rank_update", "asb_admm_iter", "asb_gemm_nn", "asb_gemm_nt", "asb_weights_sweep",
-             "asb_spmv_csr", "asb_component_centers"]
+    timed = ["asb_deflate_gemv", "asb_rank_update", "asb_admm_solve", "asb_gemm_nn", "asb_gemm_nt", "asb_weights_sweep",
+             "asb_component_centers", "asb_mf_forward", "asb_mf_backward", "asb_support_map", "asb_vertex_energy"]
     ops.time_kernels(timed)
     ops.reset_launch_count()
     clocks = ClockSampler(local_rank)
@@ -288,28 +288,31 @@ def main():
     fp64_peak = 2 * 8192.0 ** 3 / (best * 1e-3) / 1e12
     del a, b
     n_loc, ld = sh.n, sh.ld
-    per_launch = {
-        "asb_deflate_gemv": ("hbm", 24.0 * F * ld),                       # one read pass over R: S bytes (local shard)
-        "asb_rank_update": ("hbm", 2 * 24.0 * F * ld),
-        "asb_admm_iter": ("tensor", 2.0 * K * K * 3 * ld),
-        "asb_gemm_nn": ("tensor", 2.0 * K * F * 3 * ld),
-        "asb_gemm_nt": ("tensor", None),
+    M = 3.0 * ld
+    # ALGORITHMIC work of all launches of one entry point in one step (local shard)
+    per_step = {
+        "asb_deflate_gemv": ("hbm", K * 8.0 * F * M),                       # K read passes over R
+        "asb_rank_update": ("hbm", -(-K // args.block) * 2 * 8.0 * F * M),   # read + write pass per block of components
+        "asb_admm_solve": ("tensor", Is * Ia * 2.0 * K * K * M),             # Hr (Z - U), Ia iterations fused per launch
+        "asb_gemm_nn": ("tensor", Is * 2.0 * K * F * M),                     # B0 = (H^-1 W^T) X
+        "asb_gemm_nt": ("tensor", (Is + 1) * (2.0 * F * K + K * (K + 1.0)) * M),   # P = X C^T and the symmetric Q = C C^T
     }
     dom = max(ktimes.items(), key=lambda kv: kv[1][1])[0] if ktimes else None
     roof = None
-    if dom in per_launch and per_launch[dom][1] and ktimes[dom][0]:
-        bound, work = per_launch[dom]
-        avg_s = ktimes[dom][1] / ktimes[dom][0] * 1e-3
+    if dom in per_step and ktimes[dom][0]:
+        bound, work = per_step[dom]
+        work *= args.steps
+        tot_s = ktimes[dom][1] * 1e-3
+        common = {"kernel": dom, "bound": bound, "traffic": None, "avg_launch_ms": ktimes[dom][1] / ktimes[dom][0],
+                  "launches": ktimes[dom][0], "work_per_launch": work / ktimes[dom][0]}
         if bound == "hbm":
-            ach = work / avg_s / 1e9
-            roof = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                    "traffic": None, "peak_source": hbm_src, "avg_launch_ms": avg_s * 1e3, "launches": ktimes[dom][0]}
+            ach = work / tot_s / 1e9
+            roof = dict(common, achieved=ach, peak=hbm_peak, unit="GB/s", frac=ach / hbm_peak, peak_source=hbm_src)
         else:
-            ach = work / avg_s / 1e12
-            roof = {"kernel": dom, "bound": "tensor", "achieved": ach, "peak": fp64_peak, "unit": "TFLOP/s",
-                    "frac": ach / fp64_peak, "traffic": None,
-                    "peak_source": "cuBLAS DGEMM 8192^3 measured in this run (fp64 is not in MEASURED_PEAKS.json)",
-                    "avg_launch_ms": avg_s * 1e3, "launches": ktimes[dom][0]}
+            ach = work / tot_s / 1e12
+            roof = dict(common, achieved=ach, peak=fp64_peak, unit="TFLOP/s", frac=ach / fp64_peak,
+                        peak_source="cuBLAS DGEMM 8192^3 measured in this run (fp64 is not in MEASURED_PEAKS.json; "
+                                    "sm_100a has no fp64 tcgen05 kind: DMMA.8x8x4 is the fp64 tensor path)")
     defl_bytes, splocs_flops = work_units(N, F, K, Is, Ia)
     ideal = defl_bytes / world / (hbm_peak * 1e9) + splocs_flops / world / (fp64_peak * 1e12)
     line = {

@@ -79,6 +79,9 @@ int asb_unstandardize(double* T, const double* mean, double scale, int64_t R, in
 /* e[n] = sum_f ((x^2 + y^2) + z^2), f ascending; `block` > 1 sums the energies of `block` consecutive
  * rows into e[n / block] (element energy, snapbases/constraintsComponents.py:86-96). (:78-79) */
 int asb_vertex_energy(const double* R, double* e, int64_t F, int64_t N, int64_t ld, void* ws, asb_stream_t stream);
+/* out[j] = sum_{i<group} v[j*group + i] (i ascending), j < n / group: element energy over the p constraint rows of an
+ * element (indxLargestDeformation, snapbases/constraintsComponents.py:86-96). */
+int asb_group_sum(const double* v, int64_t n, int64_t group, double* out, asb_stream_t stream);
 /* First index of the maximum of v[0..n) (np.argmax tie rule): out_val[0], out_idx[0] = index + index_offset.
  * ws: asb_workspace_bytes(1, n). */
 int asb_argmax_first(const double* v, int64_t n, int64_t index_offset, double* out_val, int64_t* out_idx,
@@ -181,6 +184,14 @@ int asb_deim_solve(const double* Vp, int64_t ldv, int64_t k, double* a, int64_t 
  * maxabs[0] = max |r|.  For k == 0: r = C[0]. */
 int asb_deim_residual(const double* C, int64_t ld, int64_t N, int64_t k, const double* a, int64_t lda_a,
                       double* e, double* maxabs, void* ws, asb_stream_t stream);
+
+/* Block variants (deim_blocksForm, snapbases/constraintsComponents.py:733-795): the right-hand side / residual target is
+ * component `rhs` / `target` instead of component k (the basis is still components [0, k)), and the per-row energy
+ * of the p targets of a block is accumulated into e (accumulate != 0: e += r^2, maxabs = max over the block). */
+int asb_deim_gather_rhs(const double* C, int64_t ld, int64_t N, int64_t row0, const int64_t* Pt, int64_t k, int64_t rhs,
+                        double* Vp, int64_t ldv, asb_stream_t stream);
+int asb_deim_residual_block(const double* C, int64_t ld, int64_t N, int64_t k, int64_t target, int accumulate,
+                            const double* a, int64_t lda_a, double* e, double* maxabs, void* ws, asb_stream_t stream);
 
 /* ---- k6/k7: heat-method geodesics + support maps (utils/support.py:139-208) --------------------- */
 /* y[b] = A x[b] for nrhs vectors of length n (ldx apart), CSR with int32 indices. */

@@ -100,6 +100,9 @@ class NumpyOps:
         out_val[0] = float(a[i])
         out_idx[0] = i + index_offset
 
+    def group_sum(self, v, n, group, out):
+        out.numpy()[:n // group] = v.numpy()[:n].reshape(n // group, group).sum(axis=1)
+
     def gather_traj(self, R, N, idx_dev, row0, W, k0, C, npend, traj):
         i = int(idx_dev[0]) - row0
         if i < 0 or i >= N:
@@ -259,6 +262,29 @@ class NumpyOps:
             row = int(Pt[j]) - row0
             if 0 <= row < N:
                 vp[:, j, :k + 1] = c[:k + 1, :, row].T
+
+    def deim_gather_rhs(self, C, N, row0, Pt, k, rhs, Vp):
+        c, vp = C.numpy(), Vp.numpy()
+        for j in range(k):
+            row = int(Pt[j]) - row0
+            if 0 <= row < N:
+                vp[:, j, :k] = c[:k, :, row].T
+                vp[:, j, k] = c[rhs, :, row]
+
+    def deim_residual_block(self, C, N, k, target, accumulate, a, e, maxabs):
+        c = C.numpy()
+        if k == 0:
+            r = c[target, :, :N].copy()
+        else:
+            r = np.einsum("dl,ldn->dn", a.numpy()[:, :k], c[:k, :, :N]) - c[target, :, :N]
+        en = (r[0] ** 2 + r[1] ** 2) + r[2] ** 2
+        if accumulate:
+            e.numpy()[:N] += en
+            maxabs[0] = max(float(maxabs[0]), float(np.abs(r).max()))
+        else:
+            e.numpy()[:] = 0
+            e.numpy()[:N] = en
+            maxabs[0] = float(np.abs(r).max())
 
     def deim_solve(self, Vp, k, a, info):
         vp = Vp.numpy()
