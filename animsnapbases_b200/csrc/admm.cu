@@ -17,13 +17,18 @@
 
 namespace asb {
 
-constexpr int ADMM_THREADS = 256, ADMM_WM = 4, ADMM_WN = 2;
-constexpr int ADMM_BK = 16;            // k-slab of Hr per pipeline stage
-constexpr int ADMM_ALD = ADMM_BK + 4;  // 20 doubles: conflict-free 8x4 A-fragment reads
+// Two small CTAs per SM (4 row-warps x 1 vertex group each) instead of one 8-warp CTA: the slab barriers, the FP64
+// prox epilogue and the tile load/store of one CTA overlap with the DMMA stream of the other (ncu on the 8-warp version:
+// 14 % of the warp samples sat behind BAR.SYNC, DMMA pipe 61 % active).
+constexpr int ADMM_WM = 4, ADMM_WN = 1, ADMM_THREADS = ADMM_WM * ADMM_WN * 32, ADMM_CTAS_PER_SM = 2;
+constexpr int ADMM_BK = 8;             // k-slab of Hr per pipeline stage
+constexpr int ADMM_ALD = ADMM_BK + 4;  // 12 doubles: conflict-free 8x4 A-fragment reads
 constexpr int ADMM_STAGES = 3;
+constexpr int ADMM_CPR = ADMM_BK / 2;              // 16-byte chunks per staged row
+constexpr int ADMM_RPP = ADMM_THREADS / ADMM_CPR;  // rows staged per pass
 constexpr int ADMM_NV = 8 * ADMM_WN;   // vertices per tile
 constexpr int ADMM_NC = 24 * ADMM_WN;  // columns per tile: [vertex group][plane][8 vertices]
-constexpr int ADMM_DLD = ADMM_NC + 4;  // 52: stride mod 16 == 4 -> conflict-free 4x8 B-fragment reads
+constexpr int ADMM_DLD = ADMM_NC + 4;  // 28 / 52: stride mod 16 in {12, 4} -> conflict-free 4x8 B-fragment reads
 
 template <int MT, int MTN>
 __device__ __forceinline__ void admm_body(double* smem, const double* __restrict__ Hr, int64_t ldh,
@@ -40,25 +45,26 @@ __device__ __forceinline__ void admm_body(double* smem, const double* __restrict
     const int nslab = (K + ADMM_BK - 1) / ADMM_BK;
     const int total = iters * nslab;
 
-    // Hr slab stager: chunk t of a thread = row (tid>>3) + 32 t, doubles (tid&7)*2 .. +1 of the 16-column slab
-    const int srow = threadIdx.x >> 3, scc = (threadIdx.x & 7) * 2;
+    // Hr slab stager: chunk t of a thread = row tid / CPR + RPP t, doubles (tid % CPR) * 2 .. +1 of the slab
+    constexpr int NCH = (32 * MT + ADMM_RPP - 1) / ADMM_RPP;
+    const int srow = threadIdx.x / ADMM_CPR, scc = (threadIdx.x % ADMM_CPR) * 2;
     unsigned okmask = 0;
 #pragma unroll
-    for (int t = 0; t < MT; ++t)
-        if (srow + 32 * t < K) okmask |= 1u << t;
+    for (int t = 0; t < NCH; ++t)
+        if (srow + ADMM_RPP * t < K) okmask |= 1u << t;
     const double* hp = Hr + (int64_t)min(srow, K - 1) * ldh + scc;
-    const int64_t hstep = 32 * ldh;
+    const int64_t hstep = ADMM_RPP * ldh;
     const unsigned sdst = srow * ADMM_ALD + scc;
-    auto load_a = [&](int stage, int slab) {  // Hr[:, 16 slab : 16 slab + 16] -> As[stage]; rows / columns >= K zero-filled
+    auto load_a = [&](int stage, int slab) {  // Hr[:, BK slab : BK slab + BK] -> As[stage]; rows / columns >= K zero-filled
         const int k0 = slab * ADMM_BK;
         const bool kin = k0 + scc < K;
         const double* q = hp + k0;
         double* dst = As + stage * astage + sdst;
 #pragma unroll
-        for (int t = 0; t < MT; ++t) {
-            if (srow + 32 * t < rows8) {
+        for (int t = 0; t < NCH; ++t) {
+            if (srow + ADMM_RPP * t < rows8) {
                 const bool ok = kin && ((okmask >> t) & 1u);
-                cp_async16(dst + t * 32 * ADMM_ALD, ok ? q : Hr, ok ? 16 : 0);
+                cp_async16(dst + t * ADMM_RPP * ADMM_ALD, ok ? q : Hr, ok ? 16 : 0);
             }
             q += hstep;
         }
@@ -205,13 +211,17 @@ __device__ __forceinline__ void admm_body(double* smem, const double* __restrict
 }
 
 template <int MT>
-__global__ void __launch_bounds__(ADMM_THREADS, 1)
+__global__ void __launch_bounds__(ADMM_THREADS, ADMM_CTAS_PER_SM)
 admm_solve_kernel(const double* __restrict__ Hr, int64_t ldh, const double* __restrict__ B0, double* __restrict__ Z,
                   double* __restrict__ U, const double* __restrict__ Lambda, int K, int64_t N, int64_t ld,
                   double inv_rho, int iters, int64_t ntiles) {
     extern __shared__ __align__(16) double smem[];
     int mt0, mtn;
-    mtile_range(((K + 7) & ~7) >> 3, ADMM_WM, (threadIdx.x >> 5) / ADMM_WN, mt0, mtn);
+    // co-resident CTAs (blockIdx.x and blockIdx.x + #SMs under round-robin placement) rotate the row-warp roles by two
+    // sub-partitions, so the 7-tile warps of the two CTAs sit on different SM sub-partitions (13,12,13,12 instead of 14,12,12,12)
+    const int slot = (blockIdx.x / max(1u, gridDim.x / ADMM_CTAS_PER_SM)) & 1;
+    const int wm = (((threadIdx.x >> 5) / ADMM_WN) + 2 * slot) % ADMM_WM;
+    mtile_range(((K + 7) & ~7) >> 3, ADMM_WM, wm, mt0, mtn);
     const bool live = mtn > 0;   // K <= 24: some row-warps own no m-tile; they idle on tile 0 and never store
     if (!live) mt0 = 0;
     if (mtn == MT) admm_body<MT, MT>(smem, Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live);
@@ -225,7 +235,7 @@ static int launch_admm(const double* Hr, int64_t ldh, const double* B0, double* 
     const size_t smem = (size_t)rows8 * (ADMM_DLD + ADMM_STAGES * ADMM_ALD) * sizeof(double);
     ASB_CUDA(cudaFuncSetAttribute(admm_solve_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t ntiles = ld / ADMM_NV;
-    const unsigned grid = (unsigned)std::min<int64_t>(ntiles, sm_count());
+    const unsigned grid = (unsigned)std::min<int64_t>(ntiles, (int64_t)ADMM_CTAS_PER_SM * sm_count());
     admm_solve_kernel<MT><<<grid, ADMM_THREADS, smem, st>>>(Hr, ldh, B0, Z, U, Lambda, (int)K, N, ld, inv_rho, iters, ntiles);
     ASB_LAUNCH_CHECK();
     return ASB_OK;

@@ -9,6 +9,10 @@
 // strides (stride mod 16 doubles == 4 or 12) so that every 8x4 / 4x8 fragment read is bank-conflict free.
 #include "dmma.cuh"
 #include "dmma_skinny.cuh"
+#include <cstdlib>
+#ifndef ASB_SK_WN_DEFAULT
+#define ASB_SK_WN_DEFAULT 3
+#endif
 
 namespace asb {
 
@@ -233,13 +237,26 @@ static int64_t pick_slabs(int64_t tiles, int64_t M) {
     return best;
 }
 
+// column-warps of the skinny kernels: 2 (256 threads, 64-wide n-tile) or 3 (384 threads, 96-wide); ASB_SK_WN overrides
+static int sk_wn() {
+    static int wn = 0;
+    if (!wn) {
+        const char* e = getenv("ASB_SK_WN");
+        wn = (e && e[0] == '2') ? 2 : (e && e[0] == '3') ? 3 : ASB_SK_WN_DEFAULT;
+    }
+    return wn;
+}
+
+// 8 m-tiles per row-warp (rows > 224) need 128 accumulator registers: no room under the 168-register cap of 384 threads
+static int sk_wn_for(int64_t small_rows) { return cdiv(cdiv(small_rows, 8), SK_WM) >= 8 ? 2 : sk_wn(); }
+
 static NtPlan nt_plan(int64_t ra, int64_t rb, int64_t M, int symmetric) {
     NtPlan p{};
     const int64_t small = std::min(ra, rb);
     p.skinny = small <= 256;
     if (p.skinny) {
         p.swap = ra <= rb;  // A small: m-side = A, n-side = B
-        p.tiles = cdiv(p.swap ? rb : ra, SK_BN);
+        p.tiles = cdiv(p.swap ? rb : ra, 32 * sk_wn_for(small));
         p.tiles_j = 1;
     } else {
         const int64_t ti = cdiv(ra, BM), tj = cdiv(rb, BN);
@@ -252,26 +269,26 @@ static NtPlan nt_plan(int64_t ra, int64_t rb, int64_t M, int symmetric) {
     return p;
 }
 
-template <int MT>
+template <int MT, int WN>
 static int launch_nt_skinny(const double* Sm, int64_t lds, int64_t rs, const double* L, int64_t ldl, int64_t rl, int64_t M,
                             const NtPlan& p, int transpose_out, double* part, int64_t ldo, int64_t slab_stride,
                             cudaStream_t st) {
     const int rows8 = (int)((rs + 7) & ~7LL);
     const size_t smem = (size_t)SK_STAGES * (rows8 * SK_ALD + SK_BN * SK_ALD) * sizeof(double);
-    ASB_CUDA(cudaFuncSetAttribute(gemm_nt_skinny_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gemm_nt_skinny_kernel<MT><<<dim3((unsigned)p.tiles, (unsigned)p.slabs), SK_THREADS, smem, st>>>(
+    ASB_CUDA(cudaFuncSetAttribute(gemm_nt_skinny_kernel<MT, WN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gemm_nt_skinny_kernel<MT, WN><<<dim3((unsigned)p.tiles, (unsigned)p.slabs), SK_THREADS, smem, st>>>(
         Sm, lds, (int)rs, L, ldl, rl, M, p.slab_len, transpose_out, part, ldo, slab_stride);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
 }
 
-template <int MT>
+template <int MT, int WN>
 static int launch_nn_skinny(const double* A, int64_t lda, int64_t r, int64_t q, const double* B, int64_t ldb, int64_t M,
                             double alpha, const double* row_scale, double* D, int64_t ldd, cudaStream_t st) {
     const int rows8 = (int)((r + 7) & ~7LL);
     const size_t smem = (size_t)SK_STAGES * (rows8 * SK_ALD + SK_BK * SK_BLD_NN) * sizeof(double);
-    ASB_CUDA(cudaFuncSetAttribute(gemm_nn_skinny_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gemm_nn_skinny_kernel<MT><<<(unsigned)cdiv(M, SK_BN), GEMM_THREADS, smem, st>>>(A, lda, (int)r, q, B, ldb, M, alpha,
+    ASB_CUDA(cudaFuncSetAttribute(gemm_nn_skinny_kernel<MT, WN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gemm_nn_skinny_kernel<MT, WN><<<(unsigned)cdiv(M, SK_BN), SK_THREADS, smem, st>>>(A, lda, (int)r, q, B, ldb, M, alpha,
                                                                                   row_scale, D, ldd);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
@@ -300,10 +317,12 @@ int asb_gemm_nt(const double* A, int64_t lda, int64_t ra, const double* B, int64
         const int64_t lds = p.swap ? lda : ldb, ldl = p.swap ? ldb : lda, rs = p.swap ? ra : rb, rl = p.swap ? rb : ra;
         const int tr = p.swap ? 0 : 1;  // element (s, l): swap -> part[s][l], else part[l][s]
         int rc;
+        const bool wn3 = sk_wn_for(rs) == 3;
         switch ((int)cdiv(cdiv(rs, 8), SK_WM)) {  // m-tiles per row-warp
-#define ASB_NT_CASE(MT) case MT: rc = launch_nt_skinny<MT>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream)); break;
+#define ASB_NT_CASE(MT) case MT: rc = wn3 ? launch_nt_skinny<MT, 3>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream)) : launch_nt_skinny<MT, 2>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream)); break;
             ASB_NT_CASE(1) ASB_NT_CASE(2) ASB_NT_CASE(3) ASB_NT_CASE(4) ASB_NT_CASE(5) ASB_NT_CASE(6) ASB_NT_CASE(7)
-            default: rc = launch_nt_skinny<8>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream));
+            default: rc = wn3 ? launch_nt_skinny<8, 3>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream))
+                              : launch_nt_skinny<8, 2>(Sm, lds, rs, L, ldl, rl, M, p, tr, part, rb, slab_stride, S(stream));
 #undef ASB_NT_CASE
         }
         if (rc != ASB_OK) return rc;
@@ -333,10 +352,12 @@ int asb_gemm_nn(const double* A, int64_t lda, int64_t r, int64_t q, const double
     ASB_REQUIRE(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && ((uintptr_t)D % 16 == 0),
                 "gemm_nn: operands must be 16-byte aligned");
     if (r <= 256) {
+        const bool wn3 = sk_wn_for(r) == 3;
         switch ((int)cdiv(cdiv(r, 8), SK_WM)) {
-#define ASB_NN_CASE(MT) case MT: return launch_nn_skinny<MT>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
+#define ASB_NN_CASE(MT) case MT: return wn3 ? launch_nn_skinny<MT, 3>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream)) : launch_nn_skinny<MT, 2>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
             ASB_NN_CASE(1) ASB_NN_CASE(2) ASB_NN_CASE(3) ASB_NN_CASE(4) ASB_NN_CASE(5) ASB_NN_CASE(6) ASB_NN_CASE(7)
-            default: return launch_nn_skinny<8>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
+            default: return wn3 ? launch_nn_skinny<8, 3>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream))
+                                : launch_nn_skinny<8, 2>(A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, S(stream));
 #undef ASB_NN_CASE
         }
     }

@@ -12,12 +12,16 @@
 
 namespace asb {
 
-constexpr int SK_THREADS = 256, SK_BK = 16, SK_ALD = SK_BK + 4;  // 20 doubles per staged row (conflict-free fragments)
-constexpr int SK_BN = 64, SK_STAGES = 4, SK_WM = 4, SK_WN = 2, SK_NT = 4;
-constexpr int SK_BLD_NN = SK_BN + 4;  // B stored [k][n]: 68 (mod 16 == 4)
+constexpr int SK_BK = 16, SK_ALD = SK_BK + 4;  // 20 doubles per staged row (conflict-free fragments)
+constexpr int SK_STAGES = 4, SK_WM = 4, SK_NT = 4;
+// WN column-warps (2 or 3): threads = 128 WN, n-side tile = 32 WN, B stored [k][n] with stride 32 WN + 4 (mod 16 == 4)
+#define SK_THREADS (SK_WM * WN * 32)
+#define SK_BN (WN * SK_NT * 8)
+#define SK_BLD_NN (SK_BN + 4)
+#define SK_RPP (SK_THREADS / 8)   /* rows staged per pass of the CTA */
 
-// Rows-by-BK staging of a row-major operand: chunk t of a thread is row (tid>>3) + 32 t, doubles (tid&7)*2 .. +1.
-template <int NCH>
+// Rows-by-BK staging of a row-major operand: chunk t of a thread is row (tid>>3) + RPP t, doubles (tid&7)*2 .. +1.
+template <int NCH, int RPP>
 struct RowStager {
     const double* p;      // source of chunk 0 at the current k position
     const double* safe;   // always-valid address for zero-filled chunks
@@ -32,11 +36,11 @@ struct RowStager {
         okmask = 0;
 #pragma unroll
         for (int t = 0; t < NCH; ++t)
-            if (r + 32 * t < rows_staged && row0 + r + 32 * t < nrows) okmask |= 1u << t;
+            if (r + RPP * t < rows_staged && row0 + r + RPP * t < nrows) okmask |= 1u << t;
         const int64_t rr = min(row0 + r, nrows - 1);
         p = g + rr * ld + k0 + cc;
         safe = g;
-        step = 32 * ld;
+        step = RPP * ld;
         dst = r * SK_ALD + cc;
     }
     // stage the BK slice starting at the current position (kleft = doubles left on the contraction axis), then advance
@@ -46,9 +50,9 @@ struct RowStager {
         const int r = threadIdx.x >> 3;
 #pragma unroll
         for (int t = 0; t < NCH; ++t) {
-            if (r + 32 * t < rows_staged) {
+            if (r + RPP * t < rows_staged) {
                 const bool ok = kin && ((okmask >> t) & 1u);
-                cp_async16(stage + dst + t * 32 * SK_ALD, ok ? q : safe, ok ? 16 : 0);
+                cp_async16(stage + dst + t * RPP * SK_ALD, ok ? q : safe, ok ? 16 : 0);
             }
             q += step;
         }
@@ -56,7 +60,7 @@ struct RowStager {
     }
 };
 
-template <int MTN, bool NT_LAYOUT>
+template <int MTN, bool NT_LAYOUT, int WN>
 __device__ __forceinline__ void sk_mma_stage(const double* __restrict__ as, const double* __restrict__ bs,
                                              double (&acc)[MTN][SK_NT][2]) {
 #pragma unroll
@@ -75,7 +79,7 @@ __device__ __forceinline__ void sk_mma_stage(const double* __restrict__ as, cons
 
 // ------------------------------------------------------------------------------------------ gemm_nn, r <= 256
 // D (r x M) = alpha * diag(row_scale) * A (r x q) * B (q x M).  grid.x = column tile of 64.
-template <int MT, int MTN>
+template <int MT, int MTN, int WN>
 __device__ __forceinline__ void nn_skinny_body(double* smem, const double* __restrict__ A, int64_t lda, int r, int64_t q,
                                                const double* __restrict__ B, int64_t ldb, int64_t M, double alpha,
                                                const double* __restrict__ row_scale, double* __restrict__ D, int64_t ldd,
@@ -86,17 +90,17 @@ __device__ __forceinline__ void nn_skinny_body(double* smem, const double* __res
     double* Bs = smem + SK_STAGES * astage;
     const int64_t col0 = (int64_t)blockIdx.x * SK_BN;
     const int64_t nk = (q + SK_BK - 1) / SK_BK;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wn = warp % SK_WN, lr = lane >> 2, lc = lane & 3;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wn = warp % WN, lr = lane >> 2, lc = lane & 3;
     double acc[MTN][SK_NT][2];
 #pragma unroll
     for (int i = 0; i < MTN; ++i)
 #pragma unroll
         for (int j = 0; j < SK_NT; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-    RowStager<MT> sa;
+    RowStager<(32 * MT + SK_RPP - 1) / SK_RPP, SK_RPP> sa;
     sa.init(A, lda, 0, r, rows8, 0);
-    // B tile: BK x 64 -> [k][SK_BLD_NN]; 2 chunks per thread: k rows (tid>>5) and (tid>>5) + 8, doubles (tid&31)*2
-    const int brow = threadIdx.x >> 5, bcc = (threadIdx.x & 31) * 2;
+    // B tile: BK x 32 WN -> [k][SK_BLD_NN]; 2 chunks per thread: k rows tid / (16 WN) and + 8, doubles (tid % (16 WN)) * 2
+    const int brow = threadIdx.x / (SK_BN / 2), bcc = (threadIdx.x % (SK_BN / 2)) * 2;
     const bool bcol_ok = col0 + bcc < M;
     const double* bp = B + (int64_t)brow * ldb + (bcol_ok ? col0 + bcc : 0);
     const int64_t bstep = 8 * ldb;
@@ -127,7 +131,7 @@ __device__ __forceinline__ void nn_skinny_body(double* smem, const double* __res
             issue_b(Bs + ls * bstage, q - nx * SK_BK);
         }
         cp_async_commit();
-        sk_mma_stage<MTN, false>(afrag + cs * astage, bfrag + cs * bstage, acc);
+        sk_mma_stage<MTN, false, WN>(afrag + cs * astage, bfrag + cs * bstage, acc);
         cs = cs + 1 == SK_STAGES ? 0 : cs + 1;
         ls = ls + 1 == SK_STAGES ? 0 : ls + 1;
     }
@@ -145,24 +149,24 @@ __device__ __forceinline__ void nn_skinny_body(double* smem, const double* __res
     }
 }
 
-template <int MT>
+template <int MT, int WN>
 __global__ void __launch_bounds__(SK_THREADS, 1)
 gemm_nn_skinny_kernel(const double* __restrict__ A, int64_t lda, int r, int64_t q, const double* __restrict__ B, int64_t ldb,
                       int64_t M, double alpha, const double* __restrict__ row_scale, double* __restrict__ D, int64_t ldd) {
     extern __shared__ __align__(16) double smem[];
     int mt0, mtn;
-    mtile_range(((r + 7) & ~7) >> 3, SK_WM, (threadIdx.x >> 5) / SK_WN, mt0, mtn);
+    mtile_range(((r + 7) & ~7) >> 3, SK_WM, (threadIdx.x >> 5) / WN, mt0, mtn);
     const bool live = mtn > 0;   // r <= 24: some row-warps own no m-tile; they recompute tile 0 and never store
     if (!live) mt0 = 0;
-    if (mtn == MT) nn_skinny_body<MT, MT>(smem, A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, mt0, live);
-    else nn_skinny_body<MT, (MT > 1 ? MT - 1 : 1)>(smem, A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, mt0, live);
+    if (mtn == MT) nn_skinny_body<MT, MT, WN>(smem, A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, mt0, live);
+    else nn_skinny_body<MT, (MT > 1 ? MT - 1 : 1), WN>(smem, A, lda, r, q, B, ldb, M, alpha, row_scale, D, ldd, mt0, live);
 }
 
 // ------------------------------------------------------------------------------------------ gemm_nt, small side <= 256
 // part[slab][...] = S L^T over one slab of the long axis;  S: rs x M (the m-side), L: rl x M, 64 rows of L per CTA.
 // Output element (s, l) goes to part[l * ldo + s] (transpose_out) or part[s * ldo + l].
 // grid.x = L tile (fastest: CTAs sharing a slab of S run together -> S is read from HBM once), grid.y = slab.
-template <int MT, int MTN>
+template <int MT, int MTN, int WN>
 __device__ __forceinline__ void nt_skinny_body(double* smem, const double* __restrict__ Sm, int64_t lds, int rs,
                                                const double* __restrict__ L, int64_t ldl, int64_t rl, int64_t M,
                                                int64_t slab_len, int transpose_out, double* __restrict__ out, int64_t ldo,
@@ -175,16 +179,16 @@ __device__ __forceinline__ void nt_skinny_body(double* smem, const double* __res
     const int64_t m0 = (int64_t)blockIdx.y * slab_len;
     const int64_t m1 = min(M, m0 + slab_len);
     const int64_t nk = (m1 - m0 + SK_BK - 1) / SK_BK;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wn = warp % SK_WN, lr = lane >> 2, lc = lane & 3;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, wn = warp % WN, lr = lane >> 2, lc = lane & 3;
     double acc[MTN][SK_NT][2];
 #pragma unroll
     for (int i = 0; i < MTN; ++i)
 #pragma unroll
         for (int j = 0; j < SK_NT; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-    RowStager<MT> sa;
+    RowStager<(32 * MT + SK_RPP - 1) / SK_RPP, SK_RPP> sa;
     sa.init(Sm, lds, 0, rs, rows8, m0);
-    RowStager<2> sl;  // 64 rows of L
+    RowStager<2, SK_RPP> sl;  // 32 WN rows of L = 2 passes
     sl.init(L, ldl, l0, rl, SK_BN, m0);
 #pragma unroll
     for (int s = 0; s < SK_STAGES - 1; ++s) {
@@ -206,7 +210,7 @@ __device__ __forceinline__ void nt_skinny_body(double* smem, const double* __res
             sl.issue(Bs + ls * bstage, SK_BN, m1 - m0 - nx * SK_BK);
         }
         cp_async_commit();
-        sk_mma_stage<MTN, true>(afrag + cs * astage, bfrag + cs * bstage, acc);
+        sk_mma_stage<MTN, true, WN>(afrag + cs * astage, bfrag + cs * bstage, acc);
         cs = cs + 1 == SK_STAGES ? 0 : cs + 1;
         ls = ls + 1 == SK_STAGES ? 0 : ls + 1;
     }
@@ -230,19 +234,19 @@ __device__ __forceinline__ void nt_skinny_body(double* smem, const double* __res
     }
 }
 
-template <int MT>
+template <int MT, int WN>
 __global__ void __launch_bounds__(SK_THREADS, 1)
 gemm_nt_skinny_kernel(const double* __restrict__ Sm, int64_t lds, int rs, const double* __restrict__ L, int64_t ldl,
                       int64_t rl, int64_t M, int64_t slab_len, int transpose_out, double* __restrict__ out, int64_t ldo,
                       int64_t slab_stride) {
     extern __shared__ __align__(16) double smem[];
     int mt0, mtn;
-    mtile_range(((rs + 7) & ~7) >> 3, SK_WM, (threadIdx.x >> 5) / SK_WN, mt0, mtn);
+    mtile_range(((rs + 7) & ~7) >> 3, SK_WM, (threadIdx.x >> 5) / WN, mt0, mtn);
     const bool live = mtn > 0;
     if (!live) mt0 = 0;
-    if (mtn == MT) nt_skinny_body<MT, MT>(smem, Sm, lds, rs, L, ldl, rl, M, slab_len, transpose_out, out, ldo, slab_stride, mt0,
+    if (mtn == MT) nt_skinny_body<MT, MT, WN>(smem, Sm, lds, rs, L, ldl, rl, M, slab_len, transpose_out, out, ldo, slab_stride, mt0,
                                           live);
-    else nt_skinny_body<MT, (MT > 1 ? MT - 1 : 1)>(smem, Sm, lds, rs, L, ldl, rl, M, slab_len, transpose_out, out, ldo,
+    else nt_skinny_body<MT, (MT > 1 ? MT - 1 : 1), WN>(smem, Sm, lds, rs, L, ldl, rl, M, slab_len, transpose_out, out, ldo,
                                                     slab_stride, mt0, live);
 }
 

@@ -345,6 +345,46 @@ def pod(ops, comm, X, shard, k_desired):
     return comps, sig
 
 
+def pod_per_row(ops, comm, X, shard, p, k_desired):
+    """`pod` basis type (snapbases/constraintsComponents.py:274-294): p * 3 independent PODs, one per (constraint row i,
+    dimension d), of the (e x F) matrix X[:, i::p, d]^T; mode k of every (i, d) is written back to rows i::p of plane d of
+    component k.  The reference runs these SVDs in float32 on the CPU; here each is an F x F Gram on the DMMA pipe (fp64),
+    a replicated eigensolve and a back-projection GEMM.  Returns comps (K, 3, ld) and the singular values (p, 3, F)."""
+    F, _, ld = X.shape
+    N = shard.n
+    assert N % p == 0 and shard.row0 % p == 0, "per-row POD needs whole elements per shard"
+    e_loc = N // p
+    e_glob = shard.n_global // p
+    K = min(int(k_desired), F, e_glob)
+    ep = max((e_loc + 1) // 2 * 2, 2)
+    Fp = (F + 1) // 2 * 2
+    comps = ops.zeros((K, 3, ld))
+    sigmas = np.zeros((p, 3, F))
+    Xi = ops.zeros((F, ep))
+    Ui = ops.empty((K, ep))
+    G = ops.zeros((F, Fp))
+    order = ops.to_device(np.arange(F - 1, F - 1 - K, -1).astype(np.int64))
+    for i in range(p):
+        for d in range(3):
+            if e_loc:
+                Xi[:, :e_loc].copy_(X[:, d, i:N:p])                 # strided gather of the element rows (data movement)
+            ops.gemm_nt(Xi, F, Xi, F, ep, symmetric=True, out=G)
+            comm.allreduce_sum(G)
+            evals, info = ops.syevd(G, F)
+            if int(info.item()) != 0:
+                raise FloatingPointError("syevd failed")
+            lam = evals.cpu().numpy()[::-1].copy()
+            sig = np.sqrt(np.maximum(lam, 0.0))
+            sigmas[i, d] = sig
+            floor = F * np.finfo(np.float64).eps * lam[0]
+            inv = np.where(lam[:K] > floor, 1.0 / np.where(sig[:K] > 0, sig[:K], 1.0), 0.0)
+            A = torch.index_select(G, 0, order).contiguous()
+            ops.gemm_nn(A, K, F, Xi, ep, 1.0, Ui, row_scale=ops.to_device(inv))
+            if e_loc:
+                comps[:, d, i:N:p].copy_(Ui[:, :e_loc])
+    return comps, sigmas
+
+
 # ====================================================================================== post-processing (k18)
 def orthogonalize_rows(ops, comm, T, shard, K):
     """Per-dimension orthonormalisation of the K rows of T[:, d, :] (economic QR of the (N x K) matrix,

@@ -112,6 +112,10 @@ class HeatGeodesics:
                       "operator_bytes": self.heat.stats["operator_bytes"] + self.pois.stats["operator_bytes"]}
         self._cache = {}
 
+    def reset(self):
+        """Drop the memoised support maps (a new basis build starts cold)."""
+        self._cache = {}
+
     # ------------------------------------------------------------------ queries
     def distances(self, idx_dev):
         """phi (B, ldx) for the B source vertices in idx_dev (int64 device tensor); phi is NOT yet shifted by its

@@ -12,7 +12,9 @@ Device work goes through animsnapbases_b200.engine -> libasb.so:
   pca_blocks      (:324-412)  block deflation: element energy argmax + p rank-1 steps per block               engine.deflate_blocks
   deim_blocksForm (:733-795)  block DEIM, p rows per pick                                                   engine.deim_blocks
 
-Basis types 'pca_blocks_with_St' / 'pod' and the geometric DEIM variant raise
+  pod             (:274-294)  p * 3 independent PODs of the (e x F) blocks (f32 torch-CPU SVDs in the reference)    engine.pod_per_row
+
+Basis type 'pca_blocks_with_St' and the geometric DEIM variant raise
 NotImplementedError here rather than fall back to the CPU.
 The plotting / polyscope methods of the reference (:865-1156) are out of scope (graphics: unavailable on this box).
 """
@@ -109,11 +111,12 @@ class constraintsComponents:  # Components == bases
             headerSing = ['component', 'singVal']
         if kind not in ("pod", "pod_vectorized", "pca_blocks", "pca_blocks_with_St"):
             raise ValueError("Uknown basis type: ", kind)
-        if kind not in ("pod_vectorized", "pca_blocks"):
+        if kind not in ("pod_vectorized", "pca_blocks", "pod"):
             raise NotImplementedError(f"constProj_basis_type '{kind}' is not built on the device yet (SURVEY 8(a) a10/a11); "
                                       "there is no CPU fallback")
-        compute = self.compute_pod_for_vectorized_nonlinear_snapshots_tensor if kind == "pod_vectorized" \
-            else self.compute_nonlinearity_bases_blocks
+        compute = {"pod_vectorized": self.compute_pod_for_vectorized_nonlinear_snapshots_tensor,
+                   "pod": self.compute_pod_for_nonlinear_snapshots_tensor,
+                   "pca_blocks": self.compute_nonlinearity_bases_blocks}[kind]
         _, comm = runtime.get()
         file_name = os.path.join(p.constProj_output_directory, p.name + "_" + p.constProj_name + self.file_name_sing)
         if self.storeSingVal and comm.rank == 0:
@@ -143,6 +146,17 @@ class constraintsComponents:  # Components == bases
             for r in table:
                 writer.writerow([int(r[0]), int(r[1])] + [float(v) for v in r[2:]])
         print("bases shape", (C.shape[0], snaps.shard.n_global, 3), "number of components", self.numComp)
+
+    @log_time("")
+    def compute_pod_for_nonlinear_snapshots_tensor(self, writer=None):
+        """`pod` (:274-294): p * 3 independent PODs of the (e x F) blocks (float32 torch-CPU SVDs in the reference)."""
+        ops, comm = runtime.get()
+        snaps = self.nonlinearSnapshots
+        C, sig = engine.pod_per_row(ops, comm, snaps.state.X, snaps.shard, snaps.constraintsSize,
+                                    int(self.param.deim_desired_num_components))
+        self.singular_values = sig
+        self._C, self._host = C, {}
+        self.numComp = C.shape[0]
 
     @log_time("")
     def compute_pod_for_vectorized_nonlinear_snapshots_tensor(self, writer=None):

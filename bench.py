@@ -190,6 +190,7 @@ def main():
         return engine.prepare_snapshots(ops, comm, src_dev, mass_loc, "first", sh)
 
     def build(st):
+        geo.reset()      # every build starts cold: support maps are memoised by source vertex WITHIN a build only
         C, W, meas, picked, _ = engine.deflate(ops, comm, st.X, sh, K, True, geo, block=args.block, keep_residual=False)
         engine.splocs(ops, comm, st.X, sh, C, W, K, geo, Is, Ia, 2.0, 10.0, log=None)
         return C, W, meas

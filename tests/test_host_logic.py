@@ -85,6 +85,10 @@ def test_bar_blocks_host_logic():
     assert pipeline_checks.check_bar_blocks(NumpyOps(), engine.Comm(enabled=False))
 
 
+def test_bar_pod_per_row_host_logic():
+    assert pipeline_checks.check_bar_pod_per_row(NumpyOps(), engine.Comm(enabled=False))
+
+
 def test_two_rank_gloo_row_sharding():
     """world_size 2 over gloo: sharded deflation + SPLOCS + POD + DEIM reproduce the single-process golden results."""
     env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29613", PYTHONPATH=ROOT + os.pathsep + os.path.join(ROOT, "tests"))
