@@ -3,107 +3,174 @@
 //   repeat iters times:   C = B0 + Hr (Z - U);   V = C + U;   Z = V * max(0, 1 - Lambda / (rho |V|_3));   U = V - Z
 //
 // The iteration couples the K components of ONE vertex only (Hr is K x K, the prox acts on the 3-vector of a (k, n)
-// pair), so a CTA owns a tile of 16 vertices (x 3 planes = 48 columns) for the whole inner loop: D = Z - U lives in
-// shared memory (the DMMA right operand), the K x 48 accumulators AND the dual U in registers, and Z, U travel
-// HBM <-> SM exactly once per outer step instead of once per ADMM iteration.  What is left per iteration is the
-// K x K x 48 DMMA product, whose left operand Hr (320 KB at K = 200, does not fit beside the tile) streams L2 -> shared
-// through a 3-stage cp.async ring (16-column slabs) that keeps running across iterations.  B0 and Lambda of the tile are
-// re-read in the epilogue (L2 hits: the 148 resident tiles hold 15 MB).  Persistent grid: one CTA per SM.
+// pair), so a CTA owns a tile of vertices (x 3 planes) for the whole inner loop: D = Z - U lives in shared memory (the
+// DMMA right operand), the K x columns accumulators in registers, and Z travels HBM <-> SM exactly once per outer step
+// instead of once per ADMM iteration.  What is left per iteration is the K x K x columns DMMA product, whose left operand
+// Hr (320 KB at K = 200, does not fit beside the tile) streams L2 -> shared through a 3-stage cp.async ring (8-column
+// slabs) that keeps running across iterations.  Persistent grid.
 //
-// Warp layout: 8 warps = 4 row-warps x 2 vertex groups, warp id = wm * 2 + wn.  The ceil(K/8) m-tiles are dealt to the
-// row-warps MT or MT-1 each (K = 200: 7,6,6,6 -> SM sub-partition loads 13,13,12,12); the body is compiled for both
-// counts and chosen by a warp-uniform branch (a predicated-off DMMA still occupies the tensor pipe).
+// Layouts of the same body (template AdmmCfg), chosen by ASB_ADMM_LAYOUT; measured on B200 at 1M x K = 200, 10 iterations
+// per launch (profiles/r01_admm_layouts.md), cuBLAS DGEMM peak 35.5 TFLOP/s:
+//   4    Pair    two CTAs per SM, 4 row-warps x 1 vertex group each (8 vertices, 24 columns), U in registers (254 regs),
+//                8-column slabs, 3 stages                                           100.2 ms  24.0 TFLOP/s   <- default
+//   416  Pair16  same, 16-column slabs (half the barriers), 2 stages                 109.4 ms
+//   12   Wide    one CTA per SM, 12 warps = 4 row-warps x 3 vertex groups (24 vertices, 72 columns); no room for U in
+//                registers (168 per thread): U goes through L2 every iteration       108.9 ms
+//   1216 Wide16  same, 16-column slabs                                               112.5 ms
+// ASB_ADMM_LOCK=1 adds a per-SM epilogue mutex to the Pair layouts (keeps the two CTAs of an SM half a phase apart so one
+// runs the FP64 prox while the other owns the tensor pipe): 103.5 ms (4) / 104.6 ms (416) -- the two global atomics per
+// iteration cost what the overlap wins, so it is off by default.
+//
+// Warp layout: warp id = wm * WN + wn.  The ceil(K/8) m-tiles are dealt to the 4 row-warps MT or MT-1 each (K = 200:
+// 7,6,6,6); the body is compiled for both counts and chosen by a warp-uniform branch (a predicated-off DMMA still
+// occupies the tensor pipe).  Hr must be zero-padded by the caller to ceil8(K) x ceil8(K): the slab stager and the k-loop
+// run without bounds tests (ncu r01 before: 0.66 ISETP and 0.4 LDC per DMMA in the inner loop).
 #include "dmma.cuh"
+#include <cstdlib>
+#ifndef ASB_ADMM_LAYOUT_DEFAULT
+#define ASB_ADMM_LAYOUT_DEFAULT 4
+#endif
 
 namespace asb {
 
-// Two small CTAs per SM (4 row-warps x 1 vertex group each) instead of one 8-warp CTA: the slab barriers, the FP64
-// prox epilogue and the tile load/store of one CTA overlap with the DMMA stream of the other (ncu on the 8-warp version:
-// 14 % of the warp samples sat behind BAR.SYNC, DMMA pipe 61 % active).
-constexpr int ADMM_WM = 4, ADMM_WN = 1, ADMM_THREADS = ADMM_WM * ADMM_WN * 32, ADMM_CTAS_PER_SM = 2;
-constexpr int ADMM_BK = 8;             // k-slab of Hr per pipeline stage
-constexpr int ADMM_ALD = ADMM_BK + 4;  // 12 doubles: conflict-free 8x4 A-fragment reads
-constexpr int ADMM_STAGES = 3;
-constexpr int ADMM_CPR = ADMM_BK / 2;              // 16-byte chunks per staged row
-constexpr int ADMM_RPP = ADMM_THREADS / ADMM_CPR;  // rows staged per pass
-constexpr int ADMM_NV = 8 * ADMM_WN;   // vertices per tile
-constexpr int ADMM_NC = 24 * ADMM_WN;  // columns per tile: [vertex group][plane][8 vertices]
-constexpr int ADMM_DLD = ADMM_NC + 4;  // 28 / 52: stride mod 16 in {12, 4} -> conflict-free 4x8 B-fragment reads
+constexpr int ADMM_WM = 4;
 
-template <int MT, int MTN>
+template <int WN_, bool UREG_, int CTAS_, int BK_, int STAGES_>
+struct AdmmCfg {
+    static constexpr int WN = WN_;                    // vertex groups (8 vertices each) per CTA
+    static constexpr bool UREG = UREG_;               // dual U in registers (else through L2 every iteration)
+    static constexpr int CTAS = CTAS_;                // CTAs per SM
+    static constexpr int BK = BK_;                    // k-slab of Hr per pipeline stage (one barrier per slab)
+    static constexpr int STAGES = STAGES_;            // cp.async ring depth
+    static constexpr int ALD = BK + 4;                // 12 / 20 doubles: conflict-free 8x4 A-fragment reads
+    static constexpr int CPR = BK / 2;                // 16-byte chunks per staged row
+    static constexpr int THREADS = ADMM_WM * WN * 32;
+    static constexpr int RPP = THREADS / CPR;         // Hr rows staged per pass of the CTA
+    static constexpr int NV = 8 * WN;                 // vertices per tile
+    static constexpr int NC = 24 * WN;                // columns per tile: [vertex group][plane][8 vertices]
+    static constexpr int DLD = NC + 4;                // 28 / 76: stride mod 16 == 12 -> conflict-free 4x8 B-fragment reads
+};
+using AdmmPair = AdmmCfg<1, true, 2, 8, 3>;      // 102 KB per CTA at K = 200
+using AdmmPair16 = AdmmCfg<1, true, 2, 16, 2>;   // 109 KB: half the barriers, one stage less
+using AdmmWide = AdmmCfg<3, false, 1, 8, 3>;     // 179 KB
+using AdmmWide16 = AdmmCfg<3, false, 1, 16, 3>;  // 218 KB
+
+// Epilogue mutex, one per SM (Pair layout).  Two identical co-resident CTAs that share the DMMA pipe fall into lock-step
+// (a CTA that is ahead runs its GEMM phase at half rate while the one behind catches up during the leader's epilogue:
+// the skew halves every iteration), so both sit in the FP64 prox epilogue at the same time and the DMMA pipe idles.
+// Letting only one CTA of an SM into the epilogue at a time keeps them half a phase apart.  Performance-only: the spin is
+// bounded, a CTA that gives up simply proceeds; the host clears the array before every launch.
+__device__ int g_admm_epilogue_lock[1024];
+
+__device__ __forceinline__ unsigned smid() {
+    unsigned r;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ bool epilogue_lock_acquire(int* lock) {
+    for (int spin = 0; spin < (1 << 14); ++spin) {
+        if (atomicCAS(lock, 0, 1) == 0) return true;
+        __nanosleep(64);
+    }
+    return false;
+}
+
+// shrink = max(0, 1 - (lambda / rho) / |v|): NaN where lambda = 0 and v = 0 (0 * inf), like the reference's 0/0
+// (np.maximum propagates it, posComponents.py:253-256); 0 where v = 0 and lambda > 0 (1 - inf).
+__device__ __forceinline__ double prox_shrink(double vx, double vy, double vz, double lam, double inv_rho) {
+    const double s2 = __dadd_rn(__dadd_rn(__dmul_rn(vx, vx), __dmul_rn(vy, vy)), __dmul_rn(vz, vz));
+    const double t = 1.0 - __dmul_rn(__dmul_rn(inv_rho, lam), rsqrt(s2));
+    return (t != t) ? t : fmax(0.0, t);
+}
+
+template <class Cfg, int MT, int MTN>
 __device__ __forceinline__ void admm_body(double* smem, const double* __restrict__ Hr, int64_t ldh,
                                           const double* __restrict__ B0, double* __restrict__ Z, double* __restrict__ U,
                                           const double* __restrict__ Lambda, int K, int64_t N, int64_t ld, double inv_rho,
-                                          int iters, int64_t ntiles, int mt0, bool live) {
-    const int rows8 = (K + 7) & ~7;   // rows held in shared memory (rows >= K are zero)
-    double* Ds = smem;                                  // [rows8][ADMM_DLD]  Z - U
-    double* As = Ds + (size_t)rows8 * ADMM_DLD;         // ADMM_STAGES x [rows8][ADMM_ALD]
+                                          int iters, int64_t ntiles, int mt0, bool live, int* lock) {
+    constexpr int WN = Cfg::WN, DLD = Cfg::DLD, RPP = Cfg::RPP;
+    constexpr int ADMM_BK = Cfg::BK, ADMM_ALD = Cfg::ALD, ADMM_STAGES = Cfg::STAGES, ADMM_CPR = Cfg::CPR;
+    constexpr bool UREG = Cfg::UREG;
+    constexpr int UR = UREG ? MTN : 1;   // register copy of U only in the Pair layout
+    const int rows8 = (K + 7) & ~7;      // rows held in shared memory (rows >= K are zero)
+    const int rowsk = (K + ADMM_BK - 1) / ADMM_BK * ADMM_BK;   // contraction length: whole slabs (Hr is padded to it)
+    bool held = false;                   // thread 0: this CTA owns the SM's epilogue mutex
+    double* Ds = smem;                                  // [rowsk][DLD]  Z - U (rows >= K zero)
+    double* As = Ds + (size_t)rowsk * DLD;              // ADMM_STAGES x [rows8][ADMM_ALD]
     const int astage = rows8 * ADMM_ALD;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, lr = lane >> 2, lc = lane & 3;
-    const int wn = warp % ADMM_WN;
+    const int wn = warp % WN;
     const int64_t C3 = 3 * ld;
-    const int nslab = (K + ADMM_BK - 1) / ADMM_BK;
+    const int nslab = rowsk / ADMM_BK;
     const int total = iters * nslab;
 
-    // Hr slab stager: chunk t of a thread = row tid / CPR + RPP t, doubles (tid % CPR) * 2 .. +1 of the slab
-    constexpr int NCH = (32 * MT + ADMM_RPP - 1) / ADMM_RPP;
+    // Hr slab stager: chunk t of a thread = row tid / CPR + RPP t, doubles (tid % CPR) * 2 .. +1 of the slab.  Hr is padded
+    // by the caller (zeros) to whole slabs, so no chunk needs a column test, and the NFULL passes that end below
+    // 32 (MT - 1) < rows8 need no row test either; the remaining one or two passes use a mask computed once.
+    constexpr int NCH = (32 * MT + RPP - 1) / RPP;
+    constexpr int NFULL = (32 * (MT - 1)) / RPP;
+    static_assert(NCH - NFULL <= 4, "tail passes");
     const int srow = threadIdx.x / ADMM_CPR, scc = (threadIdx.x % ADMM_CPR) * 2;
-    unsigned okmask = 0;
+    unsigned tailmask = 0;
 #pragma unroll
-    for (int t = 0; t < NCH; ++t)
-        if (srow + ADMM_RPP * t < K) okmask |= 1u << t;
-    const double* hp = Hr + (int64_t)min(srow, K - 1) * ldh + scc;
-    const int64_t hstep = ADMM_RPP * ldh;
+    for (int t = NFULL; t < NCH; ++t)
+        if (srow + RPP * t < rows8) tailmask |= 1u << (t - NFULL);
+    const double* hp = Hr + (int64_t)min(srow, rows8 - 1) * ldh + scc;
+    const int64_t hstep = RPP * ldh;
     const unsigned sdst = srow * ADMM_ALD + scc;
-    auto load_a = [&](int stage, int slab) {  // Hr[:, BK slab : BK slab + BK] -> As[stage]; rows / columns >= K zero-filled
-        const int k0 = slab * ADMM_BK;
-        const bool kin = k0 + scc < K;
-        const double* q = hp + k0;
+    auto load_a = [&](int stage, int slab, bool valid) {  // Hr[:, BK slab : BK slab + BK] -> As[stage] (zero-fill if !valid)
+        const double* q = hp + slab * ADMM_BK;
         double* dst = As + stage * astage + sdst;
+        const int nbytes = valid ? 16 : 0;
 #pragma unroll
-        for (int t = 0; t < NCH; ++t) {
-            if (srow + ADMM_RPP * t < rows8) {
-                const bool ok = kin && ((okmask >> t) & 1u);
-                cp_async16(dst + t * ADMM_RPP * ADMM_ALD, ok ? q : Hr, ok ? 16 : 0);
-            }
+        for (int t = 0; t < NFULL; ++t) {
+            cp_async16(dst + t * RPP * ADMM_ALD, q, nbytes);
+            q += hstep;
+        }
+#pragma unroll
+        for (int t = NFULL; t < NCH; ++t) {
+            if ((tailmask >> (t - NFULL)) & 1u) cp_async16(dst + t * RPP * ADMM_ALD, q, nbytes);
             q += hstep;
         }
     };
+    // D rows [rows8, rowsk) (BK = 16, K % 16 in 1..8) are never written by a tile load or an epilogue: zero them once
+    for (int e = rows8 * DLD + threadIdx.x; e < rowsk * DLD; e += Cfg::THREADS) Ds[e] = 0.0;
     const double* afrag = As + (mt0 * 8 + lr) * ADMM_ALD + lc;
-    const double* bfrag = Ds + lc * ADMM_DLD + wn * 24 + lr;
-    double* down = Ds + wn * 24 + 2 * lc;   // + k * ADMM_DLD + d * 8: the thread's own entries of D
+    const double* bfrag = Ds + lc * DLD + wn * 24 + lr;
+    double* down = Ds + wn * 24 + 2 * lc;   // + k * DLD + d * 8: the thread's own entries of D
 
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int64_t n = tile * ADMM_NV + wn * 8 + 2 * lc;   // the thread's two vertices
+        const int64_t n = tile * Cfg::NV + wn * 8 + 2 * lc;   // the thread's two vertices
         const bool ok0 = n < N, ok1 = n + 1 < N;
+        const bool inb = live && n < ld;   // Wide: 24 does not divide ld, the last tile hangs over the padded plane
         // ---- Hr ring prologue (overlaps the tile load below)
         int gl = 0, ls = 0, lslab = 0;   // slabs issued, load stage, slab index of the next load
 #pragma unroll
         for (int s = 0; s < ADMM_STAGES - 1; ++s) {
-            if (gl < total) {
-                load_a(ls, lslab);
-                ++gl;
-                ls = ls + 1 == ADMM_STAGES ? 0 : ls + 1;
-                lslab = lslab + 1 == nslab ? 0 : lslab + 1;
-            }
+            load_a(ls, lslab, gl < total);
+            ++gl;
+            ls = ls + 1 == ADMM_STAGES ? 0 : ls + 1;
+            lslab = lslab + 1 == nslab ? 0 : lslab + 1;
             cp_async_commit();
         }
-        // ---- tile load: every thread fetches its own (k, 2 vertices, xyz) entries; U stays in registers
-        double u[MTN][3][2];
+        // ---- tile load: every thread fetches its own (k, 2 vertices, xyz) entries of Z and U
+        double u[UR][3][2];
 #pragma unroll
         for (int i = 0; i < MTN; ++i) {
             const int k = (mt0 + i) * 8 + lr;
 #pragma unroll
             for (int d = 0; d < 3; ++d) {
                 double2 z = make_double2(0.0, 0.0), uu = z;
-                if (live && k < K) {
+                if (inb && k < K) {
                     const int64_t off = (int64_t)k * C3 + (int64_t)d * ld + n;
                     z = ld2(Z + off);
                     uu = ld2(U + off);
                 }
-                u[i][d][0] = uu.x;
-                u[i][d][1] = uu.y;
-                if (live && k < rows8) st2(down + k * ADMM_DLD + d * 8, make_double2(z.x - uu.x, z.y - uu.y));
+                if (UREG) {
+                    u[i % UR][d][0] = uu.x;
+                    u[i % UR][d][1] = uu.y;
+                }
+                if (live && k < rows8) st2(down + k * DLD + d * 8, make_double2(z.x - uu.x, z.y - uu.y));   // k >= K: zeros
             }
         }
 
@@ -117,7 +184,7 @@ __device__ __forceinline__ void admm_body(double* smem, const double* __restrict
 #pragma unroll
                 for (int d = 0; d < 3; ++d) {
                     double2 b0 = make_double2(0.0, 0.0);
-                    if (live && k < K) b0 = ld2(B0 + (int64_t)k * C3 + (int64_t)d * ld + n);
+                    if (inb && k < K) b0 = ld2(B0 + (int64_t)k * C3 + (int64_t)d * ld + n);
                     acc[i][d][0] = b0.x;
                     acc[i][d][1] = b0.y;
                 }
@@ -126,82 +193,90 @@ __device__ __forceinline__ void admm_body(double* smem, const double* __restrict
             for (int s = 0; s < nslab; ++s) {
                 cp_async_wait<ADMM_STAGES - 2>();
                 __syncthreads();  // slab landed; previous stage free; D writes of the previous epilogue / tile load visible
-                if (gl < total) {
-                    load_a(ls, lslab);
-                    ++gl;
-                    ls = ls + 1 == ADMM_STAGES ? 0 : ls + 1;
-                    lslab = lslab + 1 == nslab ? 0 : lslab + 1;
-                }
+                load_a(ls, lslab, gl < total);   // past the end: a zero-fill of a stage nobody reads (no branch in the loop)
+                ++gl;
+                ls = ls + 1 == ADMM_STAGES ? 0 : ls + 1;
+                lslab = lslab + 1 == nslab ? 0 : lslab + 1;
                 cp_async_commit();
                 const double* as = afrag + cs * astage;
-                const double* ds = bfrag + s * ADMM_BK * ADMM_DLD;
+                const double* ds = bfrag + s * ADMM_BK * DLD;
                 cs = cs + 1 == ADMM_STAGES ? 0 : cs + 1;
 #pragma unroll
-                for (int kk = 0; kk < ADMM_BK / 4; ++kk) {
-                    if (s * ADMM_BK + kk * 4 < rows8) {   // the last slab of K = 200 has 8 live columns
-                        double b[3];
+                for (int kk = 0; kk < ADMM_BK / 4; ++kk) {   // whole slabs: Hr columns and D rows >= K are zero
+                    double b[3];
 #pragma unroll
-                        for (int d = 0; d < 3; ++d) b[d] = ds[kk * 4 * ADMM_DLD + d * 8];
+                    for (int d = 0; d < 3; ++d) b[d] = ds[kk * 4 * DLD + d * 8];
 #pragma unroll
-                        for (int i = 0; i < MTN; ++i) {
-                            const double a = as[i * 8 * ADMM_ALD + kk * 4];
+                    for (int i = 0; i < MTN; ++i) {
+                        const double a = as[i * 8 * ADMM_ALD + kk * 4];
 #pragma unroll
-                            for (int d = 0; d < 3; ++d) dmma(acc[i][d][0], acc[i][d][1], a, b[d]);
-                        }
+                        for (int d = 0; d < 3; ++d) dmma(acc[i][d][0], acc[i][d][1], a, b[d]);
                     }
                 }
             }
-            __syncthreads();  // every warp has finished reading D for this iteration
+            if (lock && threadIdx.x == 0) held = epilogue_lock_acquire(lock);
+            __syncthreads();  // every warp has finished reading D for this iteration (and the epilogue mutex is ours)
 
-            // ---- epilogue: prox + dual update on the thread's own entries
+            // ---- epilogue: prox + dual update on the thread's own entries.  Lambda of all m-tiles is fetched up front (one L2
+            // latency); in the Wide layout the old dual U (L2 hits: written by this thread one iteration ago) runs UDEPTH
+            // m-tiles ahead of the arithmetic.
             const bool last = it == iters - 1;
             double2 lam[MTN];
 #pragma unroll
             for (int i = 0; i < MTN; ++i) {
                 const int k = (mt0 + i) * 8 + lr;
-                lam[i] = (live && k < K) ? ld2(Lambda + (int64_t)k * ld + n) : make_double2(0.0, 0.0);
+                lam[i] = (inb && k < K) ? ld2(Lambda + (int64_t)k * ld + n) : make_double2(0.0, 0.0);
+            }
+            constexpr int UDEPTH = UREG ? 1 : (MTN < 3 ? MTN : 3);
+            double2 uo[UDEPTH][3];
+            auto fetch_u = [&](int i) {
+                const int k = (mt0 + i) * 8 + lr;
+                if (!inb || k >= K) return;
+                const int64_t base = (int64_t)k * C3 + n;
+#pragma unroll
+                for (int d = 0; d < 3; ++d) uo[i % UDEPTH][d] = ld2(U + base + (int64_t)d * ld);
+            };
+            if (!UREG) {
+#pragma unroll
+                for (int i = 0; i < UDEPTH; ++i) fetch_u(i);
             }
 #pragma unroll
             for (int i = 0; i < MTN; ++i) {
                 const int k = (mt0 + i) * 8 + lr;
-                if (!live || k >= K) continue;
+                const bool on = inb && k < K;
                 const int64_t base = (int64_t)k * C3 + n;
                 double2 v[3];
 #pragma unroll
-                for (int d = 0; d < 3; ++d) {
-                    v[d].x = acc[i][d][0] + u[i][d][0];  // V = C + U
-                    v[d].y = acc[i][d][1] + u[i][d][1];
+                for (int d = 0; d < 3; ++d) {   // V = C + U
+                    v[d].x = acc[i][d][0] + (UREG ? u[i % UR][d][0] : uo[i % UDEPTH][d].x);
+                    v[d].y = acc[i][d][1] + (UREG ? u[i % UR][d][1] : uo[i % UDEPTH][d].y);
                 }
-                // shrink = max(0, 1 - (lambda / rho) / |v|): NaN where lambda = 0 and v = 0 (0 * inf), like the reference's 0/0
-                // (np.maximum propagates it, posComponents.py:253-256); 0 where v = 0 and lambda > 0 (1 - inf).
-                double sh[2];
-                {
-                    const double s2 = __dadd_rn(__dadd_rn(__dmul_rn(v[0].x, v[0].x), __dmul_rn(v[1].x, v[1].x)),
-                                                __dmul_rn(v[2].x, v[2].x));
-                    const double t = 1.0 - __dmul_rn(__dmul_rn(inv_rho, lam[i].x), rsqrt(s2));
-                    sh[0] = (t != t) ? t : fmax(0.0, t);
-                }
-                {
-                    const double s2 = __dadd_rn(__dadd_rn(__dmul_rn(v[0].y, v[0].y), __dmul_rn(v[1].y, v[1].y)),
-                                                __dmul_rn(v[2].y, v[2].y));
-                    const double t = 1.0 - __dmul_rn(__dmul_rn(inv_rho, lam[i].y), rsqrt(s2));
-                    sh[1] = (t != t) ? t : fmax(0.0, t);
-                }
+                if (!UREG && i + UDEPTH < MTN) fetch_u(i + UDEPTH);   // slot i % UDEPTH is free again
+                if (on) {
+                    const double sh0 = prox_shrink(v[0].x, v[1].x, v[2].x, lam[i].x, inv_rho);
+                    const double sh1 = prox_shrink(v[0].y, v[1].y, v[2].y, lam[i].y, inv_rho);
 #pragma unroll
-                for (int d = 0; d < 3; ++d) {
-                    double2 z, u2;
-                    z.x = ok0 ? v[d].x * sh[0] : 0.0;
-                    z.y = ok1 ? v[d].y * sh[1] : 0.0;
-                    u2.x = ok0 ? v[d].x - z.x : 0.0;
-                    u2.y = ok1 ? v[d].y - z.y : 0.0;
-                    u[i][d][0] = u2.x;
-                    u[i][d][1] = u2.y;
-                    if (last) {
-                        st2(Z + base + (int64_t)d * ld, z);
-                        st2(U + base + (int64_t)d * ld, u2);
-                    } else {
-                        st2(down + k * ADMM_DLD + d * 8, make_double2(z.x - u2.x, z.y - u2.y));
+                    for (int d = 0; d < 3; ++d) {
+                        double2 z, u2;
+                        z.x = ok0 ? v[d].x * sh0 : 0.0;
+                        z.y = ok1 ? v[d].y * sh1 : 0.0;
+                        u2.x = ok0 ? v[d].x - z.x : 0.0;
+                        u2.y = ok1 ? v[d].y - z.y : 0.0;
+                        if (UREG) {
+                            u[i % UR][d][0] = u2.x;
+                            u[i % UR][d][1] = u2.y;
+                        }
+                        if (!UREG || last) st2(U + base + (int64_t)d * ld, u2);
+                        if (last) st2(Z + base + (int64_t)d * ld, z);
+                        else st2(down + k * DLD + d * 8, make_double2(z.x - u2.x, z.y - u2.y));
                     }
+                }
+            }
+            if (lock) {
+                __syncthreads();  // all warps are through the epilogue
+                if (threadIdx.x == 0 && held) {
+                    atomicExch(lock, 0);
+                    held = false;
                 }
             }
         }
@@ -210,35 +285,70 @@ __device__ __forceinline__ void admm_body(double* smem, const double* __restrict
     }
 }
 
-template <int MT>
-__global__ void __launch_bounds__(ADMM_THREADS, ADMM_CTAS_PER_SM)
+template <class Cfg, int MT>
+__global__ void __launch_bounds__(Cfg::THREADS, Cfg::CTAS)
 admm_solve_kernel(const double* __restrict__ Hr, int64_t ldh, const double* __restrict__ B0, double* __restrict__ Z,
                   double* __restrict__ U, const double* __restrict__ Lambda, int K, int64_t N, int64_t ld,
-                  double inv_rho, int iters, int64_t ntiles) {
+                  double inv_rho, int iters, int64_t ntiles, int use_lock) {
     extern __shared__ __align__(16) double smem[];
+    int* lock = (use_lock && Cfg::CTAS > 1) ? g_admm_epilogue_lock + (smid() & 1023) : nullptr;
     int mt0, mtn;
-    // co-resident CTAs (blockIdx.x and blockIdx.x + #SMs under round-robin placement) rotate the row-warp roles by two
-    // sub-partitions, so the 7-tile warps of the two CTAs sit on different SM sub-partitions (13,12,13,12 instead of 14,12,12,12)
-    const int slot = (blockIdx.x / max(1u, gridDim.x / ADMM_CTAS_PER_SM)) & 1;
-    const int wm = (((threadIdx.x >> 5) / ADMM_WN) + 2 * slot) % ADMM_WM;
+    int wm = (threadIdx.x >> 5) / Cfg::WN;
+    if (Cfg::CTAS == 2) {
+        // co-resident CTAs (blockIdx.x and blockIdx.x + #SMs under round-robin placement) rotate the row-warp roles by two
+        // sub-partitions, so the 7-tile warps of the two CTAs sit on different SM sub-partitions (13,12,13,12, not 14,12,12,12)
+        const int slot = (blockIdx.x / max(1u, gridDim.x / 2)) & 1;
+        wm = (wm + 2 * slot) % ADMM_WM;
+    }
     mtile_range(((K + 7) & ~7) >> 3, ADMM_WM, wm, mt0, mtn);
     const bool live = mtn > 0;   // K <= 24: some row-warps own no m-tile; they idle on tile 0 and never store
     if (!live) mt0 = 0;
-    if (mtn == MT) admm_body<MT, MT>(smem, Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live);
-    else admm_body<MT, (MT > 1 ? MT - 1 : 1)>(smem, Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live);
+    if (mtn == MT) admm_body<Cfg, MT, MT>(smem, Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live, lock);
+    else admm_body<Cfg, MT, (MT > 1 ? MT - 1 : 1)>(smem, Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live,
+                                                  lock);
+}
+
+template <class Cfg>
+static size_t admm_smem_bytes(int64_t K) {
+    const int64_t rows8 = (K + 7) & ~7LL, rowsk = cdiv(K, Cfg::BK) * Cfg::BK;
+    return ((size_t)rowsk * Cfg::DLD + (size_t)rows8 * Cfg::STAGES * Cfg::ALD) * sizeof(double);
+}
+
+static int env_int(const char* name, int dflt) {
+    const char* e = std::getenv(name);
+    return e ? std::atoi(e) : dflt;
+}
+
+template <class Cfg, int MT>
+static int launch_admm_cfg(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda,
+                           int64_t K, int64_t N, int64_t ld, double inv_rho, int iters, cudaStream_t st) {
+    const size_t smem = admm_smem_bytes<Cfg>(K);
+    ASB_CUDA(cudaFuncSetAttribute(admm_solve_kernel<Cfg, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t ntiles = cdiv(ld, Cfg::NV);
+    const unsigned grid = (unsigned)std::min<int64_t>(ntiles, (int64_t)Cfg::CTAS * sm_count());
+    static const int use_lock = env_int("ASB_ADMM_LOCK", 0);
+    if (use_lock && Cfg::CTAS > 1) {   // a previous launch that died mid-kernel must not leave a mutex taken
+        void* lk = nullptr;
+        ASB_CUDA(cudaGetSymbolAddress(&lk, g_admm_epilogue_lock));
+        ASB_CUDA(cudaMemsetAsync(lk, 0, sizeof(int) * 1024, st));
+    }
+    admm_solve_kernel<Cfg, MT><<<grid, Cfg::THREADS, smem, st>>>(Hr, ldh, B0, Z, U, Lambda, (int)K, N, ld, inv_rho, iters, ntiles,
+                                                                use_lock);
+    ASB_LAUNCH_CHECK();
+    return ASB_OK;
 }
 
 template <int MT>
 static int launch_admm(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda,
                        int64_t K, int64_t N, int64_t ld, double inv_rho, int iters, cudaStream_t st) {
-    const int rows8 = (int)((K + 7) & ~7LL);
-    const size_t smem = (size_t)rows8 * (ADMM_DLD + ADMM_STAGES * ADMM_ALD) * sizeof(double);
-    ASB_CUDA(cudaFuncSetAttribute(admm_solve_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int64_t ntiles = ld / ADMM_NV;
-    const unsigned grid = (unsigned)std::min<int64_t>(ntiles, (int64_t)ADMM_CTAS_PER_SM * sm_count());
-    admm_solve_kernel<MT><<<grid, ADMM_THREADS, smem, st>>>(Hr, ldh, B0, Z, U, Lambda, (int)K, N, ld, inv_rho, iters, ntiles);
-    ASB_LAUNCH_CHECK();
-    return ASB_OK;
+    static const int layout = env_int("ASB_ADMM_LAYOUT", ASB_ADMM_LAYOUT_DEFAULT);   // 12 / 1216: Wide, 4 / 416: Pair
+    constexpr size_t SMEM_MAX = 227 * 1024;   // a layout whose tile does not fit at this K falls through to Pair (139 KB at K = 256)
+    if (layout == 12 && admm_smem_bytes<AdmmWide>(K) <= SMEM_MAX)
+        return launch_admm_cfg<AdmmWide, MT>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+    if (layout == 1216 && admm_smem_bytes<AdmmWide16>(K) <= SMEM_MAX)
+        return launch_admm_cfg<AdmmWide16, MT>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+    if (layout == 416) return launch_admm_cfg<AdmmPair16, MT>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+    return launch_admm_cfg<AdmmPair, MT>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
 }
 
 }  // namespace asb
@@ -252,6 +362,7 @@ int asb_admm_solve(const double* Hr, int64_t ldh, const double* B0, double* Z, d
     ASB_REQUIRE(Hr && B0 && Z && U && Lambda && K > 0 && K <= 256 && N > 0 && ld >= N && ld % 32 == 0,
                 "admm_solve: bad arguments (K <= 256)");
     ASB_REQUIRE(ldh % 2 == 0 && ((uintptr_t)Hr % 16 == 0), "admm_solve: Hr must be 16-byte aligned with even ldh");
+    ASB_REQUIRE(ldh >= ((K + 15) & ~15LL), "admm_solve: Hr must be zero-padded to ceil8(K) rows x ceil16(K) columns");
     ASB_REQUIRE(iters >= 0 && iters < (1 << 20), "admm_solve: bad iteration count");
     if (iters == 0) return ASB_OK;
     const cudaStream_t st = S(stream);

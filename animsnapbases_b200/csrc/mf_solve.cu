@@ -6,12 +6,14 @@
 //                               y[own] = Mt[:n1] f1 ;  upd_t = f2 + Mt[row2:] f1
 //   backward (root -> leaves):  x[own] = Mt^T [ y[own] ; x[bnd] ]
 // HBM-bound: each launch streams the operators of one level once per right-hand side; all reductions are fixed-order.
-#include "common.cuh"
+#include "dmma.cuh"
+#include <cstdlib>
 
 namespace asb {
 
 constexpr int MF_ROWS = 32;      // rows (forward) / columns (backward) of Mt per CTA; mfsolve.ROWS_PER_BLOCK
 constexpr int MF_CHUNK = 1024;   // staged vector chunk (doubles)
+constexpr int MF_MRHS_MIN = 3;   // from this many right-hand sides on, the register-blocked multi-RHS kernels run
 
 struct FrontDesc {
     long long own_start, n1, n2, mt_off, slot_off, upd_off, ldm, row2;
@@ -127,6 +129,254 @@ __global__ void __launch_bounds__(256) mf_backward_kernel(const FrontDesc* __res
     }
 }
 
+// ------------------------------------------------------------------------------------------ batched right-hand sides
+// A SPLOCS iteration asks for the distance fields of all new component centres at once (tens of right-hand sides).
+// The single-RHS kernels above re-stream the 0.94 GB operator once per right-hand side (measured: 4 514 solves = 17 TB,
+// 4.9 s of a 21 s build).  These variants keep MF_NB right-hand sides in registers per CTA, so a level's operators are
+// read once per group of MF_NB and the pass becomes FP64-FMA bound (2 n1 (n1 + n2) flops per front and RHS).
+constexpr int MF_NB = 8;          // right-hand sides per CTA; 4 rows x 8 RHS = 32 accumulators = one per lane after the reduce
+constexpr int MF_FCHUNK = 512;    // forward: staged columns per RHS (8 x 512 doubles = 32 KB)
+constexpr int MF_BCHUNK = 256;    // backward: staged rows (256 x 8 doubles = 16 KB)
+
+// v[0..31] per lane -> lane l returns sum over the warp of v[l]  (31 shuffles instead of 32 x 5; fixed order)
+__device__ __forceinline__ double warp_transpose_sum32(double (&v)[32], int lane) {
+#pragma unroll
+    for (int h = 16; h >= 1; h >>= 1) {
+        const bool upper = (lane & h) != 0;
+#pragma unroll
+        for (int i = 0; i < h; ++i) {
+            const double send = upper ? v[i] : v[i + h];
+            const double keep = upper ? v[i + h] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, h);
+        }
+    }
+    return v[0];
+}
+
+// grid.x = work item (front, first row), grid.y = group of MF_NB right-hand sides.  256 threads = 8 warps x 4 rows.
+__global__ void __launch_bounds__(256) mf_forward_mrhs_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
+                                                             const int32_t* __restrict__ src, int64_t slots,
+                                                             const int32_t* __restrict__ work, const double* __restrict__ rhs,
+                                                             double* __restrict__ y, double* __restrict__ upd, int64_t ldx,
+                                                             int64_t ldu, int nrhs) {
+    __shared__ double fs[MF_NB][MF_FCHUNK];
+    const FrontDesc d = desc[work[2 * blockIdx.x]];
+    const int r0 = work[2 * blockIdx.x + 1];
+    const int64_t b0 = (int64_t)blockIdx.y * MF_NB;
+    const int nb = min(MF_NB, nrhs - (int)b0);
+    const double* rb = rhs + b0 * ldx + d.own_start;
+    double* ub = upd + b0 * ldu;
+    const int32_t* src0 = src + d.slot_off;
+    const int32_t* src1 = src + slots + d.slot_off;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n1 = (int)d.n1, n = (int)(d.n1 + d.n2);
+    double acc[32];
+#pragma unroll
+    for (int q = 0; q < 32; ++q) acc[q] = 0.0;
+    const double* rowp[4];
+    int jmax[4], jall = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int r = r0 + warp * 4 + i;
+        const long long srow = r < n1 ? r : d.row2 + (r - n1);
+        rowp[i] = vals + d.mt_off + (r < n ? srow : 0) * d.ldm;
+        jmax[i] = r >= n ? 0 : (r < n1 ? r + 1 : n1);   // L11^-1 is lower triangular
+        jall = max(jall, jmax[i]);
+    }
+    const int cmax = (r0 + MF_ROWS <= n1) ? r0 + MF_ROWS : n1;
+    for (int c0 = 0; c0 < cmax; c0 += MF_FCHUNK) {
+        const int len = min(MF_FCHUNK, cmax - c0);
+        __syncthreads();
+        for (int j = threadIdx.x; j < len; j += blockDim.x) {
+            const int s0 = src0[c0 + j], s1 = src1[c0 + j];
+#pragma unroll
+            for (int b = 0; b < MF_NB; ++b) {
+                double f = 0.0;
+                if (b < nb) {
+                    f = rb[b * ldx + c0 + j];
+                    double g = 0.0;                      // same order as gather_children: (0 + u0) + u1, then rhs + that
+                    if (s0 >= 0) g += ub[b * ldu + s0];
+                    if (s1 >= 0) g += ub[b * ldu + s1];
+                    f += g;
+                }
+                fs[b][j] = f;
+            }
+        }
+        __syncthreads();
+        const int je = min(len, jall - c0);
+        for (int j = lane; j < je; j += 32) {
+            double a[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) a[i] = (c0 + j < jmax[i]) ? rowp[i][c0 + j] : 0.0;
+#pragma unroll
+            for (int b = 0; b < MF_NB; ++b) {
+                const double f = fs[b][j];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[i * MF_NB + b] = fma(a[i], f, acc[i * MF_NB + b]);
+            }
+        }
+    }
+    const double s = warp_transpose_sum32(acc, lane);   // lane = i * MF_NB + b
+    const int i = lane / MF_NB, b = lane % MF_NB;
+    const int r = r0 + warp * 4 + i;
+    if (r < n && b < nb) {
+        if (r < n1)
+            y[(b0 + b) * ldx + d.own_start + r] = s;
+        else
+            ub[b * ldu + d.upd_off + (r - n1)] = gather_children(src0, src1, ub + b * ldu, r) + s;
+    }
+}
+
+// DMMA variant of the batched forward pass: Y (rows x 8 RHS) = Mt (rows x columns) F (columns x 8 RHS) per front on the
+// FP64 tensor pipe.  The FMA kernel above spends ~85 % of its instructions outside the FMAs on the leaf fronts (n1 <= 64:
+// two column steps per lane, then a 32-value transpose-reduce); here a warp owns 8 rows, reads its A fragments straight
+// from global memory (lane (lr, lc) -> Mt[row lr][k + lc]: four 8-byte lanes fill one 32-byte sector) and needs no
+// cross-lane reduction: D[row lr][rhs 2lc, 2lc+1] is the result.  grid.x = work item (front, first of 32 rows),
+// grid.y = group of 8 right-hand sides; 128 threads = 4 warps x 8 rows.
+constexpr int MF_DLD = MF_FCHUNK + 4;   // fs row stride: == 4 mod 16 -> conflict-free B fragments (lane -> fs[lr][k + lc])
+static_assert(MF_FCHUNK % 8 == 0, "chunks are consumed two k-steps at a time");
+
+__global__ void __launch_bounds__(128) mf_forward_dmma_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
+                                                             const int32_t* __restrict__ src, int64_t slots,
+                                                             const int32_t* __restrict__ work, const double* __restrict__ rhs,
+                                                             double* __restrict__ y, double* __restrict__ upd, int64_t ldx,
+                                                             int64_t ldu, int nrhs) {
+    __shared__ double fs[MF_NB][MF_DLD];
+    const FrontDesc d = desc[work[2 * blockIdx.x]];
+    const int r0 = work[2 * blockIdx.x + 1];
+    const int64_t b0 = (int64_t)blockIdx.y * MF_NB;
+    const int nb = min(MF_NB, nrhs - (int)b0);
+    const double* rb = rhs + b0 * ldx + d.own_start;
+    double* ub = upd + b0 * ldu;
+    const int32_t* src0 = src + d.slot_off;
+    const int32_t* src1 = src + slots + d.slot_off;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, lr = lane >> 2, lc = lane & 3;
+    const int n1 = (int)d.n1, n = (int)(d.n1 + d.n2);
+    // the lane's row of the A fragment
+    const int ra = r0 + warp * 8 + lr;
+    const long long sra = ra < n1 ? ra : d.row2 + (ra - n1);
+    const double* arow = vals + d.mt_off + (ra < n ? sra : 0) * d.ldm;
+    const int jmax_a = ra >= n ? 0 : (ra < n1 ? ra + 1 : n1);          // L11^-1 is lower triangular
+    // columns this warp needs: its last live row decides (warp-uniform)
+    const int rl = min(r0 + warp * 8 + 7, n - 1);
+    const int jmax_w = r0 + warp * 8 >= n ? 0 : (rl < n1 ? rl + 1 : n1);
+    const int cmax = (r0 + MF_ROWS <= n1) ? r0 + MF_ROWS : n1;          // columns the CTA stages
+    double acc0 = 0.0, acc1 = 0.0, odd0 = 0.0, odd1 = 0.0;   // two independent DMMA chains (even / odd k-steps)
+    for (int c0 = 0; c0 < cmax; c0 += MF_FCHUNK) {
+        const int len = min(MF_FCHUNK, cmax - c0);
+        const int len4 = (len + 7) & ~7;
+        __syncthreads();
+        for (int j = threadIdx.x; j < len4; j += blockDim.x) {
+            int s0 = -1, s1 = -1;
+            if (j < len) {
+                s0 = src0[c0 + j];
+                s1 = src1[c0 + j];
+            }
+#pragma unroll
+            for (int b = 0; b < MF_NB; ++b) {
+                double f = 0.0;
+                if (b < nb && j < len) {
+                    f = rb[b * ldx + c0 + j];
+                    double g = 0.0;
+                    if (s0 >= 0) g += ub[b * ldu + s0];
+                    if (s1 >= 0) g += ub[b * ldu + s1];
+                    f += g;
+                }
+                fs[b][j] = f;
+            }
+        }
+        __syncthreads();
+        const int ke = min(len4, ((jmax_w - c0) + 7) & ~7);
+        const double* bp = &fs[lr][lc];
+        for (int k0 = 0; k0 < ke; k0 += 8) {
+            const int col = c0 + k0 + lc;
+            const double a0 = col < jmax_a ? arow[col] : 0.0;
+            const double a1 = col + 4 < jmax_a ? arow[col + 4] : 0.0;
+            dmma(acc0, acc1, a0, bp[k0]);
+            dmma(odd0, odd1, a1, bp[k0 + 4]);
+        }
+    }
+    acc0 += odd0;
+    acc1 += odd1;
+    // D fragment: row lr of the warp's 8 rows, right-hand sides 2 lc and 2 lc + 1
+    const int r = r0 + warp * 8 + lr;
+    if (r < n) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int b = 2 * lc + h;
+            if (b >= nb) continue;
+            const double s = h ? acc1 : acc0;
+            if (r < n1)
+                y[(b0 + b) * ldx + d.own_start + r] = s;
+            else
+                ub[b * ldu + d.upd_off + (r - n1)] = gather_children(src0, src1, ub + b * ldu, r) + s;
+        }
+    }
+}
+
+// grid.x = work item (front, first column), grid.y = group of MF_NB right-hand sides.  256 threads = 32 columns x 8 row groups.
+__global__ void __launch_bounds__(256) mf_backward_mrhs_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
+                                                              const int32_t* __restrict__ bnd, const int32_t* __restrict__ work,
+                                                              const double* __restrict__ y, double* __restrict__ x, int64_t ldx,
+                                                              int nrhs) {
+    __shared__ __align__(16) double vs[MF_BCHUNK][MF_NB];
+    __shared__ double red[8][32][MF_NB + 1];
+    const FrontDesc d = desc[work[2 * blockIdx.x]];
+    const int c0 = work[2 * blockIdx.x + 1];
+    const int64_t b0 = (int64_t)blockIdx.y * MF_NB;
+    const int nb = min(MF_NB, nrhs - (int)b0);
+    const double* yb = y + b0 * ldx + d.own_start;
+    double* xb = x + b0 * ldx;
+    const int32_t* bl = bnd + d.upd_off;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int n1 = (int)d.n1, n = (int)(d.n1 + d.n2);
+    const int col = c0 + tx;
+    const double* mp = vals + d.mt_off + col;
+    double acc[MF_NB];
+#pragma unroll
+    for (int b = 0; b < MF_NB; ++b) acc[b] = 0.0;
+    // own rows r < c0 hold zeros in all of this CTA's columns (lower triangular): start at c0
+    for (int rb0 = c0; rb0 < n; rb0 += MF_BCHUNK) {
+        const int len = min(MF_BCHUNK, n - rb0);
+        __syncthreads();
+        for (int e = threadIdx.x; e < len * MF_NB; e += blockDim.x) {
+            const int j = e / MF_NB, b = e % MF_NB;
+            const int r = rb0 + j;
+            double v = 0.0;
+            if (b < nb) v = r < n1 ? yb[b * ldx + r] : xb[b * ldx + bl[r - n1]];
+            vs[j][b] = v;
+        }
+        __syncthreads();
+        if (col < n1) {
+            for (int j = ty; j < len; j += 8) {
+                const int r = rb0 + j;
+                if (r < n1 && r < col) continue;
+                const long long srow = r < n1 ? r : d.row2 + (r - n1);
+                const double m = mp[srow * d.ldm];
+                const double2* v2 = reinterpret_cast<const double2*>(vs[j]);
+#pragma unroll
+                for (int b = 0; b < MF_NB / 2; ++b) {
+                    const double2 v = v2[b];
+                    acc[2 * b] = fma(m, v.x, acc[2 * b]);
+                    acc[2 * b + 1] = fma(m, v.y, acc[2 * b + 1]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int b = 0; b < MF_NB; ++b) red[ty][tx][b] = acc[b];
+    __syncthreads();
+    {   // thread -> (column tx, right-hand side ty): MF_NB == 8 row groups
+        const int b = ty;
+        if (col < n1 && b < nb) {
+            double s = red[0][tx][b];
+#pragma unroll
+            for (int k = 1; k < 8; ++k) s += red[k][tx][b];
+            xb[b * ldx + d.own_start + col] = s;
+        }
+    }
+}
+
 __global__ void gather_rows_kernel(const double* __restrict__ in, const int32_t* __restrict__ map, double* __restrict__ out,
                                    int64_t n, int64_t ldin, int64_t ldout) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -144,8 +394,19 @@ int asb_mf_forward(const int64_t* desc, const double* vals, const int32_t* src, 
                    int64_t nwork, const double* rhs, double* y, double* upd, int64_t nrhs, int64_t ldx, int64_t ldu,
                    asb_stream_t stream) {
     ASB_REQUIRE(desc && vals && src && work && rhs && y && upd && nwork > 0 && nrhs > 0 && nrhs < 65536, "mf_forward: bad arguments");
-    mf_forward_kernel<<<dim3((unsigned)nwork, (unsigned)nrhs), 256, 0, S(stream)>>>(
-        reinterpret_cast<const FrontDesc*>(desc), vals, src, slots, work, rhs, y, upd, ldx, ldu);
+    static const int fwd_dmma = [] {
+        const char* e = std::getenv("ASB_MF_FWD_DMMA");
+        return e ? std::atoi(e) : 1;
+    }();
+    if (nrhs >= MF_MRHS_MIN && fwd_dmma)
+        mf_forward_dmma_kernel<<<dim3((unsigned)nwork, (unsigned)cdiv(nrhs, MF_NB)), 128, 0, S(stream)>>>(
+            reinterpret_cast<const FrontDesc*>(desc), vals, src, slots, work, rhs, y, upd, ldx, ldu, (int)nrhs);
+    else if (nrhs >= MF_MRHS_MIN)
+        mf_forward_mrhs_kernel<<<dim3((unsigned)nwork, (unsigned)cdiv(nrhs, MF_NB)), 256, 0, S(stream)>>>(
+            reinterpret_cast<const FrontDesc*>(desc), vals, src, slots, work, rhs, y, upd, ldx, ldu, (int)nrhs);
+    else
+        mf_forward_kernel<<<dim3((unsigned)nwork, (unsigned)nrhs), 256, 0, S(stream)>>>(
+            reinterpret_cast<const FrontDesc*>(desc), vals, src, slots, work, rhs, y, upd, ldx, ldu);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
 }
@@ -153,8 +414,12 @@ int asb_mf_forward(const int64_t* desc, const double* vals, const int32_t* src, 
 int asb_mf_backward(const int64_t* desc, const double* vals, const int32_t* bnd, const int32_t* work, int64_t nwork,
                     const double* y, double* x, int64_t nrhs, int64_t ldx, asb_stream_t stream) {
     ASB_REQUIRE(desc && vals && bnd && work && y && x && nwork > 0 && nrhs > 0 && nrhs < 65536, "mf_backward: bad arguments");
-    mf_backward_kernel<<<dim3((unsigned)nwork, (unsigned)nrhs), 256, 0, S(stream)>>>(
-        reinterpret_cast<const FrontDesc*>(desc), vals, bnd, work, y, x, ldx);
+    if (nrhs >= MF_MRHS_MIN)
+        mf_backward_mrhs_kernel<<<dim3((unsigned)nwork, (unsigned)cdiv(nrhs, MF_NB)), 256, 0, S(stream)>>>(
+            reinterpret_cast<const FrontDesc*>(desc), vals, bnd, work, y, x, ldx, (int)nrhs);
+    else
+        mf_backward_kernel<<<dim3((unsigned)nwork, (unsigned)nrhs), 256, 0, S(stream)>>>(
+            reinterpret_cast<const FrontDesc*>(desc), vals, bnd, work, y, x, ldx);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
 }

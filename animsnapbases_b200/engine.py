@@ -59,6 +59,28 @@ class Comm:
         if self.world > 1:
             self.dist.barrier()
 
+    def all_to_all(self, send):
+        """send[j]: equally shaped tensor for rank j -> list of the tensors every rank addressed to this one.
+        NCCL: one all_to_all (NVLink, each byte crosses once); gloo (CPU tests) has none: all_gather of the stacks."""
+        if self.world == 1:
+            return list(send)
+        if self.dist.get_backend() == "nccl":
+            recv = [torch.empty_like(t) for t in send]
+            self.dist.all_to_all(recv, [t.contiguous() for t in send])
+            return recv
+        mine = torch.stack(list(send))
+        stacks = [torch.empty_like(mine) for _ in range(self.world)]
+        self.dist.all_gather(stacks, mine)
+        return [st[self.rank] for st in stacks]
+
+    def allgather_ints(self, values):
+        """Small replicated metadata: list of python ints per rank -> list (per rank) of lists."""
+        if self.world == 1:
+            return [list(values)]
+        out = [None] * self.world
+        self.dist.all_gather_object(out, list(values))
+        return out
+
 
 @dataclass
 class Shard:
@@ -247,7 +269,9 @@ def splocs(ops, comm, X, shard, C, W, K, geodesic, num_iters, num_admm, lam, rho
     B0 = ops.empty((K, 3, ld))
     H = ops.zeros((K, Kp))
     Hinv = ops.zeros((K, Kp))
-    Hr = ops.zeros((K, Kp))
+    K8 = (K + 15) // 16 * 16
+    Hr = ops.zeros((K8, K8))                                           # asb_admm_solve: zero-padded to ceil16(K)
+    Hr_c = ops.zeros((K, Kp)) if K8 != Kp else None
     Fp = (F + 1) // 2 * 2
     Aw = ops.zeros((K, Fp))
     WQ = ops.zeros((F, Kp))
@@ -282,12 +306,16 @@ def splocs(ops, comm, X, shard, C, W, K, geodesic, num_iters, num_admm, lam, rho
         ops.weights_sweep(P, Q, W, F, K)
         ids = idx.tolist()                                              # K ints -> host (memoisation key)
         centre_hist.append(ids)
-        geodesic.support(idx, 1, lam, dmin, dmax, row0, N, Lambda, ids_host=ids)
+        geodesic.support(idx, 1, lam, dmin, dmax, row0, N, Lambda, ids_host=ids, comm=comm)
         ops.gram_small(W, F, K, rho, H)                                 # H = W^T W + rho I
         ops.spd_inverse(H, K, Hinv, info)
         ops.small_gemm(0, 1, K, F, K, 1.0, Hinv, W, Aw)                 # Aw = H^-1 W^T   (K x F)
         ops.gemm_nn(Aw, K, F, Xm, M, 1.0, B0.view(K, M))                # B0 = H^-1 (W^T X)
-        ops.axpby(Hr.view(1, -1), rho, Hinv.view(1, -1), None, 0.0, None, K * Kp)
+        if K8 == Kp:
+            ops.axpby(Hr[:K].view(1, -1), rho, Hinv.view(1, -1), None, 0.0, None, K * Kp)
+        else:                                                           # K % 8 != 0: scale, then re-stride into the padding
+            ops.axpby(Hr_c.view(1, -1), rho, Hinv.view(1, -1), None, 0.0, None, K * Kp)
+            Hr[:K, :K].copy_(Hr_c[:, :K])
         ops.admm_solve(Hr, B0, C, U, Lambda, K, N, 1.0 / rho, num_admm)
         P, Q = grams()
         centres(True)

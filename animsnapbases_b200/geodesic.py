@@ -135,10 +135,14 @@ class HeatGeodesics:
         self.stats["solves"] += B
         return phi
 
-    def support(self, idx_dev, mode, lam, dmin, dmax, row0, nloc, out, ids_host=None, chunk=64):
+    def support(self, idx_dev, mode, lam, dmin, dmax, row0, nloc, out, ids_host=None, chunk=64, comm=None):
         """out[b, :nloc] = support map of source idx_dev[b] restricted to rows [row0, row0+nloc).
         mode 0: 1 - map (deflation mask), 1: lam * map (SPLOCS Lambda), 2: phi - min(phi).
-        With `ids_host` (the same indices as a host list) rows are memoised per vertex id."""
+        With `ids_host` (the same indices as a host list) rows are memoised per vertex id.  With `comm` (world > 1) the
+        new sources of a batch are dealt round-robin to the ranks: every rank solves its share on the full mesh (the heat
+        method is global), cuts the support map of each field into the ranks' row slices and one all-to-all hands every
+        rank its rows of every field -- the geodesic work of a SPLOCS iteration is divided by the world size instead of
+        being repeated on every rank."""
         ops = self.ops
         B = idx_dev.numel()
         self.stats["queries"] += B
@@ -151,8 +155,14 @@ class HeatGeodesics:
         key = (mode, float(lam), float(dmin), float(dmax), row0, nloc)
         cache = self._cache.setdefault(key, {})
         missing = sorted({int(i) for i in ids_host if int(i) not in cache})
-        for b0 in range(0, len(missing), chunk):
-            ids = missing[b0:b0 + chunk]
+        world = comm.world if comm is not None else 1
+        if world > 1 and len(missing) > 1:
+            self._support_sharded(comm, missing, cache, mode, lam, dmin, dmax, row0, nloc, out.shape[1], chunk)
+            missing_local = []
+        else:
+            missing_local = missing
+        for b0 in range(0, len(missing_local), chunk):
+            ids = missing_local[b0:b0 + chunk]
             idt = ops.to_device(np.asarray(ids, dtype=np.int64))
             phi = self.distances(idt)
             rows = ops.zeros((len(ids), out.shape[1]))
@@ -163,3 +173,26 @@ class HeatGeodesics:
         for b, i in enumerate(ids_host):
             out[b].copy_(cache[int(i)])
         return out
+
+    def _support_sharded(self, comm, missing, cache, mode, lam, dmin, dmax, row0, nloc, ld, chunk):
+        """Round-robin the sources over the ranks, solve locally, exchange row slices (see `support`)."""
+        ops = self.ops
+        world, rank = comm.world, comm.rank
+        skey = (row0, nloc, ld)
+        if getattr(self, "_shards_key", None) != skey:
+            self._shards = comm.allgather_ints([row0, nloc, ld])      # every rank's (row0, nloc, ld), once per sharding
+            self._shards_key = skey
+        ldmax = max(s[2] for s in self._shards)
+        bmax = (len(missing) + world - 1) // world
+        mine = missing[rank::world]
+        send = [ops.zeros((bmax, ldmax)) for _ in range(world)]
+        for b0 in range(0, len(mine), chunk):
+            ids = mine[b0:b0 + chunk]
+            phi = self.distances(ops.to_device(np.asarray(ids, dtype=np.int64)))
+            for j, (r0j, nj, ldj) in enumerate(self._shards):
+                if nj > 0:
+                    ops.support_map(phi, self.n, dmin, dmax, mode, lam, r0j, nj, send[j][b0:b0 + len(ids)])
+        recv = comm.all_to_all(send)
+        for j in range(world):
+            for b, i in enumerate(missing[j::world]):
+                cache[i] = recv[j][b, :ld]

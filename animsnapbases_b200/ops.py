@@ -212,13 +212,18 @@ class CudaOps:
         return out
 
     def admm_iter(self, Hr, B0, Z, U, Lambda, K, N, inv_rho):
-        ld = Z.shape[2]
-        self._call("asb_admm_iter", self._p(Hr), Hr.stride(0), self._p(B0), self._p(Z), self._p(U), self._p(Lambda), K, N, ld,
-                   float(inv_rho))
+        """One ADMM iteration (asb_admm_iter == asb_admm_solve with iters = 1)."""
+        self.admm_solve(Hr, B0, Z, U, Lambda, K, N, inv_rho, 1)
 
     def admm_solve(self, Hr, B0, Z, U, Lambda, K, N, inv_rho, iters):
-        """`iters` fused ADMM iterations in one launch (Z, U in place)."""
+        """`iters` fused ADMM iterations in one launch (Z, U in place).  The kernel wants Hr zero-padded to
+        ceil16(K) x ceil16(K); a tensor that is not (tests, ad-hoc callers) is copied into a padded one here."""
         ld = Z.shape[2]
+        k8 = (K + 15) // 16 * 16
+        if Hr.shape[0] < k8 or Hr.stride(0) < k8:
+            Hp = self.zeros((k8, k8))
+            Hp[:K, :K] = Hr[:K, :K]
+            Hr = Hp
         self._call("asb_admm_solve", self._p(Hr), Hr.stride(0), self._p(B0), self._p(Z), self._p(U), self._p(Lambda), K, N, ld,
                    float(inv_rho), int(iters))
 

@@ -127,7 +127,8 @@ int asb_gemm_nn(const double* A, int64_t lda, int64_t r, int64_t q, const double
                 double alpha, const double* row_scale, double* D, int64_t ldd, asb_stream_t stream);
 /* The ADMM inner loop of one SPLOCS outer step (posComponents.py:175-178, :252-256), `iters` iterations fused in ONE
  * launch, in place on Z and U:
- *   C = B0 + Hr (Z - U)          Hr = rho * (W^T W + rho I)^-1  (K x K, ldh)
+ *   C = B0 + Hr (Z - U)          Hr = rho * (W^T W + rho I)^-1  (K x K, ZERO-PADDED by the caller to ceil8(K) rows and
+ *                                 ldh >= ceil16(K) columns: the slab stager runs without bounds tests)
  *   V = C + U;  Z' = V * max(0, 1 - inv_rho * Lambda[k][n] / |V[k][:, n]|);  U' = V - Z'
  * The iteration only couples the K entries of one vertex, so each CTA keeps its vertex tile (Z - U, U) in shared
  * memory for all iterations: Z and U cross HBM once per call.  B0, Z, U: K x 3*ld planar; Lambda: K x ld.  K <= 256. */

@@ -426,9 +426,10 @@ def test_geodesic_kernels(cuda_ops):
     close(og, orr, 1e-11, "heat-method distances (multifrontal solve on device vs numpy statement)")
 
 
+@pytest.mark.parametrize("B", [1, 5, 19])    # 1: single-RHS kernels; 5: one partial group of 8; 19: 2 full groups + 3
 @pytest.mark.parametrize("nx,ny,leaf,ground", [(9, 7, 64, None), (60, 45, 16, None), (150, 120, 64, None), (60, 45, 16, 5),
                                                (150, 120, 32, 0)])
-def test_multifrontal_solve(cuda_ops, nx, ny, leaf, ground):
+def test_multifrontal_solve(cuda_ops, nx, ny, leaf, ground, B):
     """asb_mf_forward / asb_mf_backward (+ batched device factorisation) against SuperLU, the reference's solver
     (utils/support.py:169-171): componentwise relative accuracy for the heat system, residual for the grounded Poisson."""
     from scipy import sparse
@@ -445,7 +446,6 @@ def test_multifrontal_solve(cuda_ops, nx, ny, leaf, ground):
     mf = MultifrontalSolver(cuda_ops, A, verts, leaf_size=leaf, ground=ground)
     ldx = mf.ldx
     rng = np.random.default_rng(4)
-    B = 5
     rhs = np.zeros((B, ldx))
     if ground is None:
         rhs[np.arange(B), rng.integers(0, n, B)] = 1.0              # heat sources

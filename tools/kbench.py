@@ -34,7 +34,12 @@ def main():
     ap.add_argument("--frames", type=int, default=2000)
     ap.add_argument("--comps", type=int, default=200)
     ap.add_argument("--only", default="")
+    ap.add_argument("--once", action="store_true", help="one launch per kernel, no warm-up (for ncu --set full captures)")
     args = ap.parse_args()
+    if args.once:
+        global timed
+        _t = timed
+        timed = lambda fn, reps=1, warm=0: _t(fn, 1, 0)  # noqa: E731
     ops = CudaOps("cuda:0")
     N, F, K = args.verts, args.frames, args.comps
     ld = pad_ld(N)
@@ -88,7 +93,7 @@ def main():
         rec("asb_vertex_energy", timed(lambda: ops.vertex_energy(X, N, out=e)), nbytes=S)
         rec("asb_deflate_gemv", timed(lambda: ops.deflate_gemv(X, N, W, 0, g)), nbytes=S)
         Wz = ops.zeros((F, Kp))
-        for nb in (4, 8, 16):
+        for nb in ((8,) if args.once else (4, 8, 16)):
             rec("asb_rank_update_nb%d" % nb, timed(lambda: ops.rank_update(X, N, Wz, C, 0, nb, e), reps=2), nbytes=2 * S)
         mean = ops.zeros((3, ld))
         rec("asb_center_stats", timed(lambda: ops.center_stats(X, mean, N)), nbytes=S)
@@ -114,10 +119,12 @@ def main():
         B0 = ops.empty((K, 3, ld)).normal_()
         U = ops.zeros((K, 3, ld))
         Lam = ops.empty((K, ld)).uniform_(0, 2)
-        Hr = ops.zeros((K, Kp))
-        Hr[:, :K] = torch.eye(K, dtype=torch.float64, device=ops.device) * 0.5
-        rec("asb_admm_iter", timed(lambda: ops.admm_iter(Hr, B0, C, U, Lam, K, N, 0.1)), flops=2.0 * K * K * M,
-            nbytes=8.0 * K * M * 5 + 8.0 * K * ld)
+        K8 = (K + 15) // 16 * 16
+        Hr = ops.zeros((K8, K8))
+        Hr[:K, :K] = torch.eye(K, dtype=torch.float64, device=ops.device) * 0.5 + 0.01 * torch.randn(K, K, dtype=torch.float64, device=ops.device)
+        if not args.once:
+            rec("asb_admm_iter", timed(lambda: ops.admm_iter(Hr, B0, C, U, Lam, K, N, 0.1)), flops=2.0 * K * K * M,
+                nbytes=8.0 * K * M * 5 + 8.0 * K * ld)
         rec("asb_admm_solve_x10", timed(lambda: ops.admm_solve(Hr, B0, C, U, Lam, K, N, 0.1, 10), reps=2), flops=20.0 * K * K * M,
             nbytes=8.0 * K * M * 5 + 8.0 * K * ld)
     json.dump(out, open(os.path.join("gpurun_out", "kbench_%dx%d.json" % (N, F)), "w"), indent=1)
