@@ -377,6 +377,62 @@ __global__ void __launch_bounds__(256) mf_backward_mrhs_kernel(const FrontDesc* 
     }
 }
 
+// DMMA variant of the batched backward pass: X (columns x 8 RHS) = Mt^T (columns x rows) V (rows x 8 RHS).  A warp owns 8
+// columns; lane (lr, lc) reads Mt[row k + lc][column lr] (eight consecutive doubles per row: two full sectors), the B
+// fragment comes from the staged vector block vs[row][rhs] (row stride 12 doubles: conflict-free), D[column lr][rhs 2lc,
+// 2lc+1] is the result.  grid.x = work item (front, first of 32 columns), grid.y = group of 8 right-hand sides; 128 threads.
+constexpr int MF_VLD = 12;
+
+__global__ void __launch_bounds__(128) mf_backward_dmma_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
+                                                              const int32_t* __restrict__ bnd, const int32_t* __restrict__ work,
+                                                              const double* __restrict__ y, double* __restrict__ x, int64_t ldx,
+                                                              int nrhs) {
+    __shared__ double vs[MF_BCHUNK * MF_VLD];
+    const FrontDesc d = desc[work[2 * blockIdx.x]];
+    const int c0 = work[2 * blockIdx.x + 1];
+    const int64_t b0 = (int64_t)blockIdx.y * MF_NB;
+    const int nb = min(MF_NB, nrhs - (int)b0);
+    const double* yb = y + b0 * ldx + d.own_start;
+    double* xb = x + b0 * ldx;
+    const int32_t* bl = bnd + d.upd_off;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, lr = lane >> 2, lc = lane & 3;
+    const int n1 = (int)d.n1, n = (int)(d.n1 + d.n2);
+    const int cola = c0 + warp * 8 + lr;                  // the lane's column of the A fragment (and of D)
+    const bool col_ok = cola < n1;
+    const double* mp = vals + d.mt_off + (col_ok ? cola : 0);
+    double acc0 = 0.0, acc1 = 0.0, odd0 = 0.0, odd1 = 0.0;
+    // own rows r < c0 hold zeros in all of this CTA's columns (lower triangular): start at c0 (a multiple of 32)
+    for (int rb0 = c0; rb0 < n; rb0 += MF_BCHUNK) {
+        const int len = min(MF_BCHUNK, n - rb0);
+        const int len8 = (len + 7) & ~7;
+        __syncthreads();
+        for (int e = threadIdx.x; e < len8 * MF_NB; e += blockDim.x) {
+            const int j = e / MF_NB, b = e % MF_NB;
+            const int r = rb0 + j;
+            double v = 0.0;
+            if (b < nb && j < len) v = r < n1 ? yb[b * ldx + r] : xb[b * ldx + bl[r - n1]];
+            vs[j * MF_VLD + b] = v;
+        }
+        __syncthreads();
+        const double* bp = vs + lc * MF_VLD + lr;
+        for (int k0 = 0; k0 < len8; k0 += 8) {
+            const int ra = rb0 + k0 + lc, rb = ra + 4;
+            const long long sa = ra < n1 ? ra : d.row2 + (ra - n1);
+            const long long sb = rb < n1 ? rb : d.row2 + (rb - n1);
+            const double a0 = (col_ok && ra < n) ? mp[sa * d.ldm] : 0.0;
+            const double a1 = (col_ok && rb < n) ? mp[sb * d.ldm] : 0.0;
+            dmma(acc0, acc1, a0, bp[k0 * MF_VLD]);
+            dmma(odd0, odd1, a1, bp[(k0 + 4) * MF_VLD]);
+        }
+    }
+    acc0 += odd0;
+    acc1 += odd1;
+    if (col_ok) {
+        if (2 * lc < nb) xb[(2 * lc) * ldx + d.own_start + cola] = acc0;
+        if (2 * lc + 1 < nb) xb[(2 * lc + 1) * ldx + d.own_start + cola] = acc1;
+    }
+}
+
 __global__ void gather_rows_kernel(const double* __restrict__ in, const int32_t* __restrict__ map, double* __restrict__ out,
                                    int64_t n, int64_t ldin, int64_t ldout) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -414,13 +470,37 @@ int asb_mf_forward(const int64_t* desc, const double* vals, const int32_t* src, 
 int asb_mf_backward(const int64_t* desc, const double* vals, const int32_t* bnd, const int32_t* work, int64_t nwork,
                     const double* y, double* x, int64_t nrhs, int64_t ldx, asb_stream_t stream) {
     ASB_REQUIRE(desc && vals && bnd && work && y && x && nwork > 0 && nrhs > 0 && nrhs < 65536, "mf_backward: bad arguments");
-    if (nrhs >= MF_MRHS_MIN)
+    static const int bwd_dmma = [] {
+        const char* e = std::getenv("ASB_MF_BWD_DMMA");
+        return e ? std::atoi(e) : 1;
+    }();
+    if (nrhs >= MF_MRHS_MIN && bwd_dmma)
+        mf_backward_dmma_kernel<<<dim3((unsigned)nwork, (unsigned)cdiv(nrhs, MF_NB)), 128, 0, S(stream)>>>(
+            reinterpret_cast<const FrontDesc*>(desc), vals, bnd, work, y, x, ldx, (int)nrhs);
+    else if (nrhs >= MF_MRHS_MIN)
         mf_backward_mrhs_kernel<<<dim3((unsigned)nwork, (unsigned)cdiv(nrhs, MF_NB)), 256, 0, S(stream)>>>(
             reinterpret_cast<const FrontDesc*>(desc), vals, bnd, work, y, x, ldx, (int)nrhs);
     else
         mf_backward_kernel<<<dim3((unsigned)nwork, (unsigned)nrhs), 256, 0, S(stream)>>>(
             reinterpret_cast<const FrontDesc*>(desc), vals, bnd, work, y, x, ldx);
     ASB_LAUNCH_CHECK();
+    return ASB_OK;
+}
+
+int asb_mf_solve(const int64_t* desc, const double* vals, const int32_t* src, int64_t slots, const int32_t* bnd,
+                 const int64_t* levels, int64_t nlevels, const double* rhs, double* y, double* x, double* upd, int64_t nrhs,
+                 int64_t ldx, int64_t ldu, asb_stream_t stream) {
+    ASB_REQUIRE(levels && nlevels > 0 && nlevels < 4096, "mf_solve: bad level table");
+    for (int64_t l = nlevels - 1; l >= 0; --l) {
+        const int rc = asb_mf_forward(desc, vals, src, slots, reinterpret_cast<const int32_t*>(levels[4 * l]), levels[4 * l + 1], rhs,
+                                      y, upd, nrhs, ldx, ldu, stream);
+        if (rc != ASB_OK) return rc;
+    }
+    for (int64_t l = 0; l < nlevels; ++l) {
+        const int rc = asb_mf_backward(desc, vals, bnd, reinterpret_cast<const int32_t*>(levels[4 * l + 2]), levels[4 * l + 3], y, x,
+                                       nrhs, ldx, stream);
+        if (rc != ASB_OK) return rc;
+    }
     return ASB_OK;
 }
 

@@ -180,8 +180,10 @@ def deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1
         comm.allreduce_sum(traj)
         ops.traj_rank1(traj, F, local_support, W, k, k0, coef, scal)
         if local_support:
-            geodesic.support(idx, 0, 1.0, dmin, dmax, row0, N, s)
+            with ops.fork():      # the heat-method query (60 small launches, latency bound) runs beside the HBM-bound pass
+                geodesic.support(idx, 0, 1.0, dmin, dmax, row0, N, s)
         ops.deflate_gemv(R, N, W, k, g)
+        ops.join()
         ops.deflate_finish(g, C, k, k0, coef, s[0] if local_support else None, scal, e, N, meas[k])
         if comm.world > 1:
             comm.allreduce_sum(meas[k, 2:3])
@@ -306,11 +308,13 @@ def splocs(ops, comm, X, shard, C, W, K, geodesic, num_iters, num_admm, lam, rho
         ops.weights_sweep(P, Q, W, F, K)
         ids = idx.tolist()                                              # K ints -> host (memoisation key)
         centre_hist.append(ids)
-        geodesic.support(idx, 1, lam, dmin, dmax, row0, N, Lambda, ids_host=ids, comm=comm)
+        with ops.fork():          # support maps of the new centres: side stream, beside the B0 GEMM (Lambda is read by ADMM only)
+            geodesic.support(idx, 1, lam, dmin, dmax, row0, N, Lambda, ids_host=ids, comm=comm)
         ops.gram_small(W, F, K, rho, H)                                 # H = W^T W + rho I
         ops.spd_inverse(H, K, Hinv, info)
         ops.small_gemm(0, 1, K, F, K, 1.0, Hinv, W, Aw)                 # Aw = H^-1 W^T   (K x F)
         ops.gemm_nn(Aw, K, F, Xm, M, 1.0, B0.view(K, M))                # B0 = H^-1 (W^T X)
+        ops.join()
         if K8 == Kp:
             ops.axpby(Hr[:K].view(1, -1), rho, Hinv.view(1, -1), None, 0.0, None, K * Kp)
         else:                                                           # K % 8 != 0: scale, then re-stride into the padding

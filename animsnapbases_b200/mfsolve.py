@@ -336,6 +336,11 @@ class MultifrontalSolver:
         self.order_host = sym.order
         self.work_fwd = [ops.to_device(w) for w in sym.work_fwd]
         self.work_bwd = [ops.to_device(w) for w in sym.work_bwd]
+        # host table for asb_mf_solve (root level first): work-list pointers and lengths of every level
+        self.levels_host = None
+        if hasattr(ops, "mf_solve"):
+            self.levels_host = np.array([[wf.data_ptr(), wf.shape[0], wb.data_ptr(), wb.shape[0]]
+                                         for wf, wb in zip(self.work_fwd, self.work_bwd)], dtype=np.int64)
         self.upd_len = (sym.upd_len + 31) // 32 * 32 + 32
         self.slots = sym.src.shape[1]
         self.stats = {"fronts": sym.T, "levels": len(sym.levels), "operator_bytes": int(sym.vals_len) * 8}
@@ -347,6 +352,9 @@ class MultifrontalSolver:
         y = ops.empty((B, self.ldx))
         x = ops.empty((B, self.ldx))
         upd = ops.empty((B, self.upd_len))
+        if self.levels_host is not None:
+            ops.mf_solve(self.desc, self.vals, self.src, self.slots, self.bnd, self.levels_host, rhs_p, y, x, upd)
+            return x
         for w in reversed(self.work_fwd):
             ops.mf_forward(self.desc, self.vals, self.src, self.slots, w, rhs_p, y, upd)
         for w in self.work_bwd:

@@ -38,7 +38,8 @@ class CudaOps:
         self.sm_count, self.cc = sms.value, (major.value, minor.value)
         if self.cc[0] < 10:
             raise _lib.AsbError(f"libasb.so is built for sm_100a only; found compute capability {self.cc}")
-        self._ws = None
+        self._ws = {}          # scratch per stream
+        self._side = None      # side stream of fork() / join()
         self._ws2 = None
         self.timers = None
 
@@ -88,9 +89,25 @@ class CudaOps:
         return t.to(self.device, non_blocking=True).contiguous()
 
     def workspace(self, nbytes: int):
-        if self._ws is None or self._ws.numel() < nbytes:
-            self._ws = torch.empty(int(nbytes) + 256, dtype=torch.uint8, device=self.device)
-        return self._ws
+        """Scratch for the reductions of the CURRENT stream (one buffer per stream: the geodesic solves run on a side
+        stream next to the streaming / DMMA kernels of the main one)."""
+        key = torch.cuda.current_stream(self.device).cuda_stream
+        ws = self._ws.get(key)
+        if ws is None or ws.numel() < nbytes:
+            ws = self._ws[key] = torch.empty(int(nbytes) + 256, dtype=torch.uint8, device=self.device)
+        return ws
+
+    def fork(self):
+        """Context manager: run the enclosed launches on the side stream, ordered after everything issued so far on the
+        current stream; `join()` makes the current stream wait for them."""
+        if self._side is None:
+            self._side = torch.cuda.Stream(self.device)
+        self._side.wait_stream(torch.cuda.current_stream(self.device))
+        return torch.cuda.stream(self._side)
+
+    def join(self):
+        if self._side is not None:
+            torch.cuda.current_stream(self.device).wait_stream(self._side)
 
     def ws_for(self, rows: int, cols: int):
         return self.workspace(self.lib.asb_workspace_bytes(int(rows), int(cols)))
@@ -325,6 +342,12 @@ class CudaOps:
     def mf_backward(self, desc, vals, bnd, work, y, x):
         self._call("asb_mf_backward", self._p(desc), self._p(vals), self._p(bnd), self._p(work), work.shape[0], self._p(y), self._p(x),
                    y.shape[0], y.stride(0))
+
+    def mf_solve(self, desc, vals, src, slots, bnd, levels_host, rhs, y, x, upd):
+        """All levels of one multifrontal solve from a single C call; levels_host: (nlevels, 4) int64 numpy (root first)."""
+        self._call("asb_mf_solve", self._p(desc), self._p(vals), self._p(src), slots, self._p(bnd),
+                   ctypes.c_void_p(levels_host.ctypes.data), levels_host.shape[0], self._p(rhs), self._p(y), self._p(x), self._p(upd),
+                   rhs.shape[0], rhs.stride(0), upd.stride(0))
 
     def heat_divergence(self, u, tri, gconst, dconst, vc_ptr, vc_idx, n, Xt, div):
         nrhs, ldx = u.shape

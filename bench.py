@@ -189,10 +189,17 @@ def main():
     def prepare(src_dev):
         return engine.prepare_snapshots(ops, comm, src_dev, mass_loc, "first", sh)
 
+    phase_ev = []        # (deflation start, deflation end = SPLOCS start, SPLOCS end) CUDA events of every build
+
     def build(st):
         geo.reset()      # every build starts cold: support maps are memoised by source vertex WITHIN a build only
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        ev[0].record()
         C, W, meas, picked, _ = engine.deflate(ops, comm, st.X, sh, K, True, geo, block=args.block, keep_residual=False)
+        ev[1].record()
         engine.splocs(ops, comm, st.X, sh, C, W, K, geo, Is, Ia, 2.0, 10.0, log=None)
+        ev[2].record()
+        phase_ev.append(ev)
         return C, W, meas
 
     st = prepare(anim_dev)
@@ -208,7 +215,7 @@ def main():
     sync_all()
     # ---- timed region (device-resident inputs)
     timed = ["asb_deflate_gemv", "asb_rank_update", "asb_admm_solve", "asb_gemm_nn", "asb_gemm_nt", "asb_weights_sweep",
-             "asb_component_centers", "asb_mf_forward", "asb_mf_backward", "asb_support_map", "asb_vertex_energy"]
+             "asb_component_centers", "asb_mf_solve", "asb_support_map", "asb_vertex_energy"]
     ops.time_kernels(timed)
     ops.reset_launch_count()
     clocks = ClockSampler(local_rank)
@@ -216,6 +223,7 @@ def main():
         clocks.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
+    phase_ev.clear()
     ev0.record()
     for _ in range(args.steps):
         if flush is not None:
@@ -231,6 +239,9 @@ def main():
     ops.time_kernels(None)
     clk = clocks.stop() if rank == 0 else None
     ms_per_step = float(ms.item()) / args.steps
+    phase_ms = {"deflation": sum(e[0].elapsed_time(e[1]) for e in phase_ev) / args.steps,
+                "splocs": sum(e[1].elapsed_time(e[2]) for e in phase_ev) / args.steps}
+    phase_ev.clear()
     geo_stats = dict(geo.stats)
 
     # ---- e2e: host float32 animation (pinned) -> H2D -> ingest -> standardise -> build -> D2H comps + weights
@@ -323,6 +334,7 @@ def main():
         "clocks": clk, "e2e": e2e, "roofline": roof,
         "path_roofline": {"ideal_s": ideal, "frac": ideal / (ms_per_step / 1e3), "hbm_gbs": hbm_peak, "fp64_tflops": fp64_peak,
                           "algorithmic": {"deflation_bytes": defl_bytes, "splocs_flops": splocs_flops}},
+        "phase_ms_per_step": phase_ms,
         "kernel_ms_per_step": {k: v[1] / args.steps for k, v in ktimes.items()},
         "kernel_launches_per_step": {k: v[0] / args.steps for k, v in ktimes.items()},
         "geodesic": geo_stats,
