@@ -520,6 +520,110 @@ def deim_blocks(ops, comm, C, shard, p):
     return dict(Pt=Pt.cpu().numpy(), alpha=ix // p, alpha_ranges=np.arange(1, K + 1), idxs=ix)
 
 
+def square_csr_slice(ops, St, shard):
+    """Device CSR of St[:, row0:row0+n] (|V| x n_local, scipy sparse on the host) embedded in an L x L matrix, L = padded
+    max(|V|, n_local): asb_spmv_csr multiplies square matrices with one leading dimension for x and y."""
+    from scipy import sparse
+    A = sparse.csr_matrix(St)[:, shard.row0:shard.row0 + shard.n].tocsr()
+    nv = A.shape[0]
+    L = pad_ld(max(nv, shard.n, 1))
+    rowptr = np.full(L + 1, A.indptr[-1], dtype=np.int32)
+    rowptr[:nv + 1] = A.indptr
+    return (ops.to_device(rowptr), ops.to_device(A.indices.astype(np.int32)), ops.to_device(A.data.astype(np.float64))), nv, L
+
+
+def deim_geom(ops, comm, C, shard, p, elems, St=None, ele_per_vert=1):
+    """Geometric block DEIM of snapbases/constraintsComponents.py:619-731.  C (K p, 3, ld) planar post-processed block basis,
+    rows sharded; elems (e, nodes) host array of the constrained elements (tets / tris / edges), replicated.
+    St (|V| x ep scipy sparse, replicated on the host) given = error_in_pos_space: the block residual is pushed through St
+    (sparse mat-mat on the device, partial products all-reduced), the worst VERTEX is picked and up to `ele_per_vert` of its
+    not yet used incident elements join the interpolation set (p rows each).  St None: the worst ELEMENT by residual energy
+    over its p rows (:86-96).  The coefficients are the minimum-norm least-squares solution on the selected rows like
+    np.linalg.lstsq (:660, :671; rectangular once a vertex contributes more than one element): a replicated
+    (|Pt| x k p) pseudo-inverse per dimension (cuSOLVER through torch, tiny), everything ep-sized runs in libasb kernels.
+    Returns dict(Pt, alpha, alpha_ranges, verts) (host) or None on a zero residual (:676-678)."""
+    N, row0 = shard.n, shard.row0
+    Kc, _, ld = C.shape
+    K = Kc // p
+    elems = np.asarray(elems)
+    dev = C.device
+    R = ops.zeros((p, 3, ld))
+    Rv = R.view(3 * p, ld)
+    e_row = ops.zeros((ld,))
+    eg = ops.zeros((max(N // p, 1),))
+    val = ops.zeros((1,))
+    idx = ops.zeros((1,), I64)
+    if St is not None:
+        csr, nv, L = square_csr_slice(ops, St, shard)
+        xb = ops.zeros((3 * p, L))
+        yb = ops.zeros((3 * p, L))
+        ev = ops.zeros((L,))
+        incident = {}
+    Pt, e_points, e_range, verts = [], [], [], []
+    for k in range(K):
+        nb = k * p
+        if k == 0:
+            R.copy_(C[0:p])
+        else:
+            # ---- selected rows of the basis so far and of the new block: G[d, i, j] = C[j, d, Pt[i]]  (data movement + all-reduce)
+            pt = torch.as_tensor(np.asarray(Pt, dtype=np.int64), device=dev)
+            mine = (pt >= row0) & (pt < row0 + N)
+            G = torch.zeros((3, len(Pt), nb + p), dtype=F64, device=dev)
+            if bool(mine.any()):
+                G[:, mine, :] = C[:nb + p][:, :, pt[mine] - row0].permute(1, 2, 0)
+            comm.allreduce_sum(G)
+            a = torch.linalg.pinv(G[:, :, :nb]) @ G[:, :, nb:]          # (3, nb, p) min-norm least squares, replicated
+            # ---- residual block R[m, d, :] = sum_j a[d, j, m] C[j, d, :] - C[nb + m, d, :]
+            A = ops.zeros((p, (nb + 1) // 2 * 2))
+            for d in range(3):
+                A[:, :nb] = a[d].T
+                ops.gemm_nn(A, p, nb, C[:nb, d, :], ld, 1.0, R[:, d, :])
+            ops.axpby(Rv, 1.0, Rv, None, -1.0, C[nb:nb + p].view(3 * p, ld), N)
+        if St is not None:
+            # ---- r <- St r : 3 p sparse mat-vecs on this rank's columns, summed over the ranks
+            xb[:, :ld].copy_(Rv)
+            ops.spmv(csr, xb, yb)
+            comm.allreduce_sum(yb)
+            E = yb.view(p, 3, L)
+            nE = nv
+        else:
+            E, nE = R, N
+        if k > 0:
+            mx = E[:, :, :nE].abs().max().reshape(1) if nE else torch.zeros(1, dtype=F64, device=dev)
+            if St is None:
+                comm.allreduce_max(mx)
+            if float(mx.item()) <= 1e-8:                                # np.allclose(r, 0)
+                print("ERROR!: zero residual!!")
+                return None
+        if St is not None:
+            ops.vertex_energy(E, nv, out=ev)
+            ops.argmax_first(ev, nv, 0, val, idx)                       # replicated after the all-reduce: no exchange
+            v = int(idx.item())
+            verts.append(v)
+            if v not in incident:
+                incident[v] = [int(i) for i in np.nonzero((elems == v).any(axis=1))[0]]
+            jump = 0
+            for alpha in incident[v]:
+                if alpha not in e_points and jump < ele_per_vert:
+                    jump += 1
+                    e_points.append(alpha)
+                    Pt += [alpha * p + m for m in range(p)]
+        else:
+            ops.vertex_energy(R, N, out=e_row)
+            if N:
+                ops.group_sum(e_row, N, p, eg)
+                ops.argmax_first(eg, N // p, row0 // p, val, idx)
+            else:
+                val.fill_(-float("inf"))
+            comm.argmax_pairs(val, idx)
+            alpha = int(idx.item())
+            assert alpha not in e_points
+            e_points.append(alpha)
+            Pt += [alpha * p + m for m in range(p)]
+        e_range.append(len(e_points))
+    return dict(Pt=np.array(Pt), alpha=np.array(e_points), alpha_ranges=np.array(e_range), verts=np.array(verts, dtype=np.int64))
+
+
 # ====================================================================================== per-dimension Gram helpers
 def _plane(T, K, d):
     """(K, ld) view of dimension d of a planar (K, 3, ld) tensor (row stride 3*ld)."""

@@ -101,7 +101,7 @@ class CudaOps:
         """Context manager: run the enclosed launches on the side stream, ordered after everything issued so far on the
         current stream; `join()` makes the current stream wait for them."""
         if self._side is None:
-            self._side = torch.cuda.Stream(self.device)
+            self._side = torch.cuda.Stream(self.device)   # default priority: priority=-1 measured no better (r01: 17.8 s vs 17.6 s)
         self._side.wait_stream(torch.cuda.current_stream(self.device))
         return torch.cuda.stream(self._side)
 

@@ -14,7 +14,7 @@ Device work goes through animsnapbases_b200.engine -> libasb.so:
 
   pod             (:274-294)  p * 3 independent PODs of the (e x F) blocks (f32 torch-CPU SVDs in the reference)    engine.pod_per_row
 
-Basis type 'pca_blocks_with_St' and the geometric DEIM variant raise
+Basis type 'pca_blocks_with_St'  and the '_verts' geometric DEIM raise
 NotImplementedError here rather than fall back to the CPU.
 The plotting / polyscope methods of the reference (:865-1156) are out of scope (graphics: unavailable on this box).
 """
@@ -228,8 +228,31 @@ class constraintsComponents:  # Components == bases
             print(k, int(self.geom_alpha[k]))
         print("Regular Deim interpolation, used", self.geom_alpha.shape[0], "constrained elements")
 
-    def geom_block_form_utilizing_differential_operator(self, error_in_pos_space=True):
-        raise NotImplementedError("geometric DEIM (constraintsComponents.py:619-731) is not built on the device yet (SURVEY a14)")
+    @log_time("")
+    def geom_block_form_utilizing_differential_operator(self, error_in_pos_space=False):
+        """Geometric block DEIM (:619-731): residual measured in position space through the differential operator St (worst
+        vertex -> up to geom_ele_per_vert of its incident elements) or in constraint space (worst element)."""
+        ops, comm = runtime.get()
+        snaps = self.nonlinearSnapshots
+        elems = {"_tets": snaps.tets, "_tris": snaps.tris, "_edges": snaps.edges}.get(snaps.ele_type)
+        St = None
+        if error_in_pos_space:
+            if snaps.ele_type not in ["_tets", "_tris", "_edges", "_verts"]:
+                print("ERROR! Unknown constained elements nonliner snapshots type!")
+                return
+            if elems is None:
+                raise NotImplementedError("geometric DEIM for '_verts' (vertex-star / verts_bending) constraints is not built yet")
+            if self.St is None:
+                raise ValueError("geometric DEIM in position space needs the differential operator St (constProj_weightedSt)")
+            St = self.St
+        out = engine.deim_geom(ops, comm, self._C, snaps.shard, snaps.constraintsSize, elems, St,
+                               int(getattr(self.param, "geom_ele_per_vert", 1)))
+        if out is None:
+            return
+        self.geom_Pt, self.geom_alpha, self.geom_alpha_ranges = out["Pt"], out["alpha"], out["alpha_ranges"]
+        self.geom_interpol_verts = out["verts"]
+        print("Computing interpolation elements utilizing differential operator, used", self.geom_alpha.shape[0],
+              "constrained elements")
 
     # ------------------------------------------------------------------ checks
     @log_time("")

@@ -214,3 +214,25 @@ def tet_element_masses(verts: np.ndarray, tets: np.ndarray, p: int = 3) -> np.nd
     mv /= mv.sum()
     me = mv[tets].sum(axis=1)
     return np.repeat(me, p)
+
+
+def tet_gradient_operator(verts: np.ndarray, tets: np.ndarray, weighted: bool = True):
+    """The differential operator of tets_deformation_gradient constraints as a scipy CSR matrix S (3e x |V|): row 3t+i
+    applied to the positions gives row i of F_t^T, F_t = Ds Dm^{-1} (same vertex order as `tet_rotation_snapshots`).
+    `weighted` scales the rows of tet t by sqrt(volume_t) (the PD assembly weight).  The `St` the reference loads from
+    assembly_ST.npz (snapbases/constraintsComponents.py:61-84) is the transpose, |V| x 3e."""
+    from scipy import sparse
+    e = len(tets)
+    v = verts
+    Dm = np.stack([v[tets[:, 0]] - v[tets[:, 3]], v[tets[:, 1]] - v[tets[:, 3]], v[tets[:, 2]] - v[tets[:, 3]]], axis=2)
+    DmInv = np.linalg.inv(Dm)                                       # (e, 3, 3)
+    w = np.sqrt(np.abs(np.linalg.det(Dm)) / 6.0) if weighted else np.ones(e)
+    rows, cols, vals = [], [], []
+    for i in range(3):
+        r = 3 * np.arange(e) + i
+        for j in range(3):
+            rows.append(r); cols.append(tets[:, j]); vals.append(w * DmInv[:, j, i])
+        rows.append(r); cols.append(tets[:, 3]); vals.append(-w * DmInv[:, :, i].sum(axis=1))
+    S = sparse.csr_matrix((np.concatenate(vals), (np.concatenate(rows), np.concatenate(cols))), shape=(3 * e, len(verts)))
+    S.sum_duplicates()
+    return S

@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--bumps", type=int, default=64)
     ap.add_argument("--sigma", type=float, default=0.05)
     ap.add_argument("--block", type=int, default=8, help="deflation rank-update block size")
+    ap.add_argument("--leaf-size", type=int, default=64, help="nested-dissection leaf size of the geodesic factorisation")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample", type=int, nargs=5, default=[120, 100, 120, 24, 2],
@@ -183,7 +184,7 @@ def main():
     rows = slice(sh.row0, sh.row0 + sh.n)
     v_loc = ops.to_device(verts0[rows])
     anim_dev = synth.device_bump_animation_from_params(v_loc, verts0[centres], amps, args.sigma)   # (F, n_loc, 3) f32
-    geo = HeatGeodesics(ops, verts0, tris)
+    geo = HeatGeodesics(ops, verts0, tris, leaf_size=args.leaf_size)
     mass_loc = mass[rows]
 
     def prepare(src_dev):
@@ -315,7 +316,15 @@ def main():
         bound, work = per_step[dom]
         work *= args.steps
         tot_s = ktimes[dom][1] * 1e-3
-        common = {"kernel": dom, "bound": bound, "traffic": None, "avg_launch_ms": ktimes[dom][1] / ktimes[dom][0],
+        traffic = None      # measured DRAM bytes per launch (ncu capture of the same kernel at this shape), if we have one
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+            w = tr["workload"]
+            if world == 1 and (w["vertices"], w["frames"], w["components"], w["admm_iters"]) == (N, F, K, Ia):
+                traffic = tr["per_launch_bytes"].get(dom)
+        except Exception:
+            pass
+        common = {"kernel": dom, "bound": bound, "traffic": traffic, "avg_launch_ms": ktimes[dom][1] / ktimes[dom][0],
                   "launches": ktimes[dom][0], "work_per_launch": work / ktimes[dom][0]}
         if bound == "hbm":
             ach = work / tot_s / 1e9

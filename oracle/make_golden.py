@@ -297,10 +297,46 @@ def writers_case():
     print("writers: .bin layouts pinned")
 
 
+# ------------------------------------------------------------------------------------------------ geometric DEIM
+def bar_geom_case():
+    """geom_block_form_utilizing_differential_operator (constraintsComponents.py:619-731) of the unmodified reference on the
+    bar fixture's post-processed bases, in position space (St = transpose of the tet gradient operator) and in constraint
+    space -> tests/golden/bar_geom.npz.  Reads tests/golden/bar.npz (does not regenerate it)."""
+    from snapbases.constraintsComponents import constraintsComponents
+    from snapbases.nonlinear_snapshots import nonlinearSnapshots
+
+    m = np.load(os.path.join(GOLD, "meshes.npz"))
+    bar = np.load(os.path.join(GOLD, "bar.npz"))
+    verts, tets = m["bar_verts"], bar["tets"].astype(np.int64)
+    e, p = len(tets), 3
+    St = synth.tet_gradient_operator(verts, tets).T.tocsr()                 # |V| x ep
+    out = dict(St_rowptr=St.indptr.astype(np.int32), St_colidx=St.indices.astype(np.int32), St_vals=St.data,
+               St_shape=np.array(St.shape))
+    cases = {"blk_pos2": (bar["blk_post"], True, 2), "pod_pos1": (bar["post_comps"][:24], True, 1),
+             "pod_pos3": (bar["post_comps"][:24], True, 3), "pod_con": (bar["post_comps"][:24], False, 1)}
+    for name, (comps, pos, per_vert) in cases.items():
+        ns = object.__new__(nonlinearSnapshots)
+        ns.constraintsSize, ns.num_constained_elements, ns.dim = p, e, 3
+        ns.ele_type, ns.tets = "_tets", tets
+        cc = object.__new__(constraintsComponents)
+        cc.param = types.SimpleNamespace(geom_ele_per_vert=per_vert, constProj_snapshots_type="tets_deformation_gradient")
+        cc.nonlinearSnapshots, cc.comps, cc.numComp, cc.St, cc.geom_interpol_verts = ns, comps.copy(), comps.shape[0] // p, St, []
+        with contextlib.redirect_stdout(io.StringIO()):
+            cc.geom_block_form_utilizing_differential_operator(pos)
+        g = port.deim_geom(comps, p, e, tets, St if pos else None, per_vert)
+        assert np.array_equal(g["Pt"], cc.geom_Pt) and np.array_equal(g["alpha"], cc.geom_alpha)
+        assert np.array_equal(g["alpha_ranges"], cc.geom_alpha_ranges) and np.array_equal(g["verts"], cc.geom_interpol_verts)
+        out.update({name + "_Pt": cc.geom_Pt, name + "_alpha": cc.geom_alpha, name + "_ranges": cc.geom_alpha_ranges,
+                    name + "_verts": np.asarray(cc.geom_interpol_verts, dtype=np.int64)})
+        print(f"bar_geom {name}: port == reference; alpha={cc.geom_alpha[:8]} ranges={cc.geom_alpha_ranges}")
+    np.savez_compressed(os.path.join(GOLD, "bar_geom.npz"), **out)
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     load_reference()
-    make_meshes()
+    if "--geom-only" not in sys.argv:
+        make_meshes()
     with scratch_cwd():
         m = np.load(os.path.join(GOLD, "meshes.npz"))
         gv, gt = synth.grid_mesh(24, 20)
@@ -308,7 +344,10 @@ def main():
                  splocs=dict(max_itrs=3, admm=5, lam=2.0, rho=10.0), seed=0)
         pos_case("pos_sphere", m["sphere_verts"], m["sphere_tris"].astype(np.int64), F=30, K=12, n_bumps=6, sigma=0.2,
                  splocs=dict(max_itrs=2, admm=10, lam=2.0, rho=10.0), seed=1)
+        if "--geom-only" in sys.argv:          # the other fixtures are committed; only (re)write bar_geom.npz
+            return bar_geom_case()
         bar_case()
+        bar_geom_case()
         align_case()
         writers_case()
 

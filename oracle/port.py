@@ -445,6 +445,55 @@ def deim_blocks(comps, p):
     return dict(Pt=np.array(Pt), alpha=np.array(alphas), alpha_ranges=np.array(ranges), idxs=np.array(idxs))
 
 
+def elements_per_vert(v, elems):
+    """utils/support.py:210-257 (get_triangles/tetrahedrons/edges_per_vert): ascending ids of the elements containing v."""
+    return [int(i) for i in np.nonzero((np.asarray(elems) == v).any(axis=1))[0]]
+
+
+def deim_geom(comps, p, e, elems, St=None, ele_per_vert=1):
+    """snapbases/constraintsComponents.py:619-731 (geom_block_form_utilizing_differential_operator), element types whose
+    incident-element query is get_*_per_vert.  comps (K p, ep, 3).  St (|V| x ep, sparse or dense) given: error measured in
+    position space (error_in_pos_space=True: worst VERTEX, up to ele_per_vert new incident elements per step, rectangular
+    least squares on V[Pt]); St None: error in constraint space (worst ELEMENT by block energy, :86-96).
+    Returns dict(Pt, alpha, alpha_ranges, verts) or None on a zero residual (:676-678)."""
+    bases = comps.swapaxes(0, 1)                       # (ep, Kp, 3)
+    K = comps.shape[0] // p
+    Pt, e_points, e_jump, e_range, verts = [], [], [], [], []
+    V = None
+    for k in range(K):
+        vk = bases[:, k * p:(k + 1) * p, :]
+        if k == 0:
+            r = vk
+        else:
+            c = np.empty(vk.shape)
+            for i in range(3):
+                c[:, :, i] = V[:, :, i] @ np.linalg.lstsq(V[Pt, :, i], vk[Pt, :, i], rcond=None)[0]
+            r = c - vk
+        if St is not None:
+            r = St @ r.reshape(r.shape[0], -1)          # (|V|, p * 3)
+        if k > 0 and np.allclose(r, np.zeros(r.shape)):
+            return None
+        if St is not None:
+            v = int(np.argmax((r ** 2).sum(axis=1)))
+            verts.append(v)
+            jump = 0
+            for alpha in elements_per_vert(v, elems):
+                if alpha not in e_points and jump < ele_per_vert:
+                    jump += 1
+                    e_points.append(alpha)
+                    Pt += [alpha * p + m for m in range(p)]
+            e_jump.append(jump)
+        else:
+            alpha = index_largest_deformation(r, p, e)
+            assert alpha not in e_points
+            e_points.append(alpha)
+            Pt += [alpha * p + m for m in range(p)]
+            e_jump.append(1)
+        e_range.append(int(sum(e_jump)))
+        V = vk if k == 0 else np.concatenate((V, vk), axis=1)
+    return dict(Pt=np.array(Pt), alpha=np.array(e_points), alpha_ranges=np.array(e_range), verts=np.array(verts))
+
+
 def deim_reconstruct(comps, frames, Pt_rows, r, p_block=1):
     """snapbases/constraintsComponents.py:489-521 (`geom_constructed`) for an explicit row set:
     per-dimension normal-equation solve on the selected rows, then expansion with the full basis."""

@@ -18,5 +18,6 @@ assert comm.world == 2
 ops = NumpyOps()
 pipeline_checks.check_positions(ops, comm, "pos_grid")
 pipeline_checks.check_bar(ops, comm)
+pipeline_checks.check_bar_geom(ops, comm)
 print(f"RANK{comm.rank} OK", flush=True)
 dist.destroy_process_group()

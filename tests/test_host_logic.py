@@ -89,6 +89,11 @@ def test_bar_pod_per_row_host_logic():
     assert pipeline_checks.check_bar_pod_per_row(NumpyOps(), engine.Comm(enabled=False))
 
 
+def test_bar_geometric_deim_host_logic():
+    """engine.deim_geom over the numpy statement of the kernels == the reference's picks (tests/golden/bar_geom.npz)."""
+    assert pipeline_checks.check_bar_geom(NumpyOps(), engine.Comm(enabled=False))
+
+
 def test_two_rank_gloo_row_sharding():
     """world_size 2 over gloo: sharded deflation + SPLOCS + POD + DEIM reproduce the single-process golden results."""
     env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29613", PYTHONPATH=ROOT + os.pathsep + os.path.join(ROOT, "tests"))

@@ -68,6 +68,19 @@ def test_port_align_and_writers():
     assert port.points_bin_bytes(w["pts"]) == w["pts_bin"].tobytes()
 
 
+def test_port_geometric_deim_golden():
+    """oracle/port.py::deim_geom against the picks of the unmodified reference (constraintsComponents.py:619-731)."""
+    from scipy import sparse
+    b, g = golden("bar"), golden("bar_geom")
+    tets = b["tets"].astype(np.int64)
+    St = sparse.csr_matrix((g["St_vals"], g["St_colidx"], g["St_rowptr"]), shape=tuple(g["St_shape"]))
+    for name, comps, pos, per_vert in (("blk_pos2", b["blk_post"], True, 2), ("pod_pos1", b["post_comps"][:24], True, 1),
+                                       ("pod_pos3", b["post_comps"][:24], True, 3), ("pod_con", b["post_comps"][:24], False, 1)):
+        out = port.deim_geom(comps, 3, len(tets), tets, St if pos else None, per_vert)
+        assert np.array_equal(out["Pt"], g[name + "_Pt"]) and np.array_equal(out["alpha"], g[name + "_alpha"])
+        assert np.array_equal(out["alpha_ranges"], g[name + "_ranges"]) and np.array_equal(out["verts"], g[name + "_verts"])
+
+
 def test_port_against_live_reference():
     from oracle import ref_shim
     if not ref_shim.reference_available():

@@ -23,5 +23,6 @@ ops = CudaOps(f"cuda:{local}")
 pipeline_checks.check_positions(ops, comm, "pos_grid")
 pipeline_checks.check_positions(ops, comm, "pos_sphere")
 pipeline_checks.check_bar(ops, comm)
+pipeline_checks.check_bar_geom(ops, comm)
 print(f"RANK{comm.rank}/{comm.world} OK ({ops.launch_count()} launches)", flush=True)
 dist.destroy_process_group()
