@@ -624,6 +624,34 @@ def deim_geom(ops, comm, C, shard, p, elems, St=None, ele_per_vert=1):
     return dict(Pt=np.array(Pt), alpha=np.array(e_points), alpha_ranges=np.array(e_range), verts=np.array(verts, dtype=np.int64))
 
 
+def deim_reconstruct(ops, comm, C, X, shard, rows, rp):
+    """`geom_constructed` (snapbases/constraintsComponents.py:489-521): DEIM reconstruction of the frames
+    X (F, 3, ld) from their entries at the global rows `rows` (host ints) with the first rp basis rows of C (K, 3, ld):
+    per dimension l, coefficients = (A^T A)^-1 A^T X[:, rows, l] with A = V_r[rows, :, l] (normal equations by LU like the
+    reference's lu_factor / lu_solve; rp x rp, replicated), expansion rec[:, l, :] = coef^T C[:rp, l, :] on the DMMA pipe.
+    Returns rec (F, 3, ld) planar on the device."""
+    N, row0 = shard.n, shard.row0
+    F, _, ld = X.shape
+    dev = C.device
+    pt = torch.as_tensor(np.asarray(rows, dtype=np.int64), device=dev)
+    mine = (pt >= row0) & (pt < row0 + N)
+    A = torch.zeros((3, len(rows), rp), dtype=F64, device=dev)
+    B = torch.zeros((3, len(rows), F), dtype=F64, device=dev)
+    if bool(mine.any()):
+        loc = pt[mine] - row0
+        A[:, mine, :] = C[:rp][:, :, loc].permute(1, 2, 0)
+        B[:, mine, :] = X[:, :, loc].permute(1, 2, 0)
+    comm.allreduce_sum(A)
+    comm.allreduce_sum(B)
+    rec = ops.empty((F, 3, ld))
+    Cf = ops.zeros((F, (rp + 1) // 2 * 2))
+    for l in range(3):
+        coef = torch.linalg.solve(A[l].T @ A[l], A[l].T @ B[l])          # (rp, F)
+        Cf[:, :rp] = coef.T
+        ops.gemm_nn(Cf, F, rp, C[:rp, l, :], ld, 1.0, rec[:, l, :])
+    return rec
+
+
 # ====================================================================================== per-dimension Gram helpers
 def _plane(T, K, d):
     """(K, ld) view of dimension d of a planar (K, 3, ld) tensor (row stride 3*ld)."""

@@ -254,6 +254,32 @@ class constraintsComponents:  # Components == bases
         print("Computing interpolation elements utilizing differential operator, used", self.geom_alpha.shape[0],
               "constrained elements")
 
+    @log_time("")
+    def geom_constructed(self, r, case, interpol="geom"):
+        """DEIM reconstruction of the train / test frames from r interpolation elements (:489-521); returns the host
+        (F, ep, 3) array the figure scripts feed to the error statics.  Keeps the reference's row choice (geom_alpha, i.e.
+        element ids used as row ids unless constProj_snapshots_type == 'verts_bending', :507-512)."""
+        ops, comm = runtime.get()
+        snaps = self.nonlinearSnapshots
+        p = snaps.constraintsSize if self.param.constProj_bases_interpolation_type in ("geom", "deim_block_form") else 1
+        sh = snaps.shard
+        if case == "train":
+            X = snaps.state.X
+        elif case == "test":
+            rows = slice(sh.row0, sh.row0 + sh.n)
+            X = ops.ingest(ops.to_device(np.ascontiguousarray(snaps.test_snapTensor[:, rows])), None, sh.ld)
+        else:
+            raise ValueError("unknown frames to reconstruct.")
+        if getattr(self.param, "constProj_snapshots_type", "") == "verts_bending":
+            Pt = self.geom_Pt[:self.geom_alpha_ranges[r - 1]]
+        else:
+            Pt = self.geom_alpha[:self.geom_alpha_ranges[r - 1]]
+        rec = engine.deim_reconstruct(ops, comm, self._C, X, sh, Pt, r * p)
+        out = ops.export_aos(rec, None, sh.n).cpu().numpy()
+        if comm.world > 1:
+            out = engine.gather_rows_host(comm, out, sh, axis=1)
+        return out
+
     # ------------------------------------------------------------------ checks
     @log_time("")
     def test_basesSingVals(self):

@@ -19,5 +19,6 @@ ops = NumpyOps()
 pipeline_checks.check_positions(ops, comm, "pos_grid")
 pipeline_checks.check_bar(ops, comm)
 pipeline_checks.check_bar_geom(ops, comm)
+pipeline_checks.check_bar_reconstruction(ops, comm)
 print(f"RANK{comm.rank} OK", flush=True)
 dist.destroy_process_group()

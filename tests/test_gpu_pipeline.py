@@ -24,6 +24,10 @@ def test_bar_pod_per_row(cuda_ops):
     assert pipeline_checks.check_bar_pod_per_row(cuda_ops, engine.Comm(enabled=False))
 
 
+def test_bar_reconstruction(cuda_ops):
+    assert pipeline_checks.check_bar_reconstruction(cuda_ops, engine.Comm(enabled=False))
+
+
 def test_bar_geometric_deim(cuda_ops):
     assert pipeline_checks.check_bar_geom(cuda_ops, engine.Comm(enabled=False))
 

@@ -89,6 +89,10 @@ def test_bar_pod_per_row_host_logic():
     assert pipeline_checks.check_bar_pod_per_row(NumpyOps(), engine.Comm(enabled=False))
 
 
+def test_bar_reconstruction_host_logic():
+    assert pipeline_checks.check_bar_reconstruction(NumpyOps(), engine.Comm(enabled=False))
+
+
 def test_bar_geometric_deim_host_logic():
     """engine.deim_geom over the numpy statement of the kernels == the reference's picks (tests/golden/bar_geom.npz)."""
     assert pipeline_checks.check_bar_geom(NumpyOps(), engine.Comm(enabled=False))

@@ -24,5 +24,6 @@ pipeline_checks.check_positions(ops, comm, "pos_grid")
 pipeline_checks.check_positions(ops, comm, "pos_sphere")
 pipeline_checks.check_bar(ops, comm)
 pipeline_checks.check_bar_geom(ops, comm)
+pipeline_checks.check_bar_reconstruction(ops, comm)
 print(f"RANK{comm.rank}/{comm.world} OK ({ops.launch_count()} launches)", flush=True)
 dist.destroy_process_group()
