@@ -17,6 +17,8 @@
 //   12   Wide    one CTA per SM, 12 warps = 4 row-warps x 3 vertex groups (24 vertices, 72 columns); no room for U in
 //                registers (168 per thread): U goes through L2 every iteration       108.9 ms
 //   1216 Wide16  same, 16-column slabs                                               112.5 ms
+//   16   Tall    one CTA per SM, 16 warps = 8 row-warps x 2 vertex groups (<= 4 m-tiles per warp, 128 registers),
+//                U through L2                                                        105.2 ms
 // ASB_ADMM_LOCK=1 adds a per-SM epilogue mutex to the Pair layouts (keeps the two CTAs of an SM half a phase apart so one
 // runs the FP64 prox while the other owns the tensor pipe): 103.5 ms (4) / 104.6 ms (416) -- the two global atomics per
 // iteration cost what the overlap wins, so it is off by default.
@@ -33,10 +35,9 @@
 
 namespace asb {
 
-constexpr int ADMM_WM = 4;
-
-template <int WN_, bool UREG_, int CTAS_, int BK_, int STAGES_>
+template <int WN_, bool UREG_, int CTAS_, int BK_, int STAGES_, int WM_ = 4>
 struct AdmmCfg {
+    static constexpr int WM = WM_;                    // row-warps: the ceil(K/8) m-tiles are dealt to them
     static constexpr int WN = WN_;                    // vertex groups (8 vertices each) per CTA
     static constexpr bool UREG = UREG_;               // dual U in registers (else through L2 every iteration)
     static constexpr int CTAS = CTAS_;                // CTAs per SM
@@ -44,7 +45,7 @@ struct AdmmCfg {
     static constexpr int STAGES = STAGES_;            // cp.async ring depth
     static constexpr int ALD = BK + 4;                // 12 / 20 doubles: conflict-free 8x4 A-fragment reads
     static constexpr int CPR = BK / 2;                // 16-byte chunks per staged row
-    static constexpr int THREADS = ADMM_WM * WN * 32;
+    static constexpr int THREADS = WM * WN * 32;
     static constexpr int RPP = THREADS / CPR;         // Hr rows staged per pass of the CTA
     static constexpr int NV = 8 * WN;                 // vertices per tile
     static constexpr int NC = 24 * WN;                // columns per tile: [vertex group][plane][8 vertices]
@@ -54,6 +55,7 @@ using AdmmPair = AdmmCfg<1, true, 2, 8, 3>;      // 102 KB per CTA at K = 200
 using AdmmPair16 = AdmmCfg<1, true, 2, 16, 2>;   // 109 KB: half the barriers, one stage less
 using AdmmWide = AdmmCfg<3, false, 1, 8, 3>;     // 179 KB
 using AdmmWide16 = AdmmCfg<3, false, 1, 16, 3>;  // 218 KB
+using AdmmTall = AdmmCfg<2, false, 1, 8, 3, 8>;  // 141 KB: 8 row-warps x 2 vertex groups = 16 warps, <= 4 m-tiles per warp
 
 // Epilogue mutex, one per SM (Pair layout).  Two identical co-resident CTAs that share the DMMA pipe fall into lock-step
 // (a CTA that is ahead runs its GEMM phase at half rate while the one behind catches up during the leader's epilogue:
@@ -106,9 +108,9 @@ __device__ __forceinline__ void admm_body(double* smem, const double* __restrict
 
     // Hr slab stager: chunk t of a thread = row tid / CPR + RPP t, doubles (tid % CPR) * 2 .. +1 of the slab.  Hr is padded
     // by the caller (zeros) to whole slabs, so no chunk needs a column test, and the NFULL passes that end below
-    // 32 (MT - 1) < rows8 need no row test either; the remaining one or two passes use a mask computed once.
-    constexpr int NCH = (32 * MT + RPP - 1) / RPP;
-    constexpr int NFULL = (32 * (MT - 1)) / RPP;
+    // 8 WM (MT - 1) < rows8 need no row test either; the remaining one or two passes use a mask computed once.
+    constexpr int NCH = (8 * Cfg::WM * MT + RPP - 1) / RPP;
+    constexpr int NFULL = (8 * Cfg::WM * (MT - 1)) / RPP;
     static_assert(NCH - NFULL <= 4, "tail passes");
     const int srow = threadIdx.x / ADMM_CPR, scc = (threadIdx.x % ADMM_CPR) * 2;
     unsigned tailmask = 0;
@@ -227,7 +229,8 @@ __device__ __forceinline__ void admm_body(double* smem, const double* __restrict
                 const int k = (mt0 + i) * 8 + lr;
                 lam[i] = (inb && k < K) ? ld2(Lambda + (int64_t)k * ld + n) : make_double2(0.0, 0.0);
             }
-            constexpr int UDEPTH = UREG ? 1 : (MTN < 3 ? MTN : 3);
+            constexpr int UDMAX = Cfg::THREADS > 384 ? 2 : 3;   // 128-register cap at 512 threads
+            constexpr int UDEPTH = UREG ? 1 : (MTN < UDMAX ? MTN : UDMAX);
             double2 uo[UDEPTH][3];
             auto fetch_u = [&](int i) {
                 const int k = (mt0 + i) * 8 + lr;
@@ -298,9 +301,9 @@ admm_solve_kernel(const double* __restrict__ Hr, int64_t ldh, const double* __re
         // co-resident CTAs (blockIdx.x and blockIdx.x + #SMs under round-robin placement) rotate the row-warp roles by two
         // sub-partitions, so the 7-tile warps of the two CTAs sit on different SM sub-partitions (13,12,13,12, not 14,12,12,12)
         const int slot = (blockIdx.x / max(1u, gridDim.x / 2)) & 1;
-        wm = (wm + 2 * slot) % ADMM_WM;
+        wm = (wm + 2 * slot) % Cfg::WM;
     }
-    mtile_range(((K + 7) & ~7) >> 3, ADMM_WM, wm, mt0, mtn);
+    mtile_range(((K + 7) & ~7) >> 3, Cfg::WM, wm, mt0, mtn);
     const bool live = mtn > 0;   // K <= 24: some row-warps own no m-tile; they idle on tile 0 and never store
     if (!live) mt0 = 0;
     if (mtn == MT) admm_body<Cfg, MT, MT>(smem, Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live, lock);
@@ -338,17 +341,31 @@ static int launch_admm_cfg(const double* Hr, int64_t ldh, const double* B0, doub
     return ASB_OK;
 }
 
-template <int MT>
+// m-tiles per row-warp decide the instantiation (accumulator registers): 1..8 with 4 row-warps, 1..4 with 8
+template <class Cfg>
+static int launch_admm_layout(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda,
+                              int64_t K, int64_t N, int64_t ld, double inv_rho, int iters, cudaStream_t st) {
+    constexpr int MTMAX = 32 / Cfg::WM;   // K <= 256
+    switch ((int)cdiv(cdiv(K, 8), Cfg::WM)) {
+#define ASB_ADMM_CASE(MT) case MT: return launch_admm_cfg<Cfg, (MT <= MTMAX ? MT : MTMAX)>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+        ASB_ADMM_CASE(1) ASB_ADMM_CASE(2) ASB_ADMM_CASE(3) ASB_ADMM_CASE(4) ASB_ADMM_CASE(5) ASB_ADMM_CASE(6) ASB_ADMM_CASE(7)
+        default: return launch_admm_cfg<Cfg, MTMAX>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+#undef ASB_ADMM_CASE
+    }
+}
+
 static int launch_admm(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda,
                        int64_t K, int64_t N, int64_t ld, double inv_rho, int iters, cudaStream_t st) {
-    static const int layout = env_int("ASB_ADMM_LAYOUT", ASB_ADMM_LAYOUT_DEFAULT);   // 12 / 1216: Wide, 4 / 416: Pair
+    static const int layout = env_int("ASB_ADMM_LAYOUT", ASB_ADMM_LAYOUT_DEFAULT);   // 4 / 416: Pair, 12 / 1216: Wide, 16: Tall
     constexpr size_t SMEM_MAX = 227 * 1024;   // a layout whose tile does not fit at this K falls through to Pair (139 KB at K = 256)
+    if (layout == 16 && admm_smem_bytes<AdmmTall>(K) <= SMEM_MAX)
+        return launch_admm_layout<AdmmTall>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
     if (layout == 12 && admm_smem_bytes<AdmmWide>(K) <= SMEM_MAX)
-        return launch_admm_cfg<AdmmWide, MT>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+        return launch_admm_layout<AdmmWide>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
     if (layout == 1216 && admm_smem_bytes<AdmmWide16>(K) <= SMEM_MAX)
-        return launch_admm_cfg<AdmmWide16, MT>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
-    if (layout == 416) return launch_admm_cfg<AdmmPair16, MT>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
-    return launch_admm_cfg<AdmmPair, MT>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+        return launch_admm_layout<AdmmWide16>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+    if (layout == 416) return launch_admm_layout<AdmmPair16>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+    return launch_admm_layout<AdmmPair>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
 }
 
 }  // namespace asb
@@ -367,12 +384,7 @@ int asb_admm_solve(const double* Hr, int64_t ldh, const double* B0, double* Z, d
     if (iters == 0) return ASB_OK;
     const cudaStream_t st = S(stream);
     const int it = (int)iters;
-    switch ((int)cdiv(cdiv(K, 8), ADMM_WM)) {  // m-tiles per row-warp
-#define ASB_ADMM_CASE(MT) case MT: return launch_admm<MT>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, it, st);
-        ASB_ADMM_CASE(1) ASB_ADMM_CASE(2) ASB_ADMM_CASE(3) ASB_ADMM_CASE(4) ASB_ADMM_CASE(5) ASB_ADMM_CASE(6) ASB_ADMM_CASE(7)
-        default: return launch_admm<8>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, it, st);
-#undef ASB_ADMM_CASE
-    }
+    return launch_admm(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, it, st);
 }
 
 int asb_admm_iter(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda, int64_t K,

@@ -111,9 +111,11 @@ __global__ void __launch_bounds__(256) mf_backward_kernel(const FrontDesc* __res
         }
         __syncthreads();
         if (col < n1) {
+            // rows r < col of the own block hold stored zeros (L11^-1 is lower triangular): no skip test, so that the
+            // strided loads of four rows are in flight together (the top fronts have 32..128 CTAs: latency, not bandwidth)
+#pragma unroll 4
             for (int j = ty; j < len; j += 8) {
                 const int r = rb0 + j;
-                if (r < n1 && r < col) continue;
                 const long long srow = r < n1 ? r : d.row2 + (r - n1);
                 acc = fma(mp[srow * d.ldm], vs[j], acc);
             }
