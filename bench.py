@@ -46,7 +46,7 @@ def parse():
     ap.add_argument("--leaf-size", type=int, default=64, help="nested-dissection leaf size of the geodesic factorisation")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-sample", type=int, nargs=5, default=[120, 100, 120, 24, 2],
+    ap.add_argument("--cpu-sample", type=int, nargs=5, default=[160, 120, 140, 28, 2],
                     help="CPU baseline sample: nx ny frames comps splocs_iters")
     return ap.parse_args()
 
