@@ -177,21 +177,23 @@ __device__ __forceinline__ void admm_body(double* smem, const double* __restrict
         }
 
         int cs = 0;
-        for (int it = 0; it < iters; ++it) {
-            // accumulators start at B0 (C = B0 + Hr D): the L2 loads are all in flight before the first slab is consumed
-            double acc[MTN][3][2];
+        // accumulators start at B0 (C = B0 + Hr D).  First iteration: loaded here (in flight while the first slab lands);
+        // later iterations: re-loaded in the epilogue as soon as an m-tile's accumulators have been consumed, so the L2
+        // latency hides behind the rest of the epilogue instead of standing in front of the first DMMA.
+        double acc[MTN][3][2];
+        auto load_b0 = [&](int i) {
+            const int k = (mt0 + i) * 8 + lr;
 #pragma unroll
-            for (int i = 0; i < MTN; ++i) {
-                const int k = (mt0 + i) * 8 + lr;
-#pragma unroll
-                for (int d = 0; d < 3; ++d) {
-                    double2 b0 = make_double2(0.0, 0.0);
-                    if (inb && k < K) b0 = ld2(B0 + (int64_t)k * C3 + (int64_t)d * ld + n);
-                    acc[i][d][0] = b0.x;
-                    acc[i][d][1] = b0.y;
-                }
+            for (int d = 0; d < 3; ++d) {
+                double2 b0 = make_double2(0.0, 0.0);
+                if (inb && k < K) b0 = ld2(B0 + (int64_t)k * C3 + (int64_t)d * ld + n);
+                acc[i][d][0] = b0.x;
+                acc[i][d][1] = b0.y;
             }
-
+        };
+#pragma unroll
+        for (int i = 0; i < MTN; ++i) load_b0(i);
+        for (int it = 0; it < iters; ++it) {
             for (int s = 0; s < nslab; ++s) {
                 cp_async_wait<ADMM_STAGES - 2>();
                 __syncthreads();  // slab landed; previous stage free; D writes of the previous epilogue / tile load visible
@@ -255,6 +257,7 @@ __device__ __forceinline__ void admm_body(double* smem, const double* __restrict
                     v[d].y = acc[i][d][1] + (UREG ? u[i % UR][d][1] : uo[i % UDEPTH][d].y);
                 }
                 if (!UREG && i + UDEPTH < MTN) fetch_u(i + UDEPTH);   // slot i % UDEPTH is free again
+                if (!last) load_b0(i);                                // acc[i] is consumed: start the next iteration's C = B0 + ...
                 if (on) {
                     const double sh0 = prox_shrink(v[0].x, v[1].x, v[2].x, lam[i].x, inv_rho);
                     const double sh1 = prox_shrink(v[0].y, v[1].y, v[2].y, lam[i].y, inv_rho);
