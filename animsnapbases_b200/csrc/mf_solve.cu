@@ -30,15 +30,10 @@ __device__ __forceinline__ double gather_children(const int32_t* __restrict__ sr
 }
 
 // grid.x = work item (front, first row), grid.y = right-hand side.  256 threads = 8 warps x 4 rows.
-__global__ void __launch_bounds__(256) mf_forward_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
-                                                        const int32_t* __restrict__ src, int64_t slots,
-                                                        const int32_t* __restrict__ work, const double* __restrict__ rhs,
-                                                        double* __restrict__ y, double* __restrict__ upd, int64_t ldx,
-                                                        int64_t ldu) {
-    __shared__ double fs[MF_CHUNK];
-    const FrontDesc d = desc[work[2 * blockIdx.x]];
-    const int r0 = work[2 * blockIdx.x + 1];
-    const int64_t b = blockIdx.y;
+__device__ __forceinline__ void mf_forward_block(const FrontDesc& d, const int r0, const int64_t b, double* fs,
+                                                 const double* __restrict__ vals, const int32_t* __restrict__ src,
+                                                 int64_t slots, const double* __restrict__ rhs, double* __restrict__ y,
+                                                 double* __restrict__ upd, int64_t ldx, int64_t ldu) {
     const double* rb = rhs + b * ldx + d.own_start;
     double* ub = upd + b * ldu;
     const int32_t* src0 = src + d.slot_off;
@@ -82,6 +77,51 @@ __global__ void __launch_bounds__(256) mf_forward_kernel(const FrontDesc* __rest
                 ub[d.upd_off + (r - n1)] = gather_children(src0, src1, ub, r) + s;
         }
     }
+}
+
+__global__ void __launch_bounds__(256) mf_forward_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
+                                                        const int32_t* __restrict__ src, int64_t slots,
+                                                        const int32_t* __restrict__ work, const double* __restrict__ rhs,
+                                                        double* __restrict__ y, double* __restrict__ upd, int64_t ldx,
+                                                        int64_t ldu) {
+    __shared__ double fs[MF_CHUNK];
+    const FrontDesc d = desc[work[2 * blockIdx.x]];
+    mf_forward_block(d, work[2 * blockIdx.x + 1], blockIdx.y, fs, vals, src, slots, rhs, y, upd, ldx, ldu);
+}
+
+// Forward pass of a DELTA right-hand side: only the fronts on the path from the source's front to the root see a
+// non-zero vector (everything else of y and upd stays at its memset zero), so a level is at most one front per
+// right-hand side.  pathfront[b][level] = that front or -1 (mf_path_kernel); grid.x = row blocks of the largest front of
+// the level, grid.y = right-hand side.
+__global__ void __launch_bounds__(256) mf_forward_path_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
+                                                             const int32_t* __restrict__ src, int64_t slots,
+                                                             const int32_t* __restrict__ pathfront, int level, int nlevels,
+                                                             const double* __restrict__ rhs, double* __restrict__ y,
+                                                             double* __restrict__ upd, int64_t ldx, int64_t ldu) {
+    __shared__ double fs[MF_CHUNK];
+    const int f = pathfront[(int64_t)blockIdx.y * nlevels + level];
+    if (f < 0) return;
+    const FrontDesc d = desc[f];
+    const int r0 = blockIdx.x * MF_ROWS;
+    if (r0 >= d.n1 + d.n2) return;
+    mf_forward_block(d, r0, blockIdx.y, fs, vals, src, slots, rhs, y, upd, ldx, ldu);
+}
+
+// One thread per right-hand side: unit entry at the source's elimination position, and the chain of fronts above it.
+__global__ void mf_path_kernel(const int64_t* __restrict__ idx, const int32_t* __restrict__ order,
+                               const int64_t* __restrict__ fstart, const int32_t* __restrict__ parent,
+                               const int32_t* __restrict__ depth, int64_t nfronts, int nlevels, int nrhs,
+                               int32_t* __restrict__ pathfront, double* __restrict__ rp, int64_t ldx) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nrhs) return;
+    const int64_t p = order[idx[b]];
+    int64_t lo = 0, hi = nfronts - 1;           // last front with fstart <= p (fronts are stored in elimination order)
+    while (lo < hi) {
+        const int64_t mid = (lo + hi + 1) >> 1;
+        if (fstart[mid] <= p) lo = mid; else hi = mid - 1;
+    }
+    rp[(int64_t)b * ldx + p] = 1.0;
+    for (int f = (int)lo; f >= 0; f = parent[f]) pathfront[(int64_t)b * nlevels + depth[f]] = f;
 }
 
 // grid.x = work item (front, first column), grid.y = right-hand side.  256 threads = 32 columns x 8 row groups.
@@ -497,6 +537,35 @@ int asb_mf_solve(const int64_t* desc, const double* vals, const int32_t* src, in
         const int rc = asb_mf_forward(desc, vals, src, slots, reinterpret_cast<const int32_t*>(levels[4 * l]), levels[4 * l + 1], rhs,
                                       y, upd, nrhs, ldx, ldu, stream);
         if (rc != ASB_OK) return rc;
+    }
+    for (int64_t l = 0; l < nlevels; ++l) {
+        const int rc = asb_mf_backward(desc, vals, bnd, reinterpret_cast<const int32_t*>(levels[4 * l + 2]), levels[4 * l + 3], y, x,
+                                       nrhs, ldx, stream);
+        if (rc != ASB_OK) return rc;
+    }
+    return ASB_OK;
+}
+
+int asb_mf_solve_delta(const int64_t* desc, const double* vals, const int32_t* src, int64_t slots, const int32_t* bnd,
+                       const int64_t* levels, int64_t nlevels, const int64_t* maxblk, const int64_t* fstart,
+                       const int32_t* parent, const int32_t* depth, int64_t nfronts, const int32_t* order, const int64_t* idx,
+                       int32_t* pathfront, double* rp, double* y, double* x, double* upd, int64_t nrhs, int64_t ldx,
+                       int64_t ldu, asb_stream_t stream) {
+    ASB_REQUIRE(desc && vals && src && bnd && levels && maxblk && fstart && parent && depth && order && idx && pathfront && rp &&
+                    y && x && upd && nlevels > 0 && nlevels < 4096 && nrhs > 0 && nrhs < 65536 && nfronts > 0,
+                "mf_solve_delta: bad arguments");
+    const cudaStream_t st = S(stream);
+    ASB_CUDA(cudaMemsetAsync(rp, 0, sizeof(double) * nrhs * ldx, st));
+    ASB_CUDA(cudaMemsetAsync(y, 0, sizeof(double) * nrhs * ldx, st));
+    ASB_CUDA(cudaMemsetAsync(upd, 0, sizeof(double) * nrhs * ldu, st));
+    ASB_CUDA(cudaMemsetAsync(pathfront, 0xFF, sizeof(int32_t) * nrhs * nlevels, st));
+    mf_path_kernel<<<(unsigned)cdiv(nrhs, 64), 64, 0, st>>>(idx, order, fstart, parent, depth, nfronts, (int)nlevels, (int)nrhs,
+                                                           pathfront, rp, ldx);
+    ASB_LAUNCH_CHECK();
+    for (int64_t l = nlevels - 1; l >= 0; --l) {
+        mf_forward_path_kernel<<<dim3((unsigned)maxblk[l], (unsigned)nrhs), 256, 0, st>>>(
+            reinterpret_cast<const FrontDesc*>(desc), vals, src, slots, pathfront, (int)l, (int)nlevels, rp, y, upd, ldx, ldu);
+        ASB_LAUNCH_CHECK();
     }
     for (int64_t l = 0; l < nlevels; ++l) {
         const int rc = asb_mf_backward(desc, vals, bnd, reinterpret_cast<const int32_t*>(levels[4 * l + 2]), levels[4 * l + 3], y, x,

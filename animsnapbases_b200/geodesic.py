@@ -122,9 +122,7 @@ class HeatGeodesics:
         minimum (asb_support_map does that, utils/support.py:206)."""
         ops, n = self.ops, self.n
         B = idx_dev.numel()
-        rhs = ops.empty((B, self.ldx))
-        ops.delta_rhs(idx_dev, n, rhs)
-        u = self.heat.solve(rhs)
+        u = self.heat.solve_delta(idx_dev)            # heat step from a delta source: forward pass along the tree path only
         Xt = ops.empty((B, self.T, 3))
         div = ops.zeros((B, self.ldx))
         ops.heat_divergence(u, self.tri, self.gconst, self.dconst, self.vc_ptr, self.vc_idx, n, Xt, div)

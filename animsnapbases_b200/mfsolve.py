@@ -341,6 +341,20 @@ class MultifrontalSolver:
         if hasattr(ops, "mf_solve"):
             self.levels_host = np.array([[wf.data_ptr(), wf.shape[0], wb.data_ptr(), wb.shape[0]]
                                          for wf, wb in zip(self.work_fwd, self.work_bwd)], dtype=np.int64)
+        # tree tables for asb_mf_solve_delta: parent / depth / first elimination position of every front, and the number
+        # of 32-row blocks of the largest front of every level
+        self.tree = None
+        if hasattr(ops, "mf_solve_delta"):
+            parent = np.full(sym.T, -1, dtype=np.int32)
+            for c in range(2):
+                has = sym.children[:, c] >= 0
+                parent[sym.children[has, c]] = np.nonzero(has)[0]
+            nn = sym.n1 + sym.n2
+            nlev = len(sym.levels)
+            self.maxblk_host = np.array([int(((nn[sym.depth == d] + ROWS_PER_BLOCK - 1) // ROWS_PER_BLOCK).max())
+                                         for d in range(nlev)], dtype=np.int64)
+            self.tree = (ops.to_device(sym.start.astype(np.int64)), ops.to_device(parent),
+                         ops.to_device(sym.depth.astype(np.int32)))
         self.upd_len = (sym.upd_len + 31) // 32 * 32 + 32
         self.slots = sym.src.shape[1]
         self.stats = {"fronts": sym.T, "levels": len(sym.levels), "operator_bytes": int(sym.vals_len) * 8}
@@ -360,6 +374,25 @@ class MultifrontalSolver:
         for w in self.work_bwd:
             ops.mf_backward(self.desc, self.vals, self.bnd, w, y, x)
         return x
+
+    def solve_delta(self, idx_dev):
+        """A^-1 e_i for the B source vertices idx_dev (int64, device), in vertex order: (B, ldx).  The forward pass only
+        walks the tree paths above the sources (asb_mf_solve_delta); the grounded variant is not needed (heat system)."""
+        ops = self.ops
+        if self.tree is None or self.ground is not None:
+            rhs = ops.empty((idx_dev.numel(), self.ldx))
+            ops.delta_rhs(idx_dev, self.n, rhs)
+            return self.solve(rhs)
+        B = idx_dev.numel()
+        fstart, parent, depth = self.tree
+        rp, y, xp = ops.empty((B, self.ldx)), ops.empty((B, self.ldx)), ops.empty((B, self.ldx))
+        upd = ops.empty((B, self.upd_len))
+        pathfront = torch.empty((B, len(self.work_fwd)), dtype=torch.int32, device=rp.device)
+        ops.mf_solve_delta(self.desc, self.vals, self.src, self.slots, self.bnd, self.levels_host, self.maxblk_host, fstart, parent,
+                           depth, self.order, idx_dev, pathfront, rp, y, xp, upd)
+        out = ops.zeros((B, self.ldx))
+        ops.gather_rows(xp, self.order, out, self.n)
+        return out
 
     def solve(self, rhs):
         """rhs: (B, ldx) in vertex order -> A^-1 rhs in vertex order (grounded unknown = 0)."""

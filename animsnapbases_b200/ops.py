@@ -349,6 +349,14 @@ class CudaOps:
                    ctypes.c_void_p(levels_host.ctypes.data), levels_host.shape[0], self._p(rhs), self._p(y), self._p(x), self._p(upd),
                    rhs.shape[0], rhs.stride(0), upd.stride(0))
 
+    def mf_solve_delta(self, desc, vals, src, slots, bnd, levels_host, maxblk_host, fstart, parent, depth, order, idx, pathfront,
+                       rp, y, x, upd):
+        """asb_mf_solve for unit right-hand sides at the source vertices `idx` (forward pass along the tree paths only)."""
+        self._call("asb_mf_solve_delta", self._p(desc), self._p(vals), self._p(src), slots, self._p(bnd),
+                   ctypes.c_void_p(levels_host.ctypes.data), levels_host.shape[0], ctypes.c_void_p(maxblk_host.ctypes.data),
+                   self._p(fstart), self._p(parent), self._p(depth), fstart.numel(), self._p(order), self._p(idx),
+                   self._p(pathfront), self._p(rp), self._p(y), self._p(x), self._p(upd), idx.numel(), rp.stride(0), upd.stride(0))
+
     def heat_divergence(self, u, tri, gconst, dconst, vc_ptr, vc_idx, n, Xt, div):
         nrhs, ldx = u.shape
         self._call("asb_heat_divergence", self._p(u), nrhs, ldx, self._p(tri), self._p(gconst), self._p(dconst), tri.shape[0],

@@ -216,7 +216,7 @@ def main():
     sync_all()
     # ---- timed region (device-resident inputs)
     timed = ["asb_deflate_gemv", "asb_rank_update", "asb_admm_solve", "asb_gemm_nn", "asb_gemm_nt", "asb_weights_sweep",
-             "asb_component_centers", "asb_mf_solve", "asb_support_map", "asb_vertex_energy"]
+             "asb_component_centers", "asb_mf_solve", "asb_mf_solve_delta", "asb_support_map", "asb_vertex_energy"]
     ops.time_kernels(timed)
     ops.reset_launch_count()
     clocks = ClockSampler(local_rank)

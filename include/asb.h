@@ -233,6 +233,16 @@ int asb_mf_backward(const int64_t* desc, const double* vals, const int32_t* bnd,
 int asb_mf_solve(const int64_t* desc, const double* vals, const int32_t* src, int64_t slots, const int32_t* bnd,
                  const int64_t* levels, int64_t nlevels, const double* rhs, double* y, double* x, double* upd, int64_t nrhs,
                  int64_t ldx, int64_t ldu, asb_stream_t stream);
+/* asb_mf_solve for right-hand sides that are unit vectors (the heat-method query, utils/support.py:182: u0 = delta at
+ * the source): the forward pass only visits the fronts between the source's front and the root.  idx: nrhs source
+ * vertices (device); order: vertex -> elimination position; fstart / parent / depth: first elimination position, parent
+ * front (-1 = root) and tree depth of every front; maxblk: HOST array, 32-row blocks of the largest front per level;
+ * pathfront: nrhs x nlevels int32 scratch; rp / y / upd: work vectors (zeroed here); x: solution in elimination order. */
+int asb_mf_solve_delta(const int64_t* desc, const double* vals, const int32_t* src, int64_t slots, const int32_t* bnd,
+                       const int64_t* levels, int64_t nlevels, const int64_t* maxblk, const int64_t* fstart,
+                       const int32_t* parent, const int32_t* depth, int64_t nfronts, const int32_t* order, const int64_t* idx,
+                       int32_t* pathfront, double* rp, double* y, double* x, double* upd, int64_t nrhs, int64_t ldx,
+                       int64_t ldu, asb_stream_t stream);
 /* out[b][i] = in[b][map[i]], i < n  (permutation to / from elimination order). */
 int asb_gather_rows(const double* in, const int32_t* map, double* out, int64_t n, int64_t nrhs, int64_t ldin, int64_t ldout,
                     asb_stream_t stream);

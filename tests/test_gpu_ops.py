@@ -455,6 +455,11 @@ def test_multifrontal_solve(cuda_ops, nx, ny, leaf, ground, B):
         assert ref.min() > 0
         err = np.max(np.abs(x - ref) / ref)
         assert err < 1e-11, f"componentwise relative error {err:.2e} (smallest value {ref.min():.1e})"
+        # unit right-hand sides through the tree-path forward pass (asb_mf_solve_delta)
+        src_idx = np.argmax(rhs[:, :n], axis=1).astype(np.int64)
+        xd = mf.solve_delta(cuda_ops.to_device(src_idx)).cpu().numpy()[:, :n]
+        errd = np.max(np.abs(xd - ref) / ref)
+        assert errd < 1e-11, f"delta solve: componentwise relative error {errd:.2e}"
     else:
         d = rng.standard_normal((B, n))
         rhs[:, :n] = d - d.mean(axis=1, keepdims=True)
