@@ -153,3 +153,93 @@ def write_components_animation(path, default_verts, tris, comps):
     out = _npz_sidecar(path)
     np.savez(out, default=default_verts, tris=tris, **{"comp%03d" % i: c for i, c in enumerate(comps)})
     return out
+
+
+# ------------------------------------------------------------------------------------------------ snapshot ingest (a1, n3)
+def load_off(filename, no_colors=False):
+    """OFF / COFF reader of utils/process.py:46-66: (verts (n, 3) float64, [colors uint8,] faces (m, k) int or None)."""
+    from io import StringIO
+    lines = [ln for ln in open(filename).readlines() if ln.strip() != "" and ln[0] != "#"]
+    assert lines[0].strip() in ["OFF", "COFF"], "OFF header missing"
+    has_colors = lines[0].strip() == "COFF"
+    n_verts, n_faces, _ = map(int, lines[1].split())
+    vertex_data = np.loadtxt(StringIO("".join(lines[2:2 + n_verts])), dtype=float, ndmin=2)
+    faces = np.loadtxt(StringIO("".join(lines[2 + n_verts:])), dtype=int, ndmin=2)[:, 1:] if n_faces > 0 else None
+    colors = None
+    if has_colors:
+        colors = vertex_data[:, 3:].astype(np.uint8)
+        vertex_data = vertex_data[:, :3]
+    return (vertex_data, faces) if no_colors else (vertex_data, colors, faces)
+
+
+def filter_reindex(condition, target):
+    """utils/process.py:94-106: indices `target` re-numbered after dropping the entries where `condition` is False."""
+    if condition.dtype != bool:
+        raise ValueError("condition must be a binary array")
+    return (np.cumsum(condition) - 1)[target]
+
+
+def preprocess_mesh_animation(verts, tris):
+    """utils/process.py:107-148: drop zero-area triangles (frame 0, |n| <= 1e-8), keep the largest connected component,
+    subtract the global mean and divide by the largest per-frame extent (-0.5 .. 0.5 cube; sets the scale of the support-map
+    distances).  The reference's `verts.ptp(axis=1)` (removed in numpy 2) is `max - min` over the vertices of each frame.
+    verts (F, N, 3) float, tris (T, 3) int -> (verts', tris', dropped-vertex mask, mean (3,), scale).  Host, once per dataset."""
+    from scipy.sparse import csr_matrix
+    from scipy.sparse.csgraph import connected_components
+    verts = np.array(verts, copy=True)
+    assert verts.ndim == 3 and tris.ndim == 2
+    e1 = verts[0, tris[:, 1]] - verts[0, tris[:, 0]]
+    e2 = verts[0, tris[:, 2]] - verts[0, tris[:, 0]]
+    tris = tris[np.linalg.norm(np.cross(e1, e2), axis=1) > 1.e-8]
+    ij = np.r_[np.c_[tris[:, 0], tris[:, 1]], np.c_[tris[:, 0], tris[:, 2]], np.c_[tris[:, 1], tris[:, 2]]]
+    G = csr_matrix((np.ones(len(ij)), ij.T), shape=(verts.shape[1], verts.shape[1]))
+    n_components, labels = connected_components(G, directed=False)
+    if n_components > 1:
+        size_components = np.bincount(labels)
+        print("[warning] found %d connected components in the mesh, keeping only the biggest one" % n_components)
+        print("component sizes: ")
+        print(size_components)
+        keep_vert = labels == size_components.argmax()
+    else:
+        keep_vert = np.ones(verts.shape[1], bool)
+    verts = verts[:, keep_vert, :]
+    tris = filter_reindex(keep_vert, tris[keep_vert[tris].all(axis=1)])
+    verts_mean = verts.mean(axis=0).mean(axis=0)
+    verts -= verts_mean
+    verts_scale = np.abs(verts.max(axis=1) - verts.min(axis=1)).max()
+    verts /= verts_scale
+    return verts, tris, ~keep_vert, verts_mean, verts_scale
+
+
+def convert_sequence_to_hdf5(filename_pattern, loader_function, hdf_output_file, max_frames, icreament):
+    """utils/process.py:68-92: a numbered sequence of mesh files -> one animation file (`verts` float32, `tris`, attributes
+    `mean`, `scale`).  Written as .h5 when h5py is present, otherwise as the `.npz` twin `read_animation` understands."""
+    import re
+    from glob import glob
+    files = glob(os.path.expanduser(filename_pattern))
+    files.sort(key=lambda s: [int(t) if t.isdigit() else t for t in re.split(r"([0-9]+)", s)])    # sort_nicely
+    verts_all, tris, count = [], None, 0
+    for i, f in enumerate(files):
+        if i % icreament == 0 and count < max_frames:
+            print("loading file %d/%d [%s]" % (i + 1, len(files), f))
+            verts, new_tris = loader_function(f)
+            if tris is not None and new_tris.shape != tris.shape:
+                raise ValueError("inconsistent topology between meshes of different frames")
+            tris = new_tris
+            verts_all.append(verts)
+            count += 1
+    verts_all = np.array(verts_all, np.float32)
+    verts_all, tris, _, verts_mean, verts_scale = preprocess_mesh_animation(verts_all, tris)
+    h5 = _h5py()
+    if h5 is not None and not hdf_output_file.endswith(".npz"):
+        with h5.File(hdf_output_file, "w") as f:
+            f.create_dataset("verts", data=verts_all, compression="gzip")
+            f["tris"] = tris
+            f.attrs["mean"] = verts_mean
+            f.attrs["scale"] = verts_scale
+        out = hdf_output_file
+    else:
+        out = _npz_sidecar(hdf_output_file)
+        np.savez(out, verts=verts_all, tris=tris, mean=verts_mean, scale=verts_scale)
+    print("saved as %s" % out)
+    return out

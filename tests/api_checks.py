@@ -163,6 +163,24 @@ def check_constraints_protocol(ops, comm, tmp):
             assert np.array_equal(pts, bases.geom_alpha[:k].astype(float))
         s = bases.test_basesSingVals()
         assert s.shape == (K, 3) and np.allclose(s, port.bases_sing_vals(bases.comps), atol=1e-7)
+        # reconstruction from r = K interpolation elements (generate_figures/nl_reduction_tests.py:117-150 -> :489-521)
+        rec = bases.geom_constructed(K, "train")
+        assert rec.shape == (F, ep, 3)
+        err = bases.frobenius_error(snaps.snapTensor, rec)
+        assert abs(err - float(b["deim_rec10_err"][0])) < 1e-6 * float(b["deim_rec10_err"][0])
+        # geometric DEIM through the differential operator (main.py:132-134): picks are a prefix of the reference's
+        from scipy import sparse
+        g = golden("bar_geom")
+        bases.St = sparse.csr_matrix((g["St_vals"], g["St_colidx"], g["St_rowptr"]), shape=tuple(g["St_shape"]))
+        snaps.tets, snaps.ele_type = b["tets"].astype(np.int64), "_tets"
+        bases.param.geom_ele_per_vert = 1
+        bases.numComp = K // 3                       # blocks of p = 3 rows
+        bases.geom_block_form_utilizing_differential_operator(True)
+        nb = K // 3
+        assert np.array_equal(bases.geom_alpha, g["pod_pos1_alpha"][:nb]) and np.array_equal(bases.geom_Pt, g["pod_pos1_Pt"][:3 * nb])
+        assert np.array_equal(bases.geom_interpol_verts, g["pod_pos1_verts"][:nb])
+        bases.geom_block_form_utilizing_differential_operator(False)
+        assert np.array_equal(bases.geom_alpha, g["pod_con_alpha"][:nb])
     finally:
         os.chdir(cwd)
         runtime.install(None, None)

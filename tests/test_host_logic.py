@@ -148,3 +148,34 @@ def test_constraints_components_protocol_host_logic(tmp_path):
     """nonlinearSnapshots / constraintsComponents drop-in protocol (main.py:106-142) with the numpy statement of the kernels."""
     import api_checks
     assert api_checks.check_constraints_protocol(NumpyOps(), engine.Comm(enabled=False), tmp_path)
+
+
+def test_preprocess_and_off_sequence_ingest(tmp_path):
+    """utils/process.py:46-148: OFF sequence -> preprocessed animation file.  The normalisation is checked
+    against the oracle restatement, the filtering (degenerate triangle, small disconnected component) structurally."""
+    from animsnapbases_b200 import hostio, synth
+    from oracle import port
+    v0, tris = synth.grid_mesh(6, 5)
+    n = len(v0)
+    island = np.array([[5.0, 5.0, 0.0], [5.1, 5.0, 0.0], [5.0, 5.1, 0.0]])          # second, smaller component
+    verts0 = np.concatenate([v0, island])
+    tris_all = np.concatenate([tris, [[n, n + 1, n + 2]], [[0, 0, 1]]])               # + one zero-area triangle
+    rng = np.random.default_rng(5)
+    frames = np.stack([verts0 + 0.01 * f * rng.standard_normal(verts0.shape) for f in range(4)]).astype(np.float32)
+    for f, fr in enumerate(frames):
+        with open(tmp_path / f"mesh_{f}.off", "w") as fh:
+            fh.write("OFF\n# comment\n%d %d 0\n" % (len(fr), len(tris_all)))
+            fh.writelines("%.9g %.9g %.9g\n" % tuple(p) for p in fr)
+            fh.writelines("3 %d %d %d\n" % tuple(t) for t in tris_all)
+    vv, ff = hostio.load_off(str(tmp_path / "mesh_2.off"), no_colors=True)
+    assert np.allclose(vv, frames[2], rtol=1e-6) and np.array_equal(ff, tris_all)
+    out = hostio.convert_sequence_to_hdf5(str(tmp_path / "mesh_*.off"), lambda p: hostio.load_off(p, no_colors=True),
+                                          str(tmp_path / "anim.h5"), max_frames=10, icreament=1)
+    verts, tr = hostio.read_animation(out)
+    assert verts.shape == (4, n, 3) and verts.dtype == np.float32, "the 3-vertex island is dropped"
+    assert np.array_equal(tr, tris), "degenerate and island triangles are dropped, indices unchanged for the kept block"
+    ref, mean, scale = port.preprocess_unit_cube(np.array([hostio.load_off(str(tmp_path / f"mesh_{f}.off"), True)[0][:n]
+                                                           for f in range(4)], np.float32))
+    assert np.array_equal(verts, ref)
+    ext = verts.max(axis=1) - verts.min(axis=1)
+    assert abs(ext.max() - 1.0) < 1e-6 and np.abs(verts.mean(axis=(0, 1))).max() < 1e-6
