@@ -98,14 +98,17 @@ def test_bar_geometric_deim_host_logic():
     assert pipeline_checks.check_bar_geom(NumpyOps(), engine.Comm(enabled=False))
 
 
-def test_two_rank_gloo_row_sharding():
-    """world_size 2 over gloo: sharded deflation + SPLOCS + POD + DEIM reproduce the single-process golden results."""
-    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29613", PYTHONPATH=ROOT + os.pathsep + os.path.join(ROOT, "tests"))
-    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
-                        "127.0.0.1", "--master-port", "29613", os.path.join(ROOT, "tests", "gloo_worker.py")],
-                       capture_output=True, text=True, env=env, timeout=600)
+@pytest.mark.parametrize("world", [2, 5])
+def test_two_rank_gloo_row_sharding(world):
+    """world_size 2 (and 5: uneven shards, the last ranks short or empty) over gloo: sharded deflation + SPLOCS (with the
+    geodesic all-to-all) + POD + DEIM + geometric DEIM + reconstruction reproduce the single-process golden results."""
+    port_no = str(29613 + world)
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=port_no, PYTHONPATH=ROOT + os.pathsep + os.path.join(ROOT, "tests"))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr",
+                        "127.0.0.1", "--master-port", port_no, os.path.join(ROOT, "tests", "gloo_worker.py")],
+                       capture_output=True, text=True, env=env, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    assert "RANK0 OK" in r.stdout and "RANK1 OK" in r.stdout
+    assert all(f"RANK{i} OK" in r.stdout for i in range(world))
 
 
 @pytest.mark.parametrize("nx,leaf,ground", [(40, 16, None), (40, 16, 3), (7, 64, None)])
