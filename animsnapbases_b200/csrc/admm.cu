@@ -19,6 +19,7 @@
 //   1216 Wide16  same, 16-column slabs                                               112.5 ms
 //   16   Tall    one CTA per SM, 16 warps = 8 row-warps x 2 vertex groups (<= 4 m-tiles per warp, 128 registers),
 //                U through L2                                                        105.2 ms
+//   8/81 Duo     two CTAs per SM of 8 row-warps x 1 vertex group (U through L2 / in registers)  115.7 / 106.8 ms
 // ASB_ADMM_LOCK=1 adds a per-SM epilogue mutex to the Pair layouts (keeps the two CTAs of an SM half a phase apart so one
 // runs the FP64 prox while the other owns the tensor pipe): 103.5 ms (4) / 104.6 ms (416) -- the two global atomics per
 // iteration cost what the overlap wins, so it is off by default.
@@ -56,6 +57,10 @@ using AdmmPair16 = AdmmCfg<1, true, 2, 16, 2>;   // 109 KB: half the barriers, o
 using AdmmWide = AdmmCfg<3, false, 1, 8, 3>;     // 179 KB
 using AdmmWide16 = AdmmCfg<3, false, 1, 16, 3>;  // 218 KB
 using AdmmTall = AdmmCfg<2, false, 1, 8, 3, 8>;  // 141 KB: 8 row-warps x 2 vertex groups = 16 warps, <= 4 m-tiles per warp
+using AdmmDuo = AdmmCfg<1, false, 2, 8, 3, 8>;   // 102 KB: two CTAs per SM of 8 row-warps x 1 vertex group (16 warps per SM in
+                                                 // two independent CTAs: one keeps 2 warps per sub-partition on the tensor pipe
+                                                 // while the other is in its epilogue), U through L2, 128 registers
+using AdmmDuoU = AdmmCfg<1, true, 2, 8, 3, 8>;   // same with U in registers
 
 // Epilogue mutex, one per SM (Pair layout).  Two identical co-resident CTAs that share the DMMA pipe fall into lock-step
 // (a CTA that is ahead runs its GEMM phase at half rate while the one behind catches up during the leader's epilogue:
@@ -363,6 +368,8 @@ static int launch_admm(const double* Hr, int64_t ldh, const double* B0, double* 
     constexpr size_t SMEM_MAX = 227 * 1024;   // a layout whose tile does not fit at this K falls through to Pair (139 KB at K = 256)
     if (layout == 16 && admm_smem_bytes<AdmmTall>(K) <= SMEM_MAX)
         return launch_admm_layout<AdmmTall>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+    if (layout == 8) return launch_admm_layout<AdmmDuo>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+    if (layout == 81) return launch_admm_layout<AdmmDuoU>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
     if (layout == 12 && admm_smem_bytes<AdmmWide>(K) <= SMEM_MAX)
         return launch_admm_layout<AdmmWide>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
     if (layout == 1216 && admm_smem_bytes<AdmmWide16>(K) <= SMEM_MAX)
