@@ -652,6 +652,58 @@ def deim_reconstruct(ops, comm, C, X, shard, rows, rp):
     return rec
 
 
+# ====================================================================================== consumer-side operators (8(f) n2)
+def reduced_group_operators(ops, comm, C, shard, rows, St):
+    """`prepare_reduced_group` (projective_dynamics/Simulators.py:157-218, reduced_position False) for one constraint group.
+    C (mp, 3, ld) planar: the first mp rows of the emitted basis, constraint rows sharded; rows: the interpolation rows Pt
+    (host ints, global); St (|V| x ep scipy sparse, replicated on the host).
+      * S^T V (:197 -- the reference densifies St): 3 mp sparse mat-vecs on this rank's columns (asb_spmv_csr),
+        partial products all-reduced -> StV (mp, 3, L) planar on the device, vertex rows replicated;
+      * A_d = V[Pt, :, d] (:205): row gather + all-reduce; A_d^T A_d + 1e-8 trace/mp I (:207-214) LU-factorised like
+        lu_factor (mp x mp, replicated, cuSOLVER through torch).
+    Returns a dict consumed by reduced_group_term."""
+    mp, _, ld = C.shape
+    N, row0 = shard.n, shard.row0
+    dev = C.device
+    csr, nv, L = square_csr_slice(ops, St, shard)
+    xb = ops.zeros((3 * mp, L))
+    StV = ops.zeros((mp, 3, L))
+    xb[:, :ld].copy_(C.reshape(3 * mp, ld))
+    ops.spmv(csr, xb, StV.view(3 * mp, L))
+    comm.allreduce_sum(StV)
+    pt = torch.as_tensor(np.asarray(rows, dtype=np.int64), device=dev)
+    mine = (pt >= row0) & (pt < row0 + N)
+    A = torch.zeros((3, len(rows), mp), dtype=F64, device=dev)
+    if bool(mine.any()):
+        A[:, mine, :] = C[:, :, pt[mine] - row0].permute(1, 2, 0)
+    comm.allreduce_sum(A)
+    AtA = A.transpose(1, 2) @ A                                          # (3, mp, mp)
+    la = 1e-8 * torch.diagonal(AtA, dim1=1, dim2=2).sum(dim=1) / mp
+    normal = AtA + la[:, None, None] * torch.eye(mp, dtype=F64, device=dev)
+    LU, piv = torch.linalg.lu_factor(normal)
+    return dict(StV=StV, nv=nv, L=L, A=A, normal=normal, LU=LU, piv=piv, mp=mp)
+
+
+def reduced_group_term(ops, grp, p_rows):
+    """`get_group_reduced_term` (projective_dynamics/Simulators.py:394-399): S^T V (A^T A + la I)^-1 A^T p per dimension for
+    a batch of projections p_rows (B, |Pt|, 3) (device or host) at the interpolation rows.  Returns (B, 3, L) planar on the
+    device (vertex n of dimension d at [:, d, n], n < grp['nv'])."""
+    mp, L, A = grp["mp"], grp["L"], grp["A"]
+    pr = torch.as_tensor(p_rows, dtype=F64, device=A.device)
+    if pr.dim() == 2:
+        pr = pr[None]
+    B = pr.shape[0]
+    rhs = A.transpose(1, 2) @ pr.permute(2, 1, 0)                        # (3, mp, B) = A_d^T p_d
+    coef = torch.linalg.lu_solve(grp["LU"], grp["piv"], rhs)             # (3, mp, B)
+    Bp = max(B, 3)
+    out = ops.zeros((Bp, 3, L))
+    Cf = ops.zeros((Bp, (mp + 1) // 2 * 2))
+    for d in range(3):
+        Cf[:B, :mp] = coef[d].T
+        ops.gemm_nn(Cf, Bp, mp, grp["StV"][:, d, :], L, 1.0, out[:, d, :])
+    return out[:B]
+
+
 # ====================================================================================== per-dimension Gram helpers
 def _plane(T, K, d):
     """(K, ld) view of dimension d of a planar (K, 3, ld) tensor (row stride 3*ld)."""

@@ -332,9 +332,70 @@ def bar_geom_case():
     np.savez_compressed(os.path.join(GOLD, "bar_geom.npz"), **out)
 
 
+# ------------------------------------------------------------------------------------------------ consumer side (n2)
+REDUCED_CASES = {   # name: (reduction type, components key, (Pt, alpha, ranges) keys, num_components)
+    "pod": ("deim_pod_vectorized", "post_comps", ("deim_Pt", "deim_alpha", "deim_ranges"), 10),
+    "blk": ("geom_pca_blocks_withSt", "blk_post", ("blk_pos2_Pt", "blk_pos2_alpha", "blk_pos2_ranges"), 4),
+}
+
+
+def bar_reduced_case():
+    """The reference's consumer of the emitted `.npz` (projective_dynamics/Simulators.py:157-218 prepare_reduced_group and
+    :366-399 get_group_reduced_term, unmodified, called unbound on a stand-in `self`) on the bar fixture's bases and
+    interpolation sets -> tests/golden/bar_reduced.npz.  Reads bar.npz / bar_geom.npz (does not regenerate them)."""
+    import tempfile
+    from scipy import sparse
+    from scipy.linalg import lu_solve
+    from oracle.ref_shim import load_pd_simulators
+    Solver = load_pd_simulators().animSnapBasesSolver
+
+    bar = np.load(os.path.join(GOLD, "bar.npz"))
+    geo = np.load(os.path.join(GOLD, "bar_geom.npz"))
+    St = sparse.csr_matrix((geo["St_vals"], geo["St_colidx"], geo["St_rowptr"]), shape=tuple(geo["St_shape"]))
+    p, group = 3, "tets_deformation_gradient"
+    fixtures = {**{k: bar[k] for k in bar.files}, **{k: geo[k] for k in geo.files}}
+    P = np.random.default_rng(11).standard_normal((St.shape[1], 3))          # stand-in constraint projections (ep, 3)
+
+    class Projection:                                                        # what get_pi returns for element alpha
+        def __init__(self, alpha):
+            self.alpha = alpha
+
+        def get_pi(self, q_t):
+            return P[self.alpha * p:(self.alpha + 1) * p]
+
+    constraints = [Projection(a) for a in range(St.shape[1] // p)]
+    out = dict(P=P)
+    for name, (rtype, ckey, (kpt, kal, krg), ncomp) in REDUCED_CASES.items():
+        local = dict(components=fixtures[ckey], interpol_alphas=fixtures[kal], Pt=fixtures[kpt],
+                     interpol_verts=np.zeros(0, dtype=np.int64), interpol_alpha_ranges=fixtures[krg])
+        me = types.SimpleNamespace(constraint_projection_reduction_type=rtype, reduced_position=False)
+        with tempfile.TemporaryDirectory() as tmp:
+            os.makedirs(os.path.join(tmp, group))
+            np.savez(os.path.join(tmp, group, "basis.npz"), **local)
+            with contextlib.redirect_stdout(io.StringIO()):
+                alpha, Pt, pm, solvers = Solver.prepare_reduced_group(me, True, True, group, ncomp, p, St, tmp, "basis.npz")
+        term = Solver.get_group_reduced_term(me, None, constraints, p, alpha, Pt, pm, solvers)
+        g_alpha, g_Pt, g_pm, g_normal, g_PtVT = port.prepare_reduced_group(local, ncomp, p, St, rtype)
+        assert np.array_equal(g_alpha, alpha) and np.array_equal(g_Pt, np.asarray(Pt))
+        assert rel(g_pm, pm) < 1e-14, rel(g_pm, pm)
+        g_term = port.group_reduced_term(P[np.asarray(Pt)], g_pm, g_normal, g_PtVT)
+        coef = np.stack([lu_solve(solvers[d][0], solvers[d][1] @ P[np.asarray(Pt), d]) for d in range(3)], axis=1)
+        g_coef = np.stack([np.linalg.solve(g_normal[d], g_PtVT[:, :, d] @ P[np.asarray(Pt), d]) for d in range(3)], axis=1)
+        print(f"bar_reduced {name}: |Pt|={len(Pt)} mp={pm.shape[1]}  port vs reference: S^T V {rel(g_pm, pm):.1e}, "
+              f"coefficients {rel(g_coef, coef):.1e}, term {rel(g_term, term):.1e}")
+        assert rel(g_term, term) < 1e-9
+        out.update({name + "_alpha": np.asarray(alpha), name + "_Pt": np.asarray(Pt, dtype=np.int64), name + "_StV": pm,
+                    name + "_PtVT": np.stack([solvers[d][1] for d in range(3)], axis=2), name + "_coef": coef,
+                    name + "_term": term})
+    np.savez_compressed(os.path.join(GOLD, "bar_reduced.npz"), **out)
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     load_reference()
+    if "--reduced-only" in sys.argv:           # reads bar.npz / bar_geom.npz, writes bar_reduced.npz only
+        with scratch_cwd():
+            return bar_reduced_case()
     if "--geom-only" not in sys.argv:
         make_meshes()
     with scratch_cwd():
@@ -348,6 +409,7 @@ def main():
             return bar_geom_case()
         bar_case()
         bar_geom_case()
+        bar_reduced_case()
         align_case()
         writers_case()
 

@@ -508,6 +508,42 @@ def deim_reconstruct(comps, frames, Pt_rows, r, p_block=1):
     return out
 
 
+# ======================================================================================= consumer side
+def prepare_reduced_group(local_data, num_components, row_dim, assembly_ST, reduction_type):
+    """projective_dynamics/Simulators.py:157-218 (reduced_position False).  local_data: mapping with the `.npz` keys
+    `components (K, ep, 3)`, `interpol_alphas`, `Pt`, `interpol_alpha_ranges` written by
+    constraintsComponents.store_components_n_interpol_points (:596-611).  Returns (interpolation_alpha, Pt, S^T V (N, mp, 3),
+    [regularised normal matrices (mp, mp) per dimension], PtV_T (mp, |Pt|, 3))."""
+    pod_rows = reduction_type in {"deim_pod", "deim_pod_vectorized"}
+    if pod_rows:
+        row_dim = 1                                                                          # :173-174
+    Vj = np.swapaxes(np.asarray(local_data["components"]), 0, 1)[:, :num_components * row_dim, :]   # :180-181
+    alpha_range = int(np.asarray(local_data["interpol_alpha_ranges"])[num_components - 1])  # :182
+    interpolation_alpha = np.asarray(local_data["interpol_alphas"])[:alpha_range]           # :184
+    if pod_rows:
+        Pt = np.asarray(local_data["Pt"])[:alpha_range]                                      # :187-188
+    else:
+        Pt = np.array([a * row_dim + l for a in interpolation_alpha for l in range(row_dim)], dtype=np.int64)   # :190-193
+    St = sparse.csr_matrix(assembly_ST)
+    projecting_mat = np.stack([St @ Vj[:, :, d] for d in range(3)], axis=2)                  # :197 (einsum on the dense St)
+    PtV = Vj[Pt, :, :]                                                                       # :205
+    PtV_T = np.swapaxes(PtV, 0, 1)                                                           # :206
+    AtA = np.einsum("nai,ami->nmi", PtV_T, PtV)                                              # :207
+    la = 1e-8 * np.trace(AtA) / AtA.shape[0]                                                 # :209 (trace over axes 0,1 -> (3,))
+    normal = [AtA[:, :, d] + la[d] * np.eye(AtA.shape[0]) for d in range(3)]                 # :214
+    return interpolation_alpha, Pt, projecting_mat, normal, PtV_T
+
+
+def group_reduced_term(p_rows, projecting_mat, normal, PtV_T):
+    """projective_dynamics/Simulators.py:394-399: S^T V (A^T A + la I)^-1 A^T p per dimension (lu_factor / lu_solve);
+    p_rows (|Pt|, 3) = the constraint projections at the interpolation rows (:382-392)."""
+    cols = []
+    for d in range(3):
+        coef = sla.lu_solve(sla.lu_factor(normal[d]), PtV_T[:, :, d] @ p_rows[:, d])
+        cols.append(projecting_mat[:, :, d] @ coef)
+    return np.column_stack(cols)
+
+
 # ======================================================================================= error measures / writers
 def frobenius_error(f, g):
     """snapbases/posComponents.py:221-227."""

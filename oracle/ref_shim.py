@@ -112,6 +112,32 @@ def load_reference():
     _loaded = True
 
 
+def load_pd_simulators():
+    """The reference's consumer module projective_dynamics/Simulators.py, loaded from source under a private
+    name.  Its `from utils import check_dir_exists` means projective_dynamics/utils.py, which would shadow the root `utils`
+    package registered above: a one-function stand-in is visible as `utils` only while the module executes."""
+    load_reference()
+    import importlib.util
+    name = "asb_ref_pd_simulators"
+    if name in sys.modules:
+        return sys.modules[name]
+    saved = sys.modules.get("utils")
+    fake = types.ModuleType("utils")
+    fake.check_dir_exists = lambda p: os.makedirs(p, exist_ok=True)
+    sys.modules["utils"] = fake
+    try:
+        spec = importlib.util.spec_from_file_location(name, os.path.join(REFERENCE_ROOT, "projective_dynamics", "Simulators.py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+    finally:
+        if saved is not None:
+            sys.modules["utils"] = saved
+        else:
+            del sys.modules["utils"]
+    sys.modules[name] = mod
+    return mod
+
+
 class scratch_cwd:
     """`log_time("")` writes function_timings.txt into the CWD (utils/utils.py:232): run the
     reference from a scratch directory."""

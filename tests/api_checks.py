@@ -98,7 +98,41 @@ def constraints_param(tmp, b, k_desired):
         constProj_basis_type="pod_vectorized", deim_desired_num_components=k_desired, name="fixture", constProj_name="tets")
 
 
-def check_constraints_protocol(ops, comm, tmp):
+def check_consumer(tmp, K, ep):
+    """the emitted `.npz` goes through the consumer-side precompute (projective_dynamics/Simulators.py:157-218)
+    and the reduced term (:366-399) -- mirror on the installed ops against the CPU restatement reading the same file."""
+    import shutil
+    from scipy import sparse
+    from animsnapbases_b200 import reduced_group
+    g = golden("bar_geom")
+    St = sparse.csr_matrix((g["St_vals"], g["St_colidx"], g["St_rowptr"]), shape=tuple(g["St_shape"]))
+    group, name = "tets_deformation_gradient", "components_interpol_alphas_interpol_verts_interpol_alpha_ranges.npz"
+    os.makedirs(os.path.join(str(tmp), group), exist_ok=True)
+    shutil.copy(os.path.join(str(tmp), name), os.path.join(str(tmp), group, name))
+    m = K - 2
+    grp = reduced_group.prepare_reduced_group(True, True, group, m, 3, St, str(tmp), name, reduction_type="deim_pod_vectorized")
+    alpha, Pt, pm, solvers = grp
+    local = np.load(os.path.join(str(tmp), group, name))
+    r_alpha, r_Pt, r_pm, r_normal, r_PtVT = port.prepare_reduced_group(local, m, 3, St, "deim_pod_vectorized")
+    assert np.array_equal(alpha, r_alpha) and np.array_equal(Pt, r_Pt) and pm.shape == (St.shape[0], m, 3)
+    assert rel(pm, r_pm) < 1e-13
+    P = np.random.default_rng(5).standard_normal((ep, 3))
+    from scipy.linalg import lu_solve
+    for d in range(3):
+        assert rel(solvers[d][1], r_PtVT[:, :, d]) < 1e-15
+        want = np.linalg.solve(r_normal[d], r_PtVT[:, :, d] @ P[r_Pt, d])
+        assert rel(lu_solve(solvers[d][0], solvers[d][1] @ P[Pt, d]), want) < 1e-9     # the reference's own use of solver_list
+    assert rel(grp.reduced_term(P[Pt]), port.group_reduced_term(P[r_Pt], r_pm, r_normal, r_PtVT)) < 1e-9
+    assert reduced_group.prepare_reduced_group(False, True, group, m, 3, St, str(tmp), name) == (None, [], None, [])
+    try:
+        reduced_group.prepare_reduced_group(True, True, group, m, 3, St, str(tmp), name, reduction_type="nope")
+        raise RuntimeError("expected ValueError")
+    except ValueError:
+        pass
+    return True
+
+
+def check_constraints_protocol(ops, comm, tmp, consumer=False):
     """main.py:106-142 on the bar fixture: pod_vectorized -> post-process (QR, un-weight) -> deim -> writers."""
     from animsnapbases_b200.snapbases.constraintsComponents import constraintsComponents
     runtime.install(ops, comm)
@@ -145,6 +179,8 @@ def check_constraints_protocol(ops, comm, tmp):
                     allow_pickle=True)
         assert set(z.files) == {"components", "interpol_alphas", "Pt", "interpol_verts", "interpol_alpha_ranges"}
         assert np.array_equal(z["components"], bases.comps) and np.array_equal(z["Pt"], bases.geom_Pt)
+        if consumer:
+            assert check_consumer(tmp, K, ep)
         # plain DEIM leaves geom_interpol_verts empty, so the reference's third writer asserts (utils/utils.py:86) after the
         # bases and interpolation-point files of the first k were written; same behaviour here.  With vertices present all
         # three files are written for every k.

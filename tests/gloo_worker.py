@@ -20,5 +20,6 @@ pipeline_checks.check_positions(ops, comm, "pos_grid")
 pipeline_checks.check_bar(ops, comm)
 pipeline_checks.check_bar_geom(ops, comm)
 pipeline_checks.check_bar_reconstruction(ops, comm)
+pipeline_checks.check_bar_reduced(ops, comm)
 print(f"RANK{comm.rank} OK", flush=True)
 dist.destroy_process_group()

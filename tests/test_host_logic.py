@@ -93,6 +93,12 @@ def test_bar_reconstruction_host_logic():
     assert pipeline_checks.check_bar_reconstruction(NumpyOps(), engine.Comm(enabled=False))
 
 
+def test_bar_reduced_group_host_logic():
+    """engine.reduced_group_operators / reduced_group_term over the numpy statement of the kernels == the reference's own
+    prepare_reduced_group / get_group_reduced_term outputs (tests/golden/bar_reduced.npz)."""
+    assert pipeline_checks.check_bar_reduced(NumpyOps(), engine.Comm(enabled=False))
+
+
 def test_bar_geometric_deim_host_logic():
     """engine.deim_geom over the numpy statement of the kernels == the reference's picks (tests/golden/bar_geom.npz)."""
     assert pipeline_checks.check_bar_geom(NumpyOps(), engine.Comm(enabled=False))
@@ -150,7 +156,7 @@ def test_pos_components_protocol_host_logic(tmp_path):
 def test_constraints_components_protocol_host_logic(tmp_path):
     """nonlinearSnapshots / constraintsComponents drop-in protocol (main.py:106-142) with the numpy statement of the kernels."""
     import api_checks
-    assert api_checks.check_constraints_protocol(NumpyOps(), engine.Comm(enabled=False), tmp_path)
+    assert api_checks.check_constraints_protocol(NumpyOps(), engine.Comm(enabled=False), tmp_path, consumer=True)
 
 
 def test_preprocess_and_off_sequence_ingest(tmp_path):

@@ -81,6 +81,25 @@ def test_port_geometric_deim_golden():
         assert np.array_equal(out["alpha_ranges"], g[name + "_ranges"]) and np.array_equal(out["verts"], g[name + "_verts"])
 
 
+def test_port_reduced_group_golden():
+    """oracle/port.py::prepare_reduced_group / group_reduced_term against the outputs of the unmodified consumer code
+    (projective_dynamics/Simulators.py:157-218, :366-399) stored in tests/golden/bar_reduced.npz."""
+    from scipy import sparse
+    b, g, r = golden("bar"), golden("bar_geom"), golden("bar_reduced")
+    St = sparse.csr_matrix((g["St_vals"], g["St_colidx"], g["St_rowptr"]), shape=tuple(g["St_shape"]))
+    fx = {**{k: b[k] for k in b.files}, **{k: g[k] for k in g.files}}
+    cases = {"pod": ("deim_pod_vectorized", "post_comps", ("deim_Pt", "deim_alpha", "deim_ranges"), 10),
+             "blk": ("geom_pca_blocks_withSt", "blk_post", ("blk_pos2_Pt", "blk_pos2_alpha", "blk_pos2_ranges"), 4)}
+    for name, (rtype, ckey, (kpt, kal, krg), ncomp) in cases.items():
+        local = dict(components=fx[ckey], interpol_alphas=fx[kal], Pt=fx[kpt], interpol_alpha_ranges=fx[krg])
+        alpha, Pt, pm, normal, PtVT = port.prepare_reduced_group(local, ncomp, 3, St, rtype)
+        assert np.array_equal(alpha, r[name + "_alpha"]) and np.array_equal(Pt, r[name + "_Pt"])
+        assert rel(pm, r[name + "_StV"]) < 1e-14 and np.array_equal(PtVT, r[name + "_PtVT"])
+        coef = np.stack([np.linalg.solve(normal[d], PtVT[:, :, d] @ r["P"][Pt, d]) for d in range(3)], axis=1)
+        assert rel(coef, r[name + "_coef"]) < 1e-9
+        assert rel(port.group_reduced_term(r["P"][Pt], pm, normal, PtVT), r[name + "_term"]) < 1e-9
+
+
 def test_port_against_live_reference():
     from oracle import ref_shim
     if not ref_shim.reference_available():
