@@ -532,7 +532,16 @@ def square_csr_slice(ops, St, shard):
     return (ops.to_device(rowptr), ops.to_device(A.indices.astype(np.int32)), ops.to_device(A.data.astype(np.float64))), nv, L
 
 
-def deim_geom(ops, comm, C, shard, p, elems, St=None, ele_per_vert=1):
+def vertex_star(v, faces):
+    """The vertices of all faces containing v (v included) in the order `list(set)` yields them when the set is filled face
+    by face -- the candidate order of the reference's '_verts' query (utils/support.py:239-246)."""
+    star = set()
+    for face in faces[(faces == v).any(axis=1)]:
+        star.update(int(i) for i in face)
+    return list(star)
+
+
+def deim_geom(ops, comm, C, shard, p, elems, St=None, ele_per_vert=1, star_faces=None, constrained_verts=None):
     """Geometric block DEIM of snapbases/constraintsComponents.py:619-731.  C (K p, 3, ld) planar post-processed block basis,
     rows sharded; elems (e, nodes) host array of the constrained elements (tets / tris / edges), replicated.
     St (|V| x ep scipy sparse, replicated on the host) given = error_in_pos_space: the block residual is pushed through St
@@ -541,11 +550,18 @@ def deim_geom(ops, comm, C, shard, p, elems, St=None, ele_per_vert=1):
     over its p rows (:86-96).  The coefficients are the minimum-norm least-squares solution on the selected rows like
     np.linalg.lstsq (:660, :671; rectangular once a vertex contributes more than one element): a replicated
     (|Pt| x k p) pseudo-inverse per dimension (cuSOLVER through torch, tiny), everything ep-sized runs in libasb kernels.
+    Constraints on vertices ('_verts', :687-692): `star_faces` (triangles) given -> the candidates of a picked vertex are its
+    vertex star; with `constrained_verts` ('verts_bending', open meshes) the star is intersected with the constrained
+    vertices (ascending) and the selected row is the position in that list while `alpha` keeps the vertex id (:700-702).
     Returns dict(Pt, alpha, alpha_ranges, verts) (host) or None on a zero residual (:676-678)."""
     N, row0 = shard.n, shard.row0
     Kc, _, ld = C.shape
     K = Kc // p
-    elems = np.asarray(elems)
+    elems = None if elems is None else np.asarray(elems)
+    if star_faces is not None:
+        star_faces = np.asarray(star_faces)
+        assert St is not None, "vertex stars are only queried for the position-space error"
+        assert constrained_verts is None or p == 1, "verts_bending selects single rows"
     dev = C.device
     R = ops.zeros((p, 3, ld))
     Rv = R.view(3 * p, ld)
@@ -600,14 +616,21 @@ def deim_geom(ops, comm, C, shard, p, elems, St=None, ele_per_vert=1):
             ops.argmax_first(ev, nv, 0, val, idx)                       # replicated after the all-reduce: no exchange
             v = int(idx.item())
             verts.append(v)
-            if v not in incident:
-                incident[v] = [int(i) for i in np.nonzero((elems == v).any(axis=1))[0]]
+            if v not in incident:                                       # candidates: [(element id, its rows)]
+                if star_faces is None:
+                    ids = [int(i) for i in np.nonzero((elems == v).any(axis=1))[0]]
+                    incident[v] = [(a, [a * p + m for m in range(p)]) for a in ids]
+                elif constrained_verts is None:
+                    incident[v] = [(a, [a * p + m for m in range(p)]) for a in vertex_star(v, star_faces)]
+                else:
+                    ids, pos, _ = np.intersect1d(constrained_verts, vertex_star(v, star_faces), return_indices=True)
+                    incident[v] = [(int(a), [int(i)]) for a, i in zip(ids, pos)]
             jump = 0
-            for alpha in incident[v]:
+            for alpha, rows_of in incident[v]:
                 if alpha not in e_points and jump < ele_per_vert:
                     jump += 1
                     e_points.append(alpha)
-                    Pt += [alpha * p + m for m in range(p)]
+                    Pt += rows_of
         else:
             ops.vertex_energy(R, N, out=e_row)
             if N:

@@ -14,8 +14,8 @@ Device work goes through animsnapbases_b200.engine -> libasb.so:
 
   pod             (:274-294)  p * 3 independent PODs of the (e x F) blocks (f32 torch-CPU SVDs in the reference)    engine.pod_per_row
 
-Basis type 'pca_blocks_with_St'  and the '_verts' geometric DEIM raise
-NotImplementedError here rather than fall back to the CPU.
+Basis type 'pca_blocks_with_St' (defective in the reference) raises NotImplementedError here
+rather than fall back to the CPU.
 The plotting / polyscope methods of the reference (:865-1156) are out of scope (graphics: unavailable on this box).
 """
 from __future__ import annotations
@@ -235,18 +235,21 @@ class constraintsComponents:  # Components == bases
         ops, comm = runtime.get()
         snaps = self.nonlinearSnapshots
         elems = {"_tets": snaps.tets, "_tris": snaps.tris, "_edges": snaps.edges}.get(snaps.ele_type)
-        St = None
+        St = star_faces = constrained = None
         if error_in_pos_space:
             if snaps.ele_type not in ["_tets", "_tris", "_edges", "_verts"]:
                 print("ERROR! Unknown constained elements nonliner snapshots type!")
                 return
-            if elems is None:
-                raise NotImplementedError("geometric DEIM for '_verts' (vertex-star / verts_bending) constraints is not built yet")
             if self.St is None:
                 raise ValueError("geometric DEIM in position space needs the differential operator St (constProj_weightedSt)")
             St = self.St
+            if snaps.ele_type == "_verts":                      # vertex stars (:687-692), index mapping for verts_bending
+                star_faces = snaps.tris
+                if self.param.constProj_snapshots_type == "verts_bending":
+                    self.constrianed_verts = np.load(self.param.constProj_input_snaps_constrained_elements)["indices"]
+                    constrained = self.constrianed_verts
         out = engine.deim_geom(ops, comm, self._C, snaps.shard, snaps.constraintsSize, elems, St,
-                               int(getattr(self.param, "geom_ele_per_vert", 1)))
+                               int(getattr(self.param, "geom_ele_per_vert", 1)), star_faces, constrained)
         if out is None:
             return
         self.geom_Pt, self.geom_alpha, self.geom_alpha_ranges = out["Pt"], out["alpha"], out["alpha_ranges"]

@@ -332,6 +332,71 @@ def bar_geom_case():
     np.savez_compressed(os.path.join(GOLD, "bar_geom.npz"), **out)
 
 
+# ------------------------------------------------------------------------------------------------ geometric DEIM, '_verts'
+def verts_geom_inputs():
+    """Vertex-based constraint snapshots on an open triangle grid: rows = cotangent-Laplacian vectors (L x_f) at the
+    constrained vertices, St = L[constrained, :]^T (|V| x e), bases = POD of the centred snapshots.  Two groups:
+    'bend' = interior vertices only (verts_bending: row index != vertex id), 'all' = every vertex."""
+    verts0, tris = synth.grid_mesh(14, 11)
+    anim = synth.bump_animation(verts0, 18, n_bumps=5, sigma=0.18, seed=3).astype(np.float64)
+    L, _ = port.mesh_laplacian(verts0.astype(np.float64), tris)
+    nv = len(verts0)
+    edge_count = {}
+    for t in tris:
+        for a, b in ((t[0], t[1]), (t[1], t[2]), (t[2], t[0])):
+            key = (min(a, b), max(a, b))
+            edge_count[key] = edge_count.get(key, 0) + 1
+    boundary = sorted({v for (a, b), c in edge_count.items() if c == 1 for v in (a, b)})
+    interior = np.setdiff1d(np.arange(nv), boundary)
+    groups = {}
+    for name, idx in (("bend", interior), ("all", np.arange(nv))):
+        Lc = L.tocsr()[idx]
+        X = np.stack([Lc @ f for f in anim])                      # (F, e, 3)
+        X = X - X.mean(axis=0)
+        comps, _ = port.pod_vectorized(X, 8)
+        groups[name] = dict(idx=idx.astype(np.int64), St=Lc.T.tocsr(), comps=comps)
+    return tris.astype(np.int64), groups
+
+
+def verts_geom_case():
+    """'_verts' flavour of geom_block_form_utilizing_differential_operator (constraintsComponents.py:684-702) of the
+    unmodified reference -> tests/golden/verts_geom.npz: vertex stars as candidate sets, with (verts_bending) and without
+    the constrained-vertex index mapping, 1 and 3 elements per picked vertex."""
+    import tempfile
+    from snapbases.constraintsComponents import constraintsComponents
+    from snapbases.nonlinear_snapshots import nonlinearSnapshots
+    tris, groups = verts_geom_inputs()
+    out = dict(tris=tris)
+    for gname, g in groups.items():
+        St, comps, idx = g["St"], g["comps"], g["idx"]
+        out.update({f"{gname}_idx": idx, f"{gname}_comps": comps, f"{gname}_St_rowptr": St.indptr.astype(np.int32),
+                    f"{gname}_St_colidx": St.indices.astype(np.int32), f"{gname}_St_vals": St.data,
+                    f"{gname}_St_shape": np.array(St.shape)})
+        for per_vert in (1, 3):
+            bending = gname == "bend"
+            ns = object.__new__(nonlinearSnapshots)
+            ns.constraintsSize, ns.num_constained_elements, ns.dim = 1, len(idx), 3
+            ns.ele_type, ns.tris = "_verts", tris
+            cc = object.__new__(constraintsComponents)
+            with tempfile.TemporaryDirectory() as tmp:
+                f = os.path.join(tmp, "verts_bending_constrained_indices.npz")
+                np.savez(f, indices=idx)
+                cc.param = types.SimpleNamespace(geom_ele_per_vert=per_vert, constProj_input_snaps_constrained_elements=f,
+                                                 constProj_snapshots_type="verts_bending" if bending else "verts_other")
+                cc.nonlinearSnapshots, cc.comps, cc.numComp, cc.St, cc.geom_interpol_verts = ns, comps.copy(), comps.shape[0], St, []
+                with contextlib.redirect_stdout(io.StringIO()):
+                    cc.geom_block_form_utilizing_differential_operator(True)
+            gp = port.deim_geom(comps, 1, len(idx), None, St, per_vert, star_faces=tris, constrained_verts=idx if bending else None)
+            assert np.array_equal(gp["Pt"], cc.geom_Pt) and np.array_equal(gp["alpha"], cc.geom_alpha)
+            assert np.array_equal(gp["alpha_ranges"], cc.geom_alpha_ranges) and np.array_equal(gp["verts"], cc.geom_interpol_verts)
+            key = f"{gname}{per_vert}"
+            out.update({key + "_Pt": np.asarray(cc.geom_Pt, dtype=np.int64), key + "_alpha": np.asarray(cc.geom_alpha, dtype=np.int64),
+                        key + "_ranges": cc.geom_alpha_ranges, key + "_verts": np.asarray(cc.geom_interpol_verts, dtype=np.int64)})
+            print(f"verts_geom {key}: port == reference; verts={cc.geom_interpol_verts} alpha={cc.geom_alpha[:8]} "
+                  f"Pt={cc.geom_Pt[:8]} ranges={cc.geom_alpha_ranges}")
+    np.savez_compressed(os.path.join(GOLD, "verts_geom.npz"), **out)
+
+
 # ------------------------------------------------------------------------------------------------ consumer side (n2)
 REDUCED_CASES = {   # name: (reduction type, components key, (Pt, alpha, ranges) keys, num_components)
     "pod": ("deim_pod_vectorized", "post_comps", ("deim_Pt", "deim_alpha", "deim_ranges"), 10),
@@ -393,6 +458,9 @@ def bar_reduced_case():
 def main():
     os.makedirs(GOLD, exist_ok=True)
     load_reference()
+    if "--verts-only" in sys.argv:             # writes verts_geom.npz only
+        with scratch_cwd():
+            return verts_geom_case()
     if "--reduced-only" in sys.argv:           # reads bar.npz / bar_geom.npz, writes bar_reduced.npz only
         with scratch_cwd():
             return bar_reduced_case()
@@ -410,6 +478,7 @@ def main():
         bar_case()
         bar_geom_case()
         bar_reduced_case()
+        verts_geom_case()
         align_case()
         writers_case()
 

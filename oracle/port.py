@@ -450,9 +450,22 @@ def elements_per_vert(v, elems):
     return [int(i) for i in np.nonzero((np.asarray(elems) == v).any(axis=1))[0]]
 
 
-def deim_geom(comps, p, e, elems, St=None, ele_per_vert=1):
-    """snapbases/constraintsComponents.py:619-731 (geom_block_form_utilizing_differential_operator), element types whose
-    incident-element query is get_*_per_vert.  comps (K p, ep, 3).  St (|V| x ep, sparse or dense) given: error measured in
+def vert_star_per_vert(v, faces):
+    """utils/support.py:239-246 (get_vert_star_per_vert as constraintsComponents.py:688 calls it): the vertices of all
+    faces containing v, v included, in the iteration order of a CPython set filled face by face (`list(neighbors)`)."""
+    neighbors = set()
+    for face in np.asarray(faces):
+        if v in face:
+            neighbors.update(face)
+    return list(neighbors)
+
+
+def deim_geom(comps, p, e, elems, St=None, ele_per_vert=1, star_faces=None, constrained_verts=None):
+    """snapbases/constraintsComponents.py:619-731 (geom_block_form_utilizing_differential_operator).  Element types
+    '_tets' / '_tris' / '_edges': incident elements by get_*_per_vert on `elems`.  '_verts' (:687-692): pass the triangles as
+    `star_faces`, the candidates are the vertex star; with `constrained_verts` (constProj_snapshots_type 'verts_bending')
+    the star is intersected with the constrained vertices (np.intersect1d: ascending) and the selected ROW is the position
+    in that list (:700-702, p == 1) while geom_alpha keeps the vertex id.  comps (K p, ep, 3).  St (|V| x ep, sparse or dense) given: error measured in
     position space (error_in_pos_space=True: worst VERTEX, up to ele_per_vert new incident elements per step, rectangular
     least squares on V[Pt]); St None: error in constraint space (worst ELEMENT by block energy, :86-96).
     Returns dict(Pt, alpha, alpha_ranges, verts) or None on a zero residual (:676-678)."""
@@ -477,11 +490,18 @@ def deim_geom(comps, p, e, elems, St=None, ele_per_vert=1):
             v = int(np.argmax((r ** 2).sum(axis=1)))
             verts.append(v)
             jump = 0
-            for alpha in elements_per_vert(v, elems):
+            mapped = None
+            if star_faces is not None:
+                alpha_list = vert_star_per_vert(v, star_faces)
+                if constrained_verts is not None:
+                    alpha_list, mapped, _ = np.intersect1d(constrained_verts, alpha_list, return_indices=True)
+            else:
+                alpha_list = elements_per_vert(v, elems)
+            for al, alpha in enumerate(alpha_list):
                 if alpha not in e_points and jump < ele_per_vert:
                     jump += 1
                     e_points.append(alpha)
-                    Pt += [alpha * p + m for m in range(p)]
+                    Pt += [mapped[al]] if mapped is not None else [alpha * p + m for m in range(p)]
             e_jump.append(jump)
         else:
             alpha = index_largest_deformation(r, p, e)

@@ -221,3 +221,38 @@ def check_constraints_protocol(ops, comm, tmp, consumer=False):
         os.chdir(cwd)
         runtime.install(None, None)
     return True
+
+
+def check_verts_geom_protocol(ops, comm, tmp):
+    """constraintsComponents.geom_block_form_utilizing_differential_operator(True) of the mirror class for '_verts'
+    constraints of type verts_bending: reads the constrained-vertex file the reference reads (:636-638) and returns the
+    reference's picks (tests/golden/verts_geom.npz)."""
+    import types
+    from scipy import sparse
+    from animsnapbases_b200 import engine
+    from animsnapbases_b200.snapbases.constraintsComponents import constraintsComponents
+    from animsnapbases_b200.snapbases.nonlinear_snapshots import nonlinearSnapshots
+    runtime.install(ops, comm)
+    try:
+        g = golden("verts_geom")
+        comps, idx = g["bend_comps"], g["bend_idx"]
+        f = os.path.join(str(tmp), "verts_bending_constrained_indices.npz")
+        np.savez(f, indices=idx)
+        ns = object.__new__(nonlinearSnapshots)
+        ns.constraintsSize, ns.num_constained_elements, ns.dim = 1, len(idx), 3
+        ns.ele_type, ns.tris, ns.tets, ns.edges = "_verts", g["tris"], None, None
+        ns.shard = engine.Shard.make(len(idx), comm.world, comm.rank)
+        cc = object.__new__(constraintsComponents)
+        cc.param = types.SimpleNamespace(geom_ele_per_vert=3, constProj_input_snaps_constrained_elements=f,
+                                         constProj_snapshots_type="verts_bending")
+        cc.nonlinearSnapshots, cc.numComp, cc.geom_interpol_verts = ns, comps.shape[0], []
+        cc.St = sparse.csr_matrix((g["bend_St_vals"], g["bend_St_colidx"], g["bend_St_rowptr"]), shape=tuple(g["bend_St_shape"]))
+        rows = slice(ns.shard.row0, ns.shard.row0 + ns.shard.n)
+        cc._C = ops.ingest(ops.to_device(np.ascontiguousarray(comps[:, rows])), None, ns.shard.ld)
+        cc.geom_block_form_utilizing_differential_operator(True)
+        assert np.array_equal(cc.geom_Pt, g["bend3_Pt"]) and np.array_equal(cc.geom_alpha, g["bend3_alpha"])
+        assert np.array_equal(cc.geom_alpha_ranges, g["bend3_ranges"]) and np.array_equal(cc.geom_interpol_verts, g["bend3_verts"])
+        assert np.array_equal(cc.constrianed_verts, idx)
+    finally:
+        runtime.install(None, None)
+    return True

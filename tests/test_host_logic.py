@@ -93,6 +93,16 @@ def test_bar_reconstruction_host_logic():
     assert pipeline_checks.check_bar_reconstruction(NumpyOps(), engine.Comm(enabled=False))
 
 
+def test_verts_geometric_deim_protocol(tmp_path):
+    import api_checks
+    assert api_checks.check_verts_geom_protocol(NumpyOps(), engine.Comm(enabled=False), tmp_path)
+
+
+def test_verts_geometric_deim_host_logic():
+    """'_verts' geometric DEIM (vertex stars, verts_bending index mapping) == the reference's picks (verts_geom.npz)."""
+    assert pipeline_checks.check_verts_geom(NumpyOps(), engine.Comm(enabled=False))
+
+
 def test_bar_reduced_group_host_logic():
     """engine.reduced_group_operators / reduced_group_term over the numpy statement of the kernels == the reference's own
     prepare_reduced_group / get_group_reduced_term outputs (tests/golden/bar_reduced.npz)."""

@@ -81,6 +81,21 @@ def test_port_geometric_deim_golden():
         assert np.array_equal(out["alpha_ranges"], g[name + "_ranges"]) and np.array_equal(out["verts"], g[name + "_verts"])
 
 
+def test_port_verts_geometric_deim_golden():
+    """oracle/port.py::deim_geom, '_verts' flavour, against the picks of the unmodified reference (:684-702)."""
+    from scipy import sparse
+    g = golden("verts_geom")
+    for gname in ("bend", "all"):
+        St = sparse.csr_matrix((g[gname + "_St_vals"], g[gname + "_St_colidx"], g[gname + "_St_rowptr"]),
+                               shape=tuple(g[gname + "_St_shape"]))
+        for per_vert in (1, 3):
+            out = port.deim_geom(g[gname + "_comps"], 1, len(g[gname + "_idx"]), None, St, per_vert, star_faces=g["tris"],
+                                 constrained_verts=g[gname + "_idx"] if gname == "bend" else None)
+            key = f"{gname}{per_vert}"
+            assert np.array_equal(out["Pt"], g[key + "_Pt"]) and np.array_equal(out["alpha"], g[key + "_alpha"])
+            assert np.array_equal(out["alpha_ranges"], g[key + "_ranges"]) and np.array_equal(out["verts"], g[key + "_verts"])
+
+
 def test_port_reduced_group_golden():
     """oracle/port.py::prepare_reduced_group / group_reduced_term against the outputs of the unmodified consumer code
     (projective_dynamics/Simulators.py:157-218, :366-399) stored in tests/golden/bar_reduced.npz."""
