@@ -155,6 +155,44 @@ def write_components_animation(path, default_verts, tris, comps):
     return out
 
 
+# ------------------------------------------------------------------------------------------------ sparse operators (n3)
+_TRIPLET = np.dtype([("row", "<i4"), ("col", "<i4"), ("val", "<f8")])
+
+
+def read_sparse_matrix_from_bin(filename):
+    """`<i rows><i cols><i nnz>` + nnz x (`<i row><i col><d value>`) -> scipy CSR, duplicates summed (utils/utils.py:289-312,
+    which unpacks the 3 nnz fields one struct at a time; here one structured read)."""
+    from scipy.sparse import csr_matrix
+    with open(filename, "rb") as f:
+        rows, cols, nnz = struct.unpack("<iii", f.read(12))
+        t = np.fromfile(f, dtype=_TRIPLET, count=nnz)
+    assert len(t) == nnz, "truncated sparse matrix file"
+    return csr_matrix((t["val"], (t["row"], t["col"])), shape=(rows, cols))
+
+
+def write_sparse_matrix_to_bin(filename, A):
+    """Inverse of read_sparse_matrix_from_bin (the reference's files come from its C++ side; this one serves tests and
+    synthetic configs)."""
+    A = A.tocoo()
+    t = np.empty(A.nnz, dtype=_TRIPLET)
+    t["row"], t["col"], t["val"] = A.row, A.col, A.data
+    with open(filename, "wb") as f:
+        f.write(struct.pack("<iii", A.shape[0], A.shape[1], A.nnz))
+        t.tofile(f)
+
+
+def read_sparse_matrix(file_name, type, key=None):
+    """utils/utils.py:314-323: '.bin' triplet file, or '.npz' holding a pickled scipy sparse matrix under `key` (returned
+    as the 0-d object array np.load yields, like the reference; constraintsComponents unwraps it)."""
+    if type == ".bin":
+        return read_sparse_matrix_from_bin(file_name)
+    elif type == ".npz":
+        if key is None:
+            raise ValueError("Empty file or wrong key:", type)
+        return np.load(file_name, allow_pickle=True)[key]
+    raise ValueError("unknown sparse matrix file_type:", type)
+
+
 # ------------------------------------------------------------------------------------------------ snapshot ingest (a1, n3)
 def load_off(filename, no_colors=False):
     """OFF / COFF reader of utils/process.py:46-66: (verts (n, 3) float64, [colors uint8,] faces (m, k) int or None)."""

@@ -198,3 +198,39 @@ def test_preprocess_and_off_sequence_ingest(tmp_path):
     assert np.array_equal(verts, ref)
     ext = verts.max(axis=1) - verts.min(axis=1)
     assert abs(ext.max() - 1.0) < 1e-6 and np.abs(verts.mean(axis=(0, 1))).max() < 1e-6
+
+
+def test_sparse_operator_files(tmp_path):
+    """utils/utils.py:289-323: the `.bin` triplet container of the differential operator St and the pickled
+    `.npz` variant; checked against the unmodified reference reader when /root/reference is mounted."""
+    from scipy import sparse
+    from animsnapbases_b200 import hostio
+    rng = np.random.default_rng(8)
+    A = sparse.random(37, 53, density=0.08, random_state=3, format="csr")
+    path = str(tmp_path / "St.bin")
+    hostio.write_sparse_matrix_to_bin(path, A)
+    raw = open(path, "rb").read()
+    assert len(raw) == 12 + 16 * A.nnz and np.frombuffer(raw[:12], "<i4").tolist() == [37, 53, A.nnz]
+    B = hostio.read_sparse_matrix_from_bin(path)
+    assert B.shape == A.shape and (abs(A - B)).nnz == 0
+    assert (abs(hostio.read_sparse_matrix(path, ".bin") - A)).nnz == 0
+    # duplicate triplets add up (COO -> CSR), as in the reference's csr_matrix((values, (rows, cols)))
+    with open(path, "wb") as f:
+        f.write(np.array([2, 2, 3], "<i4").tobytes())
+        for r, c, v in ((0, 1, 1.5), (0, 1, 2.0), (1, 0, -1.0)):
+            f.write(np.array([r, c], "<i4").tobytes() + np.array([v], "<f8").tobytes())
+    assert np.array_equal(hostio.read_sparse_matrix_from_bin(path).toarray(), [[0.0, 3.5], [-1.0, 0.0]])
+    np.savez(str(tmp_path / "assembly_ST.npz"), tets_deformation_gradient=A)
+    got = hostio.read_sparse_matrix(str(tmp_path / "assembly_ST.npz"), ".npz", key="tets_deformation_gradient")
+    assert (abs(got.item() - A)).nnz == 0
+    with pytest.raises(ValueError):
+        hostio.read_sparse_matrix(path, ".npz")
+    with pytest.raises(ValueError):
+        hostio.read_sparse_matrix(path, ".txt")
+    from oracle import ref_shim
+    if ref_shim.reference_available():
+        ref_shim.load_reference()
+        import utils.utils as ref_utils
+        hostio.write_sparse_matrix_to_bin(path, A)
+        assert (abs(ref_utils.read_sparse_matrix_from_bin(path) - A)).nnz == 0
+    del rng
