@@ -61,6 +61,12 @@ def test_position_pipeline_host_logic(name):
     assert pipeline_checks.check_positions(NumpyOps(), engine.Comm(enabled=False), name)
 
 
+def test_bunny_live_oracle_host_logic():
+    """BASELINE config 1/2 mesh (bunny, N = 14 290) at an oracle-friendly frame count: engine over the numpy statement of the
+    kernels == oracle/port.py run live (deflation with geodesic support + SPLOCS)."""
+    assert pipeline_checks.check_positions_live(NumpyOps(), engine.Comm(enabled=False), "bunny")
+
+
 def test_deflation_block_size_invariance():
     """Blocking the rank-1 updates must not change which vertices are picked nor the components."""
     import torch
