@@ -99,6 +99,18 @@ class constraintsComponents:  # Components == bases
         m = x.max()
         return x if m == 0 else x / m
 
+    @staticmethod
+    def indxLargestDeformation(R, p, e):
+        """Host statement of the element pick (:86-96; R (ep, F, d)): kept for callers of the static; the build itself picks
+        on the device (asb_vertex_energy + asb_group_sum + asb_argmax_first, same first-max rule)."""
+        magnitude = (R ** 2).sum(axis=2).reshape(e, p, -1)
+        return np.argmax(magnitude.sum(axis=(1, 2)))
+
+    @staticmethod
+    def indxLargestDeformation_e(r, e, p, d):
+        assert r.shape == (e, p * d)
+        return np.argmax((r ** 2).sum(axis=1))
+
     # ------------------------------------------------------------------ basis build
     @log_time("")
     def compute_components_store_singvalues(self):
@@ -292,6 +304,19 @@ class constraintsComponents:  # Components == bases
         for d, sig in enumerate(engine.row_singular_values(ops, comm, self._C, self.nonlinearSnapshots.shard, self._rows)):
             s[:, d] = sig / sig.max()
         return s
+
+    def is_utmu_orthogonal(self):
+        """Prints 'True..' / 'False..' per dimension for U^T M U = I (:450-459; prints, does not assert): mass-weighted
+        Kp x Kp Grams on the DMMA pipe."""
+        print('... testing M orthogonality, U^T M U = I (Kp x Kp) ...', end='', flush=True)
+        ops, comm = runtime.get()
+        snaps, sh = self.nonlinearSnapshots, self.nonlinearSnapshots.shard
+        rows = slice(sh.row0, sh.row0 + sh.n)
+        verdicts = []
+        for G in engine.weighted_row_grams(ops, comm, self._C, sh, self._rows, ops.to_device(np.sqrt(snaps.mass[rows]))):
+            verdicts.append(bool(np.allclose(G, np.eye(self._rows))))
+            print('True..' if verdicts[-1] else "False..")
+        return verdicts
 
     @staticmethod
     def frobenius_error(f, f_reconstructed):

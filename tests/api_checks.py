@@ -170,6 +170,9 @@ def check_constraints_protocol(ops, comm, tmp, consumer=False):
             s = np.sign((bases.comps[:, :, d] * post[:, :, d]).sum(axis=1))
             assert rel(bases.comps[:, :, d] * s[:, None], post[:, :, d]) < 1e-7
         assert rel(snaps.snapTensor, b["post_snap"]) < 1e-12, "post-processing also un-standardises the snapshots (:426-443)"
+        assert bases.is_utmu_orthogonal() == [True, True, True], "QR then M^-1/2 scaling: U^T M U = I per dimension (:450-459)"
+        Rt = np.swapaxes(b["X"], 0, 1)                                       # (ep, F, 3) as indxLargestDeformation expects
+        assert bases.indxLargestDeformation(Rt, 3, ep // 3) == port.index_largest_deformation(Rt, 3, ep // 3)
         bases.deim()
         assert np.array_equal(bases.geom_Pt, b["deim_Pt"][:K]), "DEIM indices must be bit-exact"
         assert np.array_equal(bases.geom_alpha, b["deim_alpha"][:K])
