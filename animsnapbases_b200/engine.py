@@ -836,3 +836,25 @@ def reconstruction_errors(ops, comm, X, shard, C, W, ks):
         rel = torch.sqrt(e2 / xn).tolist()
         rx.append(rel[0]); ry.append(rel[1]); rz.append(rel[2])
     return fro, mx, rx, ry, rz
+
+
+def tensor_error_measures(comm, X, rec, shard):
+    """frobenius_error, max_pointwise_error and relative_error_per_component (constraintsComponents.py:524-552, the same
+    statics as posComponents.py:217-249) of a reconstruction `rec` of `X`, both planar (F, 3, ld) with rows sharded, without
+    bringing the tensors to the host: torch reductions + three small all-reduces.  Returns (fro, max_err, [rx, ry, rz])."""
+    n = shard.n
+    dev = X.device
+    ninf = torch.full((1,), -float("inf"), dtype=F64, device=dev)
+    if n:
+        err = X[:, :, :n] - rec[:, :, :n]
+        e2 = torch.stack([(err[:, d, :] ** 2).sum() for d in range(3)])
+        x2 = torch.stack([(X[:, d, :n] ** 2).sum() for d in range(3)])
+        em, xm = err.abs().max().reshape(1), X[:, :, :n].max().reshape(1)
+    else:
+        e2, x2 = torch.zeros(3, dtype=F64, device=dev), torch.zeros(3, dtype=F64, device=dev)
+        em, xm = ninf.clone(), ninf.clone()
+    comm.allreduce_sum(e2)
+    comm.allreduce_sum(x2)
+    mx = torch.cat([em, xm])
+    comm.allreduce_max(mx)
+    return (float(torch.sqrt(e2.sum()).item()), float((mx[0] / mx[1]).item()), torch.sqrt(e2 / x2).tolist())

@@ -269,11 +269,8 @@ class constraintsComponents:  # Components == bases
         print("Computing interpolation elements utilizing differential operator, used", self.geom_alpha.shape[0],
               "constrained elements")
 
-    @log_time("")
-    def geom_constructed(self, r, case, interpol="geom"):
-        """DEIM reconstruction of the train / test frames from r interpolation elements (:489-521); returns the host
-        (F, ep, 3) array the figure scripts feed to the error statics.  Keeps the reference's row choice (geom_alpha, i.e.
-        element ids used as row ids unless constProj_snapshots_type == 'verts_bending', :507-512)."""
+    def _geom_constructed_device(self, r, case):
+        """(frames, reconstruction) planar on the device for geom_constructed / geom_reconstruction_errors."""
         ops, comm = runtime.get()
         snaps = self.nonlinearSnapshots
         p = snaps.constraintsSize if self.param.constProj_bases_interpolation_type in ("geom", "deim_block_form") else 1
@@ -289,11 +286,27 @@ class constraintsComponents:  # Components == bases
             Pt = self.geom_Pt[:self.geom_alpha_ranges[r - 1]]
         else:
             Pt = self.geom_alpha[:self.geom_alpha_ranges[r - 1]]
-        rec = engine.deim_reconstruct(ops, comm, self._C, X, sh, Pt, r * p)
+        return X, engine.deim_reconstruct(ops, comm, self._C, X, sh, Pt, r * p)
+
+    @log_time("")
+    def geom_constructed(self, r, case, interpol="geom"):
+        """DEIM reconstruction of the train / test frames from r interpolation elements (:489-521); returns the host
+        (F, ep, 3) array the figure scripts feed to the error statics.  Keeps the reference's row choice (geom_alpha, i.e.
+        element ids used as row ids unless constProj_snapshots_type == 'verts_bending', :507-512)."""
+        ops, comm = runtime.get()
+        sh = self.nonlinearSnapshots.shard
+        _, rec = self._geom_constructed_device(r, case)
         out = ops.export_aos(rec, None, sh.n).cpu().numpy()
         if comm.world > 1:
             out = engine.gather_rows_host(comm, out, sh, axis=1)
         return out
+
+    def geom_reconstruction_errors(self, r, case):
+        """(frobenius_error, max_pointwise_error, relative_error_per_component) of geom_constructed(r, case) against the
+        frames (generate_figures/nl_reduction_tests.py:137-140) with both tensors left on the device."""
+        _, comm = runtime.get()
+        X, rec = self._geom_constructed_device(r, case)
+        return engine.tensor_error_measures(comm, X, rec, self.nonlinearSnapshots.shard)
 
     # ------------------------------------------------------------------ checks
     @log_time("")

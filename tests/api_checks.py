@@ -25,7 +25,7 @@ def pos_param(tmp, g, bases_type="PCA", support="local", orthogonal=False):
         splocs_lambda=float(lam), splocs_rho=float(rho), q_orthogonal=orthogonal, vertPos_output_directory=d, name="fixture")
 
 
-def check_pos_protocol(ops, comm, tmp, name="pos_grid"):
+def check_pos_protocol(ops, comm, tmp, name="pos_grid", extended=False):
     from animsnapbases_b200.snapbases.posComponents import posComponents
     runtime.install(ops, comm)
     cwd = os.getcwd()
@@ -77,6 +77,13 @@ def check_pos_protocol(ops, comm, tmp, name="pos_grid"):
         bases.post_process_components()
         Mu = bases.comps[:, :, 0] * g["mass"][None]
         assert np.allclose(bases.comps[:, :, 0] @ Mu.T, np.eye(K), atol=1e-8)
+        if extended:        # headless figure-script table (generate_figures/pos_reduction_tests.py:62-92)
+            from animsnapbases_b200 import reduction_tests
+            sv = reduction_tests.pos_pca_tests(bases, bases.param)
+            tab = open(os.path.join(str(tmp), "fixture_posBases_xyz_fullBasesRange_K_singVals.csv")).read().splitlines()
+            assert tab[0] == "row,x,y,z" and len(tab) == K + 1 and tab[1].split(",")[0] == "1"
+            assert np.allclose([float(v) for v in tab[K].split(",")[1:]], sv[K - 1])
+            assert np.allclose(sv, port.bases_sing_vals(bases.comps), atol=1e-7)
     finally:
         os.chdir(cwd)
         runtime.install(None, None)
@@ -132,7 +139,7 @@ def check_consumer(tmp, K, ep):
     return True
 
 
-def check_constraints_protocol(ops, comm, tmp, consumer=False):
+def check_constraints_protocol(ops, comm, tmp, extended=False):
     """main.py:106-142 on the bar fixture: pod_vectorized -> post-process (QR, un-weight) -> deim -> writers."""
     from animsnapbases_b200.snapbases.constraintsComponents import constraintsComponents
     runtime.install(ops, comm)
@@ -182,7 +189,7 @@ def check_constraints_protocol(ops, comm, tmp, consumer=False):
                     allow_pickle=True)
         assert set(z.files) == {"components", "interpol_alphas", "Pt", "interpol_verts", "interpol_alpha_ranges"}
         assert np.array_equal(z["components"], bases.comps) and np.array_equal(z["Pt"], bases.geom_Pt)
-        if consumer:
+        if extended:
             assert check_consumer(tmp, K, ep)
         # plain DEIM leaves geom_interpol_verts empty, so the reference's third writer asserts (utils/utils.py:86) after the
         # bases and interpolation-point files of the first k were written; same behaviour here.  With vertices present all
@@ -207,6 +214,27 @@ def check_constraints_protocol(ops, comm, tmp, consumer=False):
         assert rec.shape == (F, ep, 3)
         err = bases.frobenius_error(snaps.snapTensor, rec)
         assert abs(err - float(b["deim_rec10_err"][0])) < 1e-6 * float(b["deim_rec10_err"][0])
+        if extended:
+            # headless figure-script numbers (generate_figures/nl_reduction_tests.py:120-225) against the host statics
+            from animsnapbases_b200 import reduction_tests
+            train, test = reduction_tests.nl_geom_tests(bases, steps=4)
+            assert [r[0] for r in train] == list(range(1, K + 1, 4)) and len(test) == len(train)
+            for rows, case, frames in ((train, "train", snaps.snapTensor), (test, "test", snaps.test_snapTensor)):
+                for r, fro, mx, rx, ry, rz, r3 in rows:
+                    got = bases.geom_constructed(r, case)
+                    want = [port.frobenius_error(frames, got), port.max_pointwise_error(frames, got)] + \
+                        list(port.relative_error_per_component(frames, got))
+                    assert np.allclose([fro, mx, rx, ry, rz], want, rtol=1e-9), (case, r)
+                    assert abs(r3 - (rx + ry + rz) / 3) < 1e-15
+            stem = os.path.join(str(tmp), "fixture_tets_deim_pod_vectorized")
+            lines = open(stem + "_train_convergence_tests.csv").read().splitlines()
+            assert lines[0] == "numPoints,fro_error,max_err,relative_errors_x,relative_errors_y,relative_errors_z,relative3d"
+            assert len(lines) == 1 + len(train) and os.path.exists(stem + "_test_convergence_tests.csv")
+            assert open(stem + "_num_interpol_elemnets.csv").read().splitlines()[:2] == ["numPoints,num_elements", "1,1"]
+            sv = reduction_tests.nl_pca_tests(bases)
+            tab = open(os.path.join(str(tmp), "fixture_tets_constrprojBases_xyz_fullBasesRange_Kp_singVals.csv")).read().splitlines()
+            assert tab[0] == "i,x,y,z" and len(tab) == 1 + 2 * K and tab[1].split(",")[0] == "1" and sv.shape == (K, 3)
+            assert reduction_tests.nl_postprocess_tests(bases) == [True, True, True]
         # geometric DEIM through the differential operator (main.py:132-134): picks are a prefix of the reference's
         from scipy import sparse
         g = golden("bar_geom")

@@ -166,13 +166,13 @@ def test_multifrontal_symbolic_and_numeric(nx, leaf, ground):
 def test_pos_components_protocol_host_logic(tmp_path):
     """posSnapshots / posComponents drop-in protocol with the numpy statement of the kernels (host logic only)."""
     import api_checks
-    assert api_checks.check_pos_protocol(NumpyOps(), engine.Comm(enabled=False), tmp_path)
+    assert api_checks.check_pos_protocol(NumpyOps(), engine.Comm(enabled=False), tmp_path, extended=True)
 
 
 def test_constraints_components_protocol_host_logic(tmp_path):
     """nonlinearSnapshots / constraintsComponents drop-in protocol (main.py:106-142) with the numpy statement of the kernels."""
     import api_checks
-    assert api_checks.check_constraints_protocol(NumpyOps(), engine.Comm(enabled=False), tmp_path, consumer=True)
+    assert api_checks.check_constraints_protocol(NumpyOps(), engine.Comm(enabled=False), tmp_path, extended=True)
 
 
 def test_preprocess_and_off_sequence_ingest(tmp_path):

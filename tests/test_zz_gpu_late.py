@@ -27,9 +27,14 @@ def test_verts_geometric_deim(cuda_ops):
 
 def test_constraints_protocol_with_consumer(cuda_ops, tmp_path):
     import api_checks
-    assert api_checks.check_constraints_protocol(cuda_ops, engine.Comm(enabled=False), tmp_path, consumer=True)
+    assert api_checks.check_constraints_protocol(cuda_ops, engine.Comm(enabled=False), tmp_path, extended=True)
 
 
 def test_verts_geometric_deim_protocol(cuda_ops, tmp_path):
     import api_checks
     assert api_checks.check_verts_geom_protocol(cuda_ops, engine.Comm(enabled=False), tmp_path)
+
+
+def test_pos_protocol_with_figure_tables(cuda_ops, tmp_path):
+    import api_checks
+    assert api_checks.check_pos_protocol(cuda_ops, engine.Comm(enabled=False), tmp_path, extended=True)
