@@ -1,4 +1,4 @@
-"""`-m gpu` parity checks added after the round's last GPU session, kept in a file that sorts last: the consumer-side
+"""`-m gpu` parity checks added at the very end of r01, kept in a file that sorts last: the consumer-side
 operators, the '_verts' geometric DEIM and the real-mesh runs against the live oracle.  They go through
 kernels whose own parity tests run earlier in the suite (asb_spmv_csr, asb_gemm_nn, asb_ingest / asb_export_aos, ...)."""
 import pytest
