@@ -107,9 +107,10 @@ def write_mass_bin(path, mass):
 
 
 def _h5py():
+    """The real h5py when it is installed (a stand-in module registered by a test shim does not count)."""
     try:
         import h5py
-        return h5py
+        return h5py if isinstance(h5py.version.version, str) else None
     except Exception:
         return None
 
