@@ -52,7 +52,7 @@ NO_CON = {"computeState": {"compute": False, "run_main": True}}
 
 def test_reference_main_drives_pos_components(reference_main):
     """main.py:19-100 with a config.json shaped like config/examples/bunny_gFall_posSubspace.json (repaired: valid JSON,
-    `volumetric` and `run_main` keys present), SPLOCS on, local support."""
+    `volumetric` and `run_main` keys present), SPLOCS on, local support, run_tests on."""
     g = golden("pos_grid")
     F, N, _ = g["anim"].shape
     K = int(g["K"])
@@ -67,7 +67,7 @@ def test_reference_main_drives_pos_components(reference_main):
                "orthogonalized": "_nonOrthogonalized", "support": {"min_dist": 0.1, "max_dist": 0.25},
                "pca": {"compute": True, "numComponents": K, "supported": "_Local", "store_sing_val": True},
                "splocs": {"compute": True, "max_itrs": int(its), "admm_num_itrs": int(admm), "lambda": float(lam), "rho": float(rho)},
-               "store": True, "run_tests": False, "visualize": False},
+               "store": True, "run_tests": True, "visualize": False},
            "constraintProj_bases": NO_CON}
     param = _params(cfg)
     os.makedirs(param.aligned_snapshots_directory, exist_ok=True)
@@ -97,6 +97,13 @@ def test_reference_main_drives_pos_components(reference_main):
         B = np.frombuffer(raw[8:], "<f8").reshape(3, k, N).transpose(1, 2, 0)
         assert rel(B, post[:k]) < 1e-7
     assert os.path.exists(os.path.join(out, "components.npz")) or os.path.exists(os.path.join(out, "components.h5"))
+    # run_tests = true: the reference's own figure script (generate_figures/pos_reduction_tests.py, pyplot stubbed) consumed the
+    # object: its singular-value table is there and carries what reduction_tests.pos_pca_tests (headless) writes
+    tab = open(os.path.join(out, "grid_posBases_xyz_fullBasesRange_K_singVals.csv")).read().splitlines()
+    assert tab[0] == "row,x,y,z" and len(tab) == K + 1
+    ref_s = port.bases_sing_vals(post)
+    got_s = np.array([[float(v) for v in r.split(",")[1:]] for r in tab[1:]])
+    assert np.allclose(got_s, ref_s, atol=1e-7)
 
 
 def test_reference_main_drives_constraints_components(reference_main):
@@ -120,7 +127,7 @@ def test_reference_main_drives_constraints_components(reference_main):
                "basis_type": "pod_vectorized", "interpolation_type": "deim", "desired_num_components": K, "numComponents_verts": 5,
                "bases_res_tol": 98, "dim": 3, "constraintsDim": 1, "max_element_per_geom_vert": 100000000, "rest_shape": "first",
                "massWeighted": "_Volkwein", "standarized": "_Standarized", "supported": "_Global", "orthogonalized": "_Orthogonalized",
-               "store_sing_val": True, "store_to_files": True, "run_tests": False, "visualize_elements_at_bases_num": 30,
+               "store_sing_val": True, "store_to_files": True, "run_tests": True, "visualize_elements_at_bases_num": 30,
                "visualize_geom_elements": 528}}
     param = _params(cfg)
     os.makedirs(os.path.dirname(param.constProj_input_snapshots_pattern), exist_ok=True)
@@ -146,3 +153,12 @@ def test_reference_main_drives_constraints_components(reference_main):
         assert np.allclose((U * b["mass"][None]) @ U.T, np.eye(K), atol=1e-8), "orthogonalised + un-weighted: U^T M U = I"
     assert z["Pt"].shape == (K,) and len(np.unique(z["Pt"])) == K and np.array_equal(z["interpol_alphas"], z["Pt"] // 3)
     assert np.array_equal(z["interpol_alpha_ranges"], np.arange(1, K + 1))
+    # run_tests = true: the reference's nl_reduction_tests figure script (pyplot / polyscope stubbed) drove geom_constructed
+    # and the error statics over the object and wrote its convergence tables
+    stem = os.path.join(param.constProj_output_directory, "bar_tets_deformation_gradient_deim_pod_vectorized")
+    tab = open(stem + "_train_convergence_tests.csv").read().splitlines()
+    assert tab[0].startswith("numPoints,fro_error,max_err") and len(tab) == K + 1
+    ref_rows = np.array([[float(v) for v in r.split(",")] for r in tab[1:]])
+    assert os.path.exists(stem + "_test_convergence_tests.csv") and os.path.exists(stem + "_num_interpol_elemnets.csv")
+    # (not monotone: the reference reconstructs from element ids used as row ids, constraintsComponents.py:512)
+    assert np.isfinite(ref_rows).all() and ref_rows[0, 1] > ref_rows[-1, 1] > 0 and np.array_equal(ref_rows[:, 0], np.arange(1, K + 1))
