@@ -152,6 +152,7 @@ class nonlinearSnapshots:
                 f"{self.mass_file}: the reference derives element masses from libigl's mass matrix here "
                 "(snapbases/nonlinear_snapshots.py:193-241); libigl is a third-party dependency that is not available. "
                 "Supply the mass .bin (hostio.write_mass_bin of element_masses_from_vertex_masses(...))")
+        self._read_connectivity()
         massL = np.sqrt(self.mass)
         assert np.allclose(massL * massL - self.mass, 0.0)
         invMassL = np.zeros(n)
@@ -159,6 +160,18 @@ class nonlinearSnapshots:
         invMassL[nz] = 1.0 / massL[nz]
         assert np.allclose(invMassL * massL, np.ones(n))
         self.massL, self.invMassL = massL, invMassL
+
+    def _read_connectivity(self):
+        """verts / tets / tris of the rest mesh when its file exists.  The reference reads them only on its libigl branch
+        (nonlinear_snapshots.py:197-241, i.e. when no mass file is given), yet the geometric DEIM needs them (:684-690 of
+        constraintsComponents.py); reading them alongside the mass file lets `interpolation_type: geom` run under main.py."""
+        from ..synth import read_medit_mesh, read_obj_mesh
+        if self.tets is None and self.tet_mesh and os.path.exists(self.tet_mesh):
+            self.verts, self.tets, tris = read_medit_mesh(self.tet_mesh)
+            if len(tris):
+                self.tris = tris
+        if self.tris is None and self.tri_mesh and os.path.exists(self.tri_mesh):
+            self.verts, self.tris = read_obj_mesh(self.tri_mesh)
 
     @log_time("")
     def standarize(self):

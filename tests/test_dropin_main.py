@@ -162,3 +162,66 @@ def test_reference_main_drives_constraints_components(reference_main):
     assert os.path.exists(stem + "_test_convergence_tests.csv") and os.path.exists(stem + "_num_interpol_elemnets.csv")
     # (not monotone: the reference reconstructs from element ids used as row ids, constraintsComponents.py:512)
     assert np.isfinite(ref_rows).all() and ref_rows[0, 1] > ref_rows[-1, 1] > 0 and np.array_equal(ref_rows[:, 0], np.arange(1, K + 1))
+
+
+def _write_medit(path, verts, tets):
+    with open(path, "w") as fh:
+        fh.write("MeshVersionFormatted 1\nDimension 3\nVertices\n%d\n" % len(verts))
+        fh.writelines("%.17g %.17g %.17g 0\n" % tuple(v) for v in verts)
+        fh.write("Tetrahedra\n%d\n" % len(tets))
+        fh.writelines("%d %d %d %d 0\n" % tuple(t + 1) for t in tets)
+        fh.write("End\n")
+
+
+def test_reference_main_drives_geometric_interpolation(reference_main):
+    """main.py:102-142 with `basis_type: pca_blocks`, `interpolation_type: geom` (shaped like
+    config/examples/bar_automated_geom_tetDeformationGradientSubspace.json): block deflation -> post-process -> geometric DEIM
+    through the pickled `assembly_ST.npz` -> the simulator's .npz.  Block signs are free (and post-processing adds the mean),
+    so the picks are checked structurally here; the sign-pinned comparison with the reference's picks is check_bar_geom."""
+    from scipy import sparse
+    b, g, m = golden("bar"), golden("bar_geom"), golden("meshes")
+    F, ep, _ = b["snaps"].shape
+    tets = b["tets"].astype(np.int64)
+    nb, per_vert = 4, 2
+    folder = "/constraint_projection/FOM/tets_deformation_gradient"
+    cfg = {"object": {"experiment_dir": "pd_out/", "mesh": "bar", "volumetric": True, "experiment": "bar_defgrad/", "snap_format": ".off"},
+           "vertexPos_bases": NO_POS,
+           "constraintProj_bases": {
+               "computeState": {"compute": True, "run_main": True, "testingComputations": "_Release"},
+               "constraintType": {"name": "tets_deformation_gradient", "elements": "_tets", "p_snaps_folder": folder,
+                                  "pos_snaps_folder": "/position_snapshots/FOM", "geom_pos_snaps_folder": "/position_snapshots/geom/",
+                                  "assembly_file_name": "assembly_ST.npz", "assembly_key": "tets_deformation_gradient",
+                                  "snaps_pattern_full_p": "/tets_deformation_gradient_p.npz", "constrained_elements": "", "rowSize": 3},
+               "snapshots": {"max_numFrames": F, "numFrames": F, "frame_increment": 1, "read_all_from_first": True,
+                             "processed_snapshots_file": "/processed_snapshots/", "preAlignement": "_noAlignement",
+                             "processed_snapshots_ready": False, "reduced_snaps_available": False},
+               "basis_type": "pca_blocks", "interpolation_type": "geom", "desired_num_components": nb, "numComponents_verts": 5,
+               "bases_res_tol": 1e-12, "dim": 3, "constraintsDim": 1, "max_element_per_geom_vert": per_vert, "rest_shape": "first",
+               "massWeighted": "_Volkwein", "standarized": "_Standarized", "supported": "_Global", "orthogonalized": "_Orthogonalized",
+               "store_sing_val": True, "store_to_files": True, "run_tests": False, "visualize_elements_at_bases_num": 30,
+               "visualize_geom_elements": 528}}
+    param = _params(cfg)
+    os.makedirs(os.path.dirname(param.constProj_input_snapshots_pattern), exist_ok=True)
+    np.savez(param.constProj_input_snapshots_pattern, **{str(i): b["snaps"][i] for i in range(F)})
+    St = sparse.csr_matrix((g["St_vals"], g["St_colidx"], g["St_rowptr"]), shape=tuple(g["St_shape"]))
+    np.savez(param.constProj_weightedSt, tets_deformation_gradient=St)          # pickled scipy sparse, as the simulator stores it
+    os.makedirs(os.path.dirname(param.constProj_masses_file), exist_ok=True)
+    hostio.write_mass_bin(param.constProj_masses_file, b["mass"])
+    _write_medit(param.tet_mesh_file, m["bar_verts"], tets)
+
+    reference_main.main(param)
+
+    z = np.load(os.path.join(param.constProj_output_directory, "components_interpol_alphas_interpol_verts_interpol_alpha_ranges.npz"),
+                allow_pickle=True)
+    comps, alphas, Pt, verts, ranges = (z[k] for k in ("components", "interpol_alphas", "Pt", "interpol_verts", "interpol_alpha_ranges"))
+    assert comps.shape == (3 * nb, ep, 3) and len(verts) == nb and len(ranges) == nb
+    assert np.array_equal(Pt, (alphas[:, None] * 3 + np.arange(3)[None]).ravel()) and len(np.unique(alphas)) == len(alphas)
+    steps = np.diff(np.concatenate([[0], ranges]))
+    assert ranges[-1] == len(alphas) and np.all(steps >= 0) and np.all(steps <= per_vert)
+    start = 0
+    for v, stop in zip(verts, ranges):
+        assert all(v in tets[a] for a in alphas[start:stop]), "every new element is incident to the vertex picked in that step"
+        start = stop
+    # and the emitted file is what the simulator-side precompute consumes (Simulators.py:157-218)
+    pm = port.prepare_reduced_group(z, nb, 3, St, "geom_pca_blocks_withSt")[2]
+    assert pm.shape == (St.shape[0], 3 * nb, 3) and np.isfinite(pm).all()
