@@ -282,3 +282,15 @@ def convert_sequence_to_hdf5(filename_pattern, loader_function, hdf_output_file,
         np.savez(out, verts=verts_all, tris=tris, mean=verts_mean, scale=verts_scale)
     print("saved as %s" % out)
     return out
+
+
+def align(input_hdf5_file, output_hdf5_file, rigid):
+    """utils/process.py:235-250: Procrustes-align every frame of an animation file to frame 0 (rigid: rotation + translation,
+    otherwise translation only) and write `verts` (float32) / `tris` to the output file.  The per-frame centroid / 3x3
+    covariance reductions and the transform pass run on the device (asb_align_centroids / _cov / _solve / _apply); the
+    reference's Python loop over frames with a 4x4 homogeneous matmul each is gone."""
+    from . import runtime
+    ops, _ = runtime.get()
+    verts, tris = read_animation(input_hdf5_file)
+    out, _ = ops.align(ops.to_device(np.ascontiguousarray(verts, dtype=np.float32)), rigid)
+    return write_animation(output_hdf5_file, out.cpu().numpy(), tris)

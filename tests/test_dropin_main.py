@@ -225,3 +225,63 @@ def test_reference_main_drives_geometric_interpolation(reference_main):
     # and the emitted file is what the simulator-side precompute consumes (Simulators.py:157-218)
     pm = port.prepare_reduced_group(z, nb, 3, St, "geom_pca_blocks_withSt")[2]
     assert pm.shape == (St.shape[0], 3 * nb, 3) and np.isfinite(pm).all()
+
+
+def test_reference_main_imports_off_sequence(reference_main, monkeypatch):
+    """main.py:28-63, the branch that runs when the aligned animation files do not exist yet: OFF sequence -> animation file
+    -> Procrustes alignment -> bases.  `convert_sequence_to_hdf5` / `load_off` / `align` are the names main.py imports from
+    utils/process.py (h5py-bound); the maintainer's import swap of INTEGRATION.md points them at hostio.  Result against
+    the oracle pipeline run on the same raw frames."""
+    from animsnapbases_b200 import synth
+    monkeypatch.setattr(reference_main, "convert_sequence_to_hdf5", hostio.convert_sequence_to_hdf5)
+    monkeypatch.setattr(reference_main, "load_off", hostio.load_off)
+    monkeypatch.setattr(reference_main, "align", hostio.align)
+    m = synth.golden_mesh("sphere")               # a genuinely 3-D shape: rigid Procrustes of a near-planar one is ill-posed
+    verts0, tris = m["verts"], m["tris"]
+    F, K = 12, 5
+    rng = np.random.default_rng(21)
+    raw = (2.5 * synth.bump_animation(verts0, 2 * F, n_bumps=4, sigma=0.2, seed=6) + np.array([1.0, 2.0, 3.0])
+           + 0.05 * rng.standard_normal((2 * F, 1, 3))).astype(np.float32)          # unnormalised, drifting frames
+    cfg = {"object": {"mesh": "grid", "volumetric": False, "experiment": "_bumps", "experiment_dir": "data_in/", "snap_format": ".off"},
+           "vertexPos_bases": {
+               "computeState": {"compute": True, "testingComputations": "_Release"},
+               "snapshots": {"max_numFrames": 2 * F, "frame_increment": 1, "numFrames": F, "format": ".off", "snaps_folder": "fom",
+                             "read_all_from_first": True, "anims_folder": "FOM_animations_h5", "preAlignement": "_alignedRigid",
+                             "anim_folder_ready": False, "visualize_aligned_animations": False, "reduced_snaps_available": False},
+               "dim": 3, "rest_shape": "first", "massWeighted": "_Volkwein", "standarized": "_Standarized",
+               "orthogonalized": "_nonOrthogonalized", "support": {"min_dist": 0.1, "max_dist": 0.25},
+               "pca": {"compute": True, "numComponents": K, "supported": "_Global", "store_sing_val": True},
+               "splocs": {"compute": False, "max_itrs": 2, "admm_num_itrs": 2, "lambda": 2, "rho": 10.0},
+               "store": True, "run_tests": False, "visualize": False},
+           "constraintProj_bases": NO_CON}
+    param = _params(cfg)
+    os.makedirs(os.path.dirname(param.input_snapshots_pattern), exist_ok=True)
+    for f, fr in enumerate(raw):
+        with open(param.input_snapshots_files_name + "%d.off" % f, "w") as fh:
+            fh.write("OFF\n%d %d 0\n" % (len(fr), len(tris)))
+            fh.writelines("%.9g %.9g %.9g\n" % tuple(p) for p in fr)
+            fh.writelines("3 %d %d %d\n" % tuple(t) for t in tris)
+    # oracle: the same frames through the restated ingest (first F files, increment 1), rigid alignment, masses of frame 0
+    pre, _, _ = port.preprocess_unit_cube(raw[:F])
+    aligned = port.align_frames(pre, rigid=True)
+    mass = synth.lumped_vertex_masses(aligned[0].astype(float), tris)
+    os.makedirs(os.path.dirname(param.vertPos_masses_file), exist_ok=True)
+    hostio.write_mass_bin(param.vertPos_masses_file, mass)
+
+    reference_main.main(param)
+
+    got, got_tris = hostio.read_animation(os.path.join(param.aligned_snapshots_directory, param.train_aligned_snapshots_animation_file))
+    assert got.dtype == np.float32 and got.shape == aligned.shape and np.array_equal(got_tris, tris)
+    assert np.abs(got - aligned).max() < 2e-6, "float32 Procrustes: device reductions vs LAPACK"
+    test_anim, _ = hostio.read_animation(os.path.join(param.aligned_snapshots_directory, param.test_aligned_snapshots_animation_file))
+    assert test_anim.shape == (F, len(verts0), 3), "testing frames: every (increment + train_test_jump)-th file (main.py:49-51)"
+    prep = port.prepare_snapshots(got, mass, "first")
+    C, W, meas, picked, _ = port.extract_k_components(prep["snapTensor"], K, "global")
+    post = port.post_process_pos(C, prep["mean"], prep["pre_scale_factor"], prep["invMassL"], True, False, True)
+    raw_bin = open(os.path.join(param.vertPos_output_directory, "q_pos_F%dK%d.bin" % (F, K)), "rb").read()
+    B = np.frombuffer(raw_bin[8:], "<f8").reshape(3, K, len(verts0)).transpose(1, 2, 0)
+    # global support: the sign of each (w, c) pair is free and un-standardising adds the mean, so compare per component
+    # against both signs of the oracle's c_k
+    flipped = port.post_process_pos(-C, prep["mean"], prep["pre_scale_factor"], prep["invMassL"], True, False, True)
+    for k in range(K):
+        assert min(rel(B[k], post[k]), rel(B[k], flipped[k])) < 1e-7, k
