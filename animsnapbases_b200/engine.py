@@ -59,6 +59,22 @@ class Comm:
         if self.world > 1:
             self.dist.barrier()
 
+    def on_rank0(self, fn):
+        """File output: run fn() on rank 0 only.  Every rank returns after it has finished (the files exist when a writer
+        method returns, whichever rank looks), and an exception it raised is re-raised on every rank."""
+        err = None
+        if self.rank == 0:
+            try:
+                fn()
+            except Exception as e:          # noqa: BLE001 -- re-raised below, on all ranks
+                err = e
+        if self.world > 1:
+            box = [err]
+            self.dist.broadcast_object_list(box, src=0)
+            err = box[0]
+        if err is not None:
+            raise err
+
     def all_to_all(self, send):
         """send[j]: equally shaped tensor for rank j -> list of the tensors every rank addressed to this one.
         NCCL: one all_to_all (NVLink, each byte crosses once); gloo (CPU tests) has none: all_gather of the stacks."""
@@ -800,6 +816,14 @@ def sparsity_and_rank(ops, comm, T, shard, K):
     for sig in row_singular_values(ops, comm, T, shard, K):
         ranks.append(int((sig > sig[0] * max(shard.n_global, K) * np.finfo(np.float64).eps).sum()))
     return sparsity, ranks
+
+
+def host_rows(ops, comm, T, shard, row_scale=None):
+    """Planar (R, 3, ld) row-sharded device tensor -> the reference's host layout (R, n_global, 3), complete on every rank
+    (the attribute views `comps`, `snapTensor`, `mean` of the drop-in classes: scripts written against the reference index
+    them by global row).  Lazy and only for outputs; nothing on the build path calls it."""
+    out = ops.export_aos(T, row_scale, shard.n).cpu().numpy()
+    return gather_rows_host(comm, out, shard, axis=1) if comm.world > 1 else out
 
 
 def gather_rows_host(comm, arr, shard, axis):

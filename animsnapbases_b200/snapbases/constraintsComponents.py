@@ -62,8 +62,8 @@ class constraintsComponents:  # Components == bases
         if self._C is None:
             return None
         if "comps" not in self._host:
-            ops, _ = runtime.get()
-            self._host["comps"] = ops.export_aos(self._C, None, self.nonlinearSnapshots.shard.n).cpu().numpy()
+            ops, comm = runtime.get()
+            self._host["comps"] = engine.host_rows(ops, comm, self._C, self.nonlinearSnapshots.shard)
         return self._host["comps"]
 
     @property
@@ -131,13 +131,19 @@ class constraintsComponents:  # Components == bases
                    "pca_blocks": self.compute_nonlinearity_bases_blocks}[kind]
         _, comm = runtime.get()
         file_name = os.path.join(p.constProj_output_directory, p.name + "_" + p.constProj_name + self.file_name_sing)
-        if self.storeSingVal and comm.rank == 0:
-            with open(file_name + '.csv', 'w', encoding='UTF8') as singFile:
-                writer = csv.writer(singFile)
-                writer.writerow(headerSing)
-                compute(writer)
-        else:
-            compute(None)
+        rows = []                                      # collected on every rank (collectives inside), written by rank 0
+
+        class _Rows:
+            writerow = staticmethod(rows.append)
+
+        compute(_Rows if self.storeSingVal else None)
+        if self.storeSingVal:
+            def write():
+                with open(file_name + '.csv', 'w', encoding='UTF8') as singFile:
+                    writer = csv.writer(singFile)
+                    writer.writerow(headerSing)
+                    writer.writerows(rows)
+            comm.on_rank0(write)
 
     @log_time("")
     def compute_nonlinearity_bases_blocks(self, writer=None):
@@ -345,11 +351,7 @@ class constraintsComponents:  # Components == bases
 
     # ------------------------------------------------------------------ outputs
     def _gathered_comps(self):
-        _, comm = runtime.get()
-        c = self.comps
-        if comm.world > 1:
-            c = engine.gather_rows_host(comm, c, self.nonlinearSnapshots.shard, axis=1)
-        return c
+        return self.comps                    # complete (all row shards) on every rank
 
     @log_time("")
     def store_components_gradually_to_files(self, start, end, step, fileType):
@@ -366,12 +368,13 @@ class constraintsComponents:  # Components == bases
         packed = ops.pack_bin(self._C, self._rows, snaps.shard.n).cpu().numpy()        # (3, Kp, ep): the .bin body order
         if comm.world > 1:
             packed = engine.gather_rows_host(comm, packed, snaps.shard, axis=2)
-        if comm.rank == 0:
+        def write():
             for k in range(start, end + 1, step):
                 hostio.store_components_packed(basesFile, snaps.frs, k * p, numverts, 3, packed, fileType, 'Kp')
                 hostio.store_interpol_points_vector(pointsFile, snaps.frs, k,
                                                     self.geom_alpha[:self.geom_alpha_ranges[k - 1]], fileType)
                 hostio.store_interpol_points_vector(vertsFile, snaps.frs, k, self.geom_interpol_verts[:k], fileType)
+        comm.on_rank0(write)
         print('done.')
 
     @log_time("")
@@ -380,9 +383,8 @@ class constraintsComponents:  # Components == bases
         print('Storing bases and interpolation points to one file ...', end='', flush=True)
         _, comm = runtime.get()
         comps = self._gathered_comps()
-        if comm.rank == 0:
-            np.savez(os.path.join(self.param.constProj_output_directory,
-                                  "components_interpol_alphas_interpol_verts_interpol_alpha_ranges.npz"),
-                     components=comps, interpol_alphas=self.geom_alpha, Pt=self.geom_Pt,
-                     interpol_verts=self.geom_interpol_verts, interpol_alpha_ranges=self.geom_alpha_ranges)
+        comm.on_rank0(lambda: np.savez(
+            os.path.join(self.param.constProj_output_directory, "components_interpol_alphas_interpol_verts_interpol_alpha_ranges.npz"),
+            components=comps, interpol_alphas=self.geom_alpha, Pt=self.geom_Pt,
+            interpol_verts=self.geom_interpol_verts, interpol_alpha_ranges=self.geom_alpha_ranges))
         print("done!")

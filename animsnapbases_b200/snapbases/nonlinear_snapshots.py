@@ -57,16 +57,16 @@ class nonlinearSnapshots:
         if self.state is None:
             return self._raw
         if "snapTensor" not in self._host:
-            ops, _ = runtime.get()
-            self._host["snapTensor"] = ops.export_aos(self.state.X, None, self.shard.n).cpu().numpy()
+            ops, comm = runtime.get()
+            self._host["snapTensor"] = engine.host_rows(ops, comm, self.state.X, self.shard)
         return self._host["snapTensor"]
 
     @property
     def mean(self):
         if self.state is None or self.state.mean is None:
             return None
-        ops, _ = runtime.get()
-        return ops.export_aos(self.state.mean[None], None, self.shard.n).cpu().numpy()[0]
+        ops, comm = runtime.get()
+        return engine.host_rows(ops, comm, self.state.mean[None], self.shard)[0]
 
     def invalidate_host_views(self):
         self._host = {}

@@ -46,8 +46,8 @@ class posComponents:  # Components == bases
 
     # ------------------------------------------------------------------ host views (reference attribute names)
     def _aos(self, T):
-        ops, _ = runtime.get()
-        return ops.export_aos(T, None, self.pos_snapshots.shard.n).cpu().numpy()
+        ops, comm = runtime.get()
+        return engine.host_rows(ops, comm, T, self.pos_snapshots.shard)     # complete (all row shards) on every rank
 
     @property
     def comps(self):
@@ -141,13 +141,19 @@ class posComponents:  # Components == bases
         file_name = os.path.join(self.param.vertPos_output_directory,
                                  self.param.name + "_posBases_pcaExtraction_singValues_errorNorm")
         _, comm = runtime.get()
-        if self.storeSingVal and comm.rank == 0:
-            with open(file_name + '.csv', 'w', encoding='UTF8') as singFile:
-                writer = csv.writer(singFile)
-                writer.writerow(headerSing)
-                self.extract_k_components(writer)
-        else:
-            self.extract_k_components(None)
+        rows = []                                      # collected on every rank (collectives inside), written by rank 0
+
+        class _Rows:
+            writerow = staticmethod(rows.append)
+
+        self.extract_k_components(_Rows if self.storeSingVal else None)
+        if self.storeSingVal:
+            def write():
+                with open(file_name + '.csv', 'w', encoding='UTF8') as singFile:
+                    writer = csv.writer(singFile)
+                    writer.writerow(headerSing)
+                    writer.writerows(rows)
+            comm.on_rank0(write)
 
     # ------------------------------------------------------------------ post-processing
     @log_time("")
@@ -167,9 +173,7 @@ class posComponents:  # Components == bases
             assert snaps.nVerts == snaps.invMassL.shape[0]
             aos = ops.export_aos(C, snaps.state.invMassL, sh.n)                        # comps *= invMassL[:, None]
             self._C = C = ops.ingest(aos, None, sh.ld)
-            self._host = {"comps": aos.cpu().numpy()}
-        else:
-            self._host = {}
+        self._host = {}
         sparsity, ranks = engine.sparsity_and_rank(ops, comm, C, sh, self.numComp)
         if min(sparsity) > 0.5:
             print("sparse, min %" + str(100 * min(sparsity)) + " zero entries.")
@@ -207,15 +211,18 @@ class posComponents:  # Components == bases
         packed = ops.pack_bin(self._C, self.numComp, snaps.shard.n).cpu().numpy()     # (3, K, N): the .bin body order
         if comm.world > 1:
             packed = engine.gather_rows_host(comm, packed, snaps.shard, axis=2)
-        if comm.rank == 0:
+        def write():
             for k in range(start, end + 1, step):
                 hostio.store_components_packed(basesFile, snaps.frs, k, snaps.nVerts, 3, packed, fileType, 'K')
+        comm.on_rank0(write)
         print('done.')
 
     @log_time("")
     def store_animations(self, output_bases_dir):
+        _, comm = runtime.get()
         out = os.path.join(output_bases_dir, self.output_components_file)
-        hostio.write_components_animation(out, self.pos_snapshots.verts[0], self.pos_snapshots.tris, self.comps)
+        comps = self.comps
+        comm.on_rank0(lambda: hostio.write_components_animation(out, self.pos_snapshots.verts[0], self.pos_snapshots.tris, comps))
 
     @log_time("")
     def test_basesSingVals(self):

@@ -43,13 +43,13 @@ class posSnapshots:
     # ---- lazily materialised host views of device tensors (reference attribute names)
     @property
     def snapTensor(self):
-        ops, _ = runtime.get()
-        return ops.export_aos(self.state.X, None, self.shard.n).cpu().numpy()
+        ops, comm = runtime.get()
+        return engine.host_rows(ops, comm, self.state.X, self.shard)
 
     @property
     def mean(self):
-        ops, _ = runtime.get()
-        return ops.export_aos(self.state.mean[None], None, self.shard.n).cpu().numpy()[0]
+        ops, comm = runtime.get()
+        return engine.host_rows(ops, comm, self.state.mean[None], self.shard)[0]
 
     @log_time("")
     def do_snapshots_precomputations(self, standarize, massWeight):

@@ -10,11 +10,24 @@ from animsnapbases_b200 import hostio, runtime
 from oracle import port
 
 
+def _inputs_once(tmp, write):
+    """Input fixtures of a protocol check: written by rank 0 only (several ranks share the directory under torchrun), once."""
+    _, comm = runtime.get()
+    marker = os.path.join(str(tmp), ".inputs_written")
+    if comm.rank == 0 and not os.path.exists(marker):
+        write()
+        open(marker, "w").close()
+    comm.barrier()
+
+
 def pos_param(tmp, g, bases_type="PCA", support="local", orthogonal=False):
     d = str(tmp)
-    hostio.write_animation(os.path.join(d, "train.h5"), g["anim"], g["tris"])
-    hostio.write_animation(os.path.join(d, "test.h5"), g["anim"][::2], g["tris"])
-    hostio.write_mass_bin(os.path.join(d, "mass.bin"), g["mass"])
+
+    def write():
+        hostio.write_animation(os.path.join(d, "train.h5"), g["anim"], g["tris"])
+        hostio.write_animation(os.path.join(d, "test.h5"), g["anim"][::2], g["tris"])
+        hostio.write_mass_bin(os.path.join(d, "mass.bin"), g["mass"])
+    _inputs_once(tmp, write)
     it, admm, lam, rho = g["splocs"]
     return types.SimpleNamespace(
         vertPos_bases_type=bases_type, aligned_snapshots_directory=d, train_aligned_snapshots_animation_file="train.h5",
@@ -93,8 +106,11 @@ def check_pos_protocol(ops, comm, tmp, name="pos_grid", extended=False):
 def constraints_param(tmp, b, k_desired):
     d = str(tmp)
     snaps = b["snaps"]
-    np.savez(os.path.join(d, "bar_p.npz"), **{str(i): snaps[i] for i in range(snaps.shape[0])})
-    hostio.write_mass_bin(os.path.join(d, "elem_mass.bin"), b["mass"])
+
+    def write():
+        np.savez(os.path.join(d, "bar_p.npz"), **{str(i): snaps[i] for i in range(snaps.shape[0])})
+        hostio.write_mass_bin(os.path.join(d, "elem_mass.bin"), b["mass"])
+    _inputs_once(tmp, write)
     return types.SimpleNamespace(
         constProj_input_snapshots_pattern=os.path.join(d, "bar_p.npz"), constProj_rest_shape="first", constProj_dim=3,
         constProj_masses_file=os.path.join(d, "elem_mass.bin"), constProj_numFrames=snaps.shape[0], constProj_p_size=3,

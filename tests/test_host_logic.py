@@ -133,6 +133,18 @@ def test_two_rank_gloo_row_sharding(world):
     assert all(f"RANK{i} OK" in r.stdout for i in range(world))
 
 
+def test_two_rank_gloo_mirror_classes(tmp_path):
+    """The drop-in classes under torchrun (gloo, 2 ranks): main.py's two protocols with the rows sharded, host attribute views
+    complete on every rank, files written by rank 0 and visible to every rank when the writer returns."""
+    port_no = "29671"
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=port_no, PYTHONPATH=ROOT + os.pathsep + os.path.join(ROOT, "tests"))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", port_no, os.path.join(ROOT, "tests", "gloo_api_worker.py"), str(tmp_path)],
+                       capture_output=True, text=True, env=env, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert all(f"RANK{i} OK" in r.stdout for i in range(2))
+
+
 @pytest.mark.parametrize("nx,leaf,ground", [(40, 16, None), (40, 16, 3), (7, 64, None)])
 def test_multifrontal_symbolic_and_numeric(nx, leaf, ground):
     """Host side of animsnapbases_b200/mfsolve.py (ordering, symbolic maps, batched numeric factorisation with torch on the
