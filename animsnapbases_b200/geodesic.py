@@ -22,7 +22,6 @@ The mesh operator is global: with row-sharded snapshots every rank solves on the
 from __future__ import annotations
 
 import numpy as np
-import torch
 from scipy import sparse
 
 

@@ -2,7 +2,6 @@
 import os
 import sys
 
-import torch
 import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
