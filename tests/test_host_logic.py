@@ -252,3 +252,29 @@ def test_sparse_operator_files(tmp_path):
         hostio.write_sparse_matrix_to_bin(path, A)
         assert (abs(ref_utils.read_sparse_matrix_from_bin(path) - A)).nnz == 0
     del rng
+
+
+def test_header_is_plain_c_and_links(tmp_path):
+    """include/asb.h is the boundary a non-Python host binds: it must compile as strict C99 and as C++17, and a program
+    linked against libasb.so must resolve the entry points (no compute call: there is no GPU here)."""
+    import shutil
+    if shutil.which("gcc") is None or shutil.which("g++") is None:
+        pytest.skip("no host compiler")
+    lib_dir = os.path.join(ROOT, "animsnapbases_b200", "lib")
+    if not os.path.exists(os.path.join(lib_dir, "libasb.so")):
+        pytest.skip("libasb.so not built")
+    src = tmp_path / "host.c"
+    src.write_text('#include "asb.h"\n#include <stdio.h>\n'
+                   'int main(void) {\n'
+                   '    int (*solve)(const double*, int64_t, const double*, double*, double*, const double*, int64_t, int64_t, int64_t,\n'
+                   '                 double, int64_t, asb_stream_t) = asb_admm_solve;   /* signature check against the header */\n'
+                   '    const char* e = asb_last_error();\n'
+                   '    printf("%d %d %s\\n", asb_version(), solve != 0, e ? "str" : "null");\n'
+                   '    return 0;\n}\n')
+    for cc, std, extra in (("gcc", "-std=c99", ["-pedantic"]), ("g++", "-std=c++17", ["-x", "c++"])):
+        exe = tmp_path / ("host_" + cc.replace("+", "p"))
+        r = subprocess.run([cc, std, "-Wall", "-Wextra", "-Werror", *extra, "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe),
+                            "-L", lib_dir, "-lasb", "-Wl,-rpath," + lib_dir], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
+        assert out.returncode == 0 and out.stdout.split() == ["100", "1", "str"], out.stdout + out.stderr
