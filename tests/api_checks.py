@@ -10,10 +10,10 @@ from animsnapbases_b200 import hostio, runtime
 from oracle import port
 
 
-def _inputs_once(tmp, write):
+def _inputs_once(tmp, write, tag):
     """Input fixtures of a protocol check: written by rank 0 only (several ranks share the directory under torchrun), once."""
     _, comm = runtime.get()
-    marker = os.path.join(str(tmp), ".inputs_written")
+    marker = os.path.join(str(tmp), ".inputs_written_" + tag)
     if comm.rank == 0 and not os.path.exists(marker):
         write()
         open(marker, "w").close()
@@ -27,7 +27,7 @@ def pos_param(tmp, g, bases_type="PCA", support="local", orthogonal=False):
         hostio.write_animation(os.path.join(d, "train.h5"), g["anim"], g["tris"])
         hostio.write_animation(os.path.join(d, "test.h5"), g["anim"][::2], g["tris"])
         hostio.write_mass_bin(os.path.join(d, "mass.bin"), g["mass"])
-    _inputs_once(tmp, write)
+    _inputs_once(tmp, write, "pos")
     it, admm, lam, rho = g["splocs"]
     return types.SimpleNamespace(
         vertPos_bases_type=bases_type, aligned_snapshots_directory=d, train_aligned_snapshots_animation_file="train.h5",
@@ -110,7 +110,7 @@ def constraints_param(tmp, b, k_desired):
     def write():
         np.savez(os.path.join(d, "bar_p.npz"), **{str(i): snaps[i] for i in range(snaps.shape[0])})
         hostio.write_mass_bin(os.path.join(d, "elem_mass.bin"), b["mass"])
-    _inputs_once(tmp, write)
+    _inputs_once(tmp, write, "constraints")
     return types.SimpleNamespace(
         constProj_input_snapshots_pattern=os.path.join(d, "bar_p.npz"), constProj_rest_shape="first", constProj_dim=3,
         constProj_masses_file=os.path.join(d, "elem_mass.bin"), constProj_numFrames=snaps.shape[0], constProj_p_size=3,

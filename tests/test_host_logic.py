@@ -278,3 +278,70 @@ def test_header_is_plain_c_and_links(tmp_path):
         assert r.returncode == 0, r.stderr
         out = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
         assert out.returncode == 0 and out.stdout.split() == ["100", "1", "str"], out.stdout + out.stderr
+
+
+def test_mirror_error_behaviour(tmp_path):
+    """SURVEY 8(b) 'Errors': the drop-in classes keep the reference's exception types -- AssertionError for an unknown position
+    basis type (posComponents.py:22), SystemExit(1) for an unknown rest shape (posSnapshots.py:93, nonlinear_snapshots.py:278),
+    ValueError for an unknown constraint basis type (constraintsComponents.py:141,153), for local support on constraint
+    bases (:376) and for unknown frames to reconstruct (:503); a missing mass file is a FileNotFoundError that names the absent
+    third-party fallback (libigl) instead of a CPU path."""
+    import api_checks
+    from conftest import golden
+    from animsnapbases_b200 import runtime
+    from animsnapbases_b200.snapbases.constraintsComponents import constraintsComponents
+    from animsnapbases_b200.snapbases.posComponents import posComponents
+    runtime.install(NumpyOps(), engine.Comm(enabled=False))
+    cwd = os.getcwd()
+    os.chdir(str(tmp_path))
+    try:
+        g, b = golden("pos_grid"), golden("bar")
+        with pytest.raises(AssertionError):
+            posComponents(api_checks.pos_param(tmp_path, g, bases_type="NMF"))
+        p = api_checks.pos_param(tmp_path, g)
+        p.vertPos_rest_shape = "median"
+        with pytest.raises(SystemExit) as ex:
+            posComponents(p)
+        assert ex.value.code == 1
+        p = api_checks.pos_param(tmp_path, g)
+        p.vertPos_masses_file = os.path.join(str(tmp_path), "absent.bin")
+        with pytest.raises(FileNotFoundError, match="libigl"):
+            posComponents(p)
+
+        def constraints(**over):
+            cp = api_checks.constraints_param(tmp_path, b, 6)
+            for k, v in over.items():
+                setattr(cp, k, v)
+            cc = constraintsComponents(cp)
+            cc.nonlinearSnapshots.config()
+            cc.config(fileNameBases="p_nl_", fileName_geom_points="p_nl_interpol_points_")
+            return cc
+        cc = constraints(constProj_rest_shape="median")
+        with pytest.raises(SystemExit) as ex:
+            cc.nonlinearSnapshots.snapshots_prepare()
+        assert ex.value.code == 1
+        cc = constraints(constProj_basis_type="nmf")
+        cc.nonlinearSnapshots.snapshots_prepare()
+        with pytest.raises(ValueError):
+            cc.compute_components_store_singvalues()
+        cc = constraints(constProj_basis_type="pca_blocks", constProj_support="local")
+        cc.nonlinearSnapshots.snapshots_prepare()
+        with pytest.raises(ValueError, match="Local support"):
+            cc.compute_components_store_singvalues()
+        cc = constraints(constProj_basis_type="pca_blocks_with_St")
+        cc.nonlinearSnapshots.snapshots_prepare()
+        with pytest.raises(NotImplementedError):         # defective in the reference (DESIGN.md section 7): refused, no CPU path
+            cc.compute_components_store_singvalues()
+        cc = constraints()
+        cc.nonlinearSnapshots.snapshots_prepare()
+        cc.compute_components_store_singvalues()
+        cc.post_process_components()
+        cc.deim()
+        with pytest.raises(ValueError, match="unknown frames"):
+            cc.geom_constructed(3, "validation")
+        cc = constraints(constProj_masses_file=os.path.join(str(tmp_path), "absent.bin"))
+        with pytest.raises(FileNotFoundError, match="libigl"):
+            cc.nonlinearSnapshots.snapshots_prepare()
+    finally:
+        os.chdir(cwd)
+        runtime.install(None, None)
