@@ -482,12 +482,14 @@ def deim(ops, comm, C, shard, K):
         Pt[k:k + 1].copy_(idx)
     comm.allreduce_max(maxabs)
     mx = maxabs.cpu().numpy()
-    if int(info.item()) != 0:
-        raise FloatingPointError("DEIM: singular interpolation matrix at step %d" % int(info.item()))
-    # np.allclose(r, 0) <=> max|r| <= 1e-8
+    # np.allclose(r, 0) <=> max|r| <= 1e-8.  The reference stops at the first vanishing residual (:832-834); the loop above
+    # runs on without host synchronisation, so whatever the later steps did with a repeated row (a singular interpolation
+    # matrix, flagged in `info`) is a consequence of it and is discarded with them.
     if K > 1 and np.any(mx[1:] <= 1e-8):
         print("ERROR!: zero residual!!")
         return None
+    if int(info.item()) != 0:
+        raise FloatingPointError("DEIM: singular interpolation matrix (zero pivot in column %d)" % int(info.item()))
     return Pt.cpu().numpy()
 
 

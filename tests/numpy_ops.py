@@ -296,7 +296,10 @@ class NumpyOps:
     def deim_solve(self, Vp, k, a, info):
         vp = Vp.numpy()
         for d in range(3):
-            a.numpy()[d, :k] = np.linalg.solve(vp[d, :k, :k], vp[d, :k, k])
+            try:
+                a.numpy()[d, :k] = np.linalg.solve(vp[d, :k, :k], vp[d, :k, k])
+            except np.linalg.LinAlgError:          # the kernel flags a zero pivot and leaves a_d as it was
+                info[0] = max(int(info[0]), 1)
 
     def deim_residual(self, C, N, k, a, e, maxabs):
         c = C.numpy()

@@ -109,6 +109,10 @@ def test_verts_geometric_deim_host_logic():
     assert pipeline_checks.check_verts_geom(NumpyOps(), engine.Comm(enabled=False))
 
 
+def test_zero_residual_host_logic():
+    assert pipeline_checks.check_zero_residual(NumpyOps(), engine.Comm(enabled=False))
+
+
 def test_bar_reduced_group_host_logic():
     """engine.reduced_group_operators / reduced_group_term over the numpy statement of the kernels == the reference's own
     prepare_reduced_group / get_group_reduced_term outputs (tests/golden/bar_reduced.npz)."""

@@ -38,3 +38,8 @@ def test_verts_geometric_deim_protocol(cuda_ops, tmp_path):
 def test_pos_protocol_with_figure_tables(cuda_ops, tmp_path):
     import api_checks
     assert api_checks.check_pos_protocol(cuda_ops, engine.Comm(enabled=False), tmp_path, extended=True)
+
+
+def test_zero_residual(cuda_ops):
+    """Vanishing DEIM residual: print + no result, like the reference, in all three selections."""
+    assert pipeline_checks.check_zero_residual(cuda_ops, engine.Comm(enabled=False))
