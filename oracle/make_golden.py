@@ -455,9 +455,65 @@ def bar_reduced_case():
     np.savez_compressed(os.path.join(GOLD, "bar_reduced.npz"), **out)
 
 
+# ------------------------------------------------------------------------------------------------ PD local step (n4)
+def pd_local_inputs():
+    """A few tets / triangles / edges of the bar and of a grid with seeded deformed positions (some tets inverted so that the
+    reflection branches run)."""
+    m = np.load(os.path.join(GOLD, "meshes.npz"))
+    rng = np.random.default_rng(17)
+    bv, bt = m["bar_verts"].astype(np.float64), m["bar_tets"].astype(np.int64)[::130][:24]
+    gv, gt = synth.grid_mesh(6, 5)
+    gv = gv.astype(np.float64) + 0.02 * rng.standard_normal(gv.shape)
+    gt = gt.astype(np.int64)[:30]
+    ge = np.unique(np.sort(np.concatenate([gt[:, [0, 1]], gt[:, [1, 2]], gt[:, [2, 0]]]), axis=1), axis=0)[:40]
+    qb = bv + 0.15 * rng.standard_normal(bv.shape)
+    flip = np.unique(bt[::5].ravel())
+    qb[flip, 0] = -qb[flip, 0]                                              # inverts some tets
+    qg = gv + 0.1 * rng.standard_normal(gv.shape)
+    return dict(bar_verts=bv, bar_tets=bt, bar_q=qb, grid_verts=gv, grid_tris=gt, grid_edges=ge, grid_q=qg)
+
+
+def pd_local_case():
+    """get_pi and S_i^T of the reference's constraint classes (projective_dynamics/Constraint_projections.py, unmodified, loaded
+    by ref_shim.load_pd_module) per element -> tests/golden/pd_local.npz, and oracle/pd_local.py checked against them."""
+    from scipy import sparse
+    from oracle import pd_local
+    from oracle.ref_shim import load_pd_module
+    cp = load_pd_module("Constraint_projections")
+    d = pd_local_inputs()
+    wi, smin, smax = 3.5, 0.9, 1.1
+    groups = {
+        "tet_dg": (pd_local.TetDeformationGradient(d["bar_verts"], d["bar_tets"], wi),
+                   [cp.TetDeformationGradientConstraint(list(t), wi, d["bar_verts"]) for t in d["bar_tets"]], d["bar_q"]),
+        "tet_strain": (pd_local.TetStrain(d["bar_verts"], d["bar_tets"], wi, smin, smax),
+                       [cp.TetStrainConstraint(list(t), wi, d["bar_verts"], smin, smax) for t in d["bar_tets"]], d["bar_q"]),
+        "tri_strain": (pd_local.TriStrain(d["grid_verts"], d["grid_tris"], wi, smin, smax),
+                       [cp.TriStrainConstraint(list(t), wi, d["grid_verts"], smin, smax) for t in d["grid_tris"]], d["grid_q"]),
+        "edge_spring": (pd_local.EdgeSpring(d["grid_verts"], d["grid_edges"], wi),
+                        [cp.EdgeSpringConstraint(list(t), wi, d["grid_verts"]) for t in d["grid_edges"]], d["grid_q"]),
+    }
+    out = dict(d, wi=wi, sigma=np.array([smin, smax]))
+    for name, (mine, theirs, q) in groups.items():
+        p_ref = np.concatenate([c.get_pi(q.reshape(-1)) for c in theirs], axis=0)
+        St_ref = sparse.hstack([sparse.csr_matrix(c.selection_matrix) for c in theirs]).tocsr()
+        p_mine, St_mine = mine.project(q), mine.assembly()
+        assert p_mine.shape == p_ref.shape and rel(p_mine, p_ref) < 1e-13, (name, rel(p_mine, p_ref))
+        assert St_mine.shape == St_ref.shape and abs(St_mine - St_ref).max() < 1e-12 * abs(St_ref).max(), name
+        rhs_ref = np.zeros_like(q)
+        for c in theirs:
+            c.project_wi_SiT_pi(q.reshape(-1), rhs_ref)                   # the assembled local-step term S^T p
+        assert rel(St_mine @ p_mine, rhs_ref) < 1e-12, name
+        out[name + "_p"], out[name + "_StP"] = p_ref, rhs_ref
+        print(f"pd_local {name}: {len(theirs)} elements, port vs reference p {rel(p_mine, p_ref):.1e}, S^T p {rel(St_mine @ p_mine, rhs_ref):.1e}")
+    np.savez_compressed(os.path.join(GOLD, "pd_local.npz"), **out)
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     load_reference()
+    if "--pd-only" in sys.argv:                # writes pd_local.npz only
+        with scratch_cwd():
+            return pd_local_case()
     if "--verts-only" in sys.argv:             # writes verts_geom.npz only
         with scratch_cwd():
             return verts_geom_case()
@@ -479,6 +535,7 @@ def main():
         bar_geom_case()
         bar_reduced_case()
         verts_geom_case()
+        pd_local_case()
         align_case()
         writers_case()
 

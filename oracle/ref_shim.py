@@ -43,7 +43,7 @@ class _Stub(types.ModuleType):
 
 
 _STUBS = [
-    "h5py", "igl", "trimesh", "polyscope", "polyscope.imgui", "matplotlib", "matplotlib.pyplot",
+    "h5py", "igl", "igl.copyleft", "igl.copyleft.tetgen", "trimesh", "polyscope", "polyscope.imgui", "matplotlib", "matplotlib.pyplot",
     "matplotlib.cm", "matplotlib.colors", "matplotlib.ticker",
     "mayavi", "mayavi.mlab", "mayavi.tools", "mayavi.tools.mlab_scene_model", "mayavi.core",
     "mayavi.core.ui", "mayavi.core.ui.mayavi_scene", "traits", "traits.api", "traitsui",
@@ -112,30 +112,39 @@ def load_reference():
     _loaded = True
 
 
-def load_pd_simulators():
-    """The reference's consumer module projective_dynamics/Simulators.py, loaded from source under a private
-    name.  Its `from utils import check_dir_exists` means projective_dynamics/utils.py, which would shadow the root `utils`
-    package registered above: a one-function stand-in is visible as `utils` only while the module executes."""
+def load_pd_module(stem):
+    """A module of the reference's consumer package projective_dynamics/ (SURVEY 8(f) n2 / n4), loaded from source under a
+    private name.  Those modules say `from utils import ...` and mean projective_dynamics/utils.py, which would shadow the
+    root `utils` package registered above: a small stand-in is visible as `utils` only while the module executes."""
     load_reference()
     import importlib.util
-    name = "asb_ref_pd_simulators"
+    name = "asb_ref_pd_" + stem.lower()
     if name in sys.modules:
         return sys.modules[name]
     saved = sys.modules.get("utils")
     fake = types.ModuleType("utils")
     fake.check_dir_exists = lambda p: os.makedirs(p, exist_ok=True)
+    fake.delete_matching_column = mock.MagicMock(name="utils.delete_matching_column")
     sys.modules["utils"] = fake
     try:
-        spec = importlib.util.spec_from_file_location(name, os.path.join(REFERENCE_ROOT, "projective_dynamics", "Simulators.py"))
+        spec = importlib.util.spec_from_file_location(name, os.path.join(REFERENCE_ROOT, "projective_dynamics", stem + ".py"))
         mod = importlib.util.module_from_spec(spec)
-        spec.loader.exec_module(mod)
+        sys.modules[name] = mod                      # dataclasses look their module up while the class body executes
+        try:
+            spec.loader.exec_module(mod)
+        except BaseException:
+            del sys.modules[name]
+            raise
     finally:
         if saved is not None:
             sys.modules["utils"] = saved
         else:
             del sys.modules["utils"]
-    sys.modules[name] = mod
     return mod
+
+
+def load_pd_simulators():
+    return load_pd_module("Simulators")
 
 
 class scratch_cwd:

@@ -115,6 +115,40 @@ def test_port_reduced_group_golden():
         assert rel(port.group_reduced_term(r["P"][Pt], pm, normal, PtVT), r[name + "_term"]) < 1e-9
 
 
+def test_pd_local_step_golden():
+    """oracle/pd_local.py (the local step that produces the constraint-projection snapshots) against get_pi /
+    S_i^T of the unmodified constraint classes (projective_dynamics/Constraint_projections.py) stored in pd_local.npz; and
+    the synthetic bar generator of the fixtures (animsnapbases_b200.synth) against the same statement."""
+    from oracle import pd_local
+    from animsnapbases_b200 import synth
+    g = golden("pd_local")
+    wi, (smin, smax) = float(g["wi"]), g["sigma"]
+    cases = {"tet_dg": (pd_local.TetDeformationGradient(g["bar_verts"], g["bar_tets"], wi), g["bar_q"]),
+             "tet_strain": (pd_local.TetStrain(g["bar_verts"], g["bar_tets"], wi, smin, smax), g["bar_q"]),
+             "tri_strain": (pd_local.TriStrain(g["grid_verts"], g["grid_tris"], wi, smin, smax), g["grid_q"]),
+             "edge_spring": (pd_local.EdgeSpring(g["grid_verts"], g["grid_edges"], wi), g["grid_q"])}
+    for name, (group, q) in cases.items():
+        p = group.project(q)
+        assert p.shape == g[name + "_p"].shape == (group.rows * len(p) // group.rows, 3)
+        assert rel(p, g[name + "_p"]) < 1e-12, name
+        assert rel(group.assembly() @ p, g[name + "_StP"]) < 1e-12, name
+    # the generator behind tests/golden/bar*.npz: same rotation rows, and its gradient operator is S (unit weights)
+    dg = pd_local.TetDeformationGradient(g["bar_verts"], g["bar_tets"], 1.0)
+    S = synth.tet_gradient_operator(g["bar_verts"], g["bar_tets"], weighted=False)
+    unit = dg.assembly() @ sparse_diag(1.0 / np.repeat(np.abs(dg.V0), 3))
+    assert abs(S.T - unit).max() < 1e-12 * abs(unit).max()
+    Ft = (S @ g["bar_q"]).reshape(-1, 3, 3)                                    # rows of F^T per tet
+    U, _, Vt = np.linalg.svd(np.swapaxes(Ft, 1, 2))
+    R = U @ Vt
+    R[np.linalg.det(R) < 0, :, 2] *= -1
+    assert rel(np.swapaxes(R, 1, 2).reshape(-1, 3), g["tet_dg_p"]) < 1e-12
+
+
+def sparse_diag(v):
+    from scipy import sparse
+    return sparse.diags(v)
+
+
 def test_port_against_live_reference():
     from oracle import ref_shim
     if not ref_shim.reference_available():
