@@ -280,6 +280,8 @@ def check_verts_geom_protocol(ops, comm, tmp):
     from animsnapbases_b200.snapbases.constraintsComponents import constraintsComponents
     from animsnapbases_b200.snapbases.nonlinear_snapshots import nonlinearSnapshots
     runtime.install(ops, comm)
+    cwd = os.getcwd()
+    os.chdir(str(tmp))                     # log_time("") writes function_timings.txt into the CWD
     try:
         g = golden("verts_geom")
         comps, idx = g["bend_comps"], g["bend_idx"]
@@ -301,5 +303,6 @@ def check_verts_geom_protocol(ops, comm, tmp):
         assert np.array_equal(cc.geom_alpha_ranges, g["bend3_ranges"]) and np.array_equal(cc.geom_interpol_verts, g["bend3_verts"])
         assert np.array_equal(cc.constrianed_verts, idx)
     finally:
+        os.chdir(cwd)
         runtime.install(None, None)
     return True
