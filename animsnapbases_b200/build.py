@@ -15,7 +15,7 @@ ROOT = os.path.dirname(PKG)
 CSRC = os.path.join(PKG, "csrc")
 LIBDIR = os.path.join(PKG, "lib")
 LIBPATH = os.path.join(LIBDIR, "libasb.so")
-SOURCES = ["stream_ops.cu", "small_dense.cu", "dmma_gemm.cu", "admm.cu", "geodesic.cu", "mf_solve.cu", "align.cu"]
+SOURCES = ["stream_ops.cu", "small_dense.cu", "dmma_gemm.cu", "admm.cu", "geodesic.cu", "mf_solve.cu", "align.cu", "pd_local.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
               "-Xcompiler", "-fvisibility=default"]
 

@@ -371,6 +371,14 @@ class CudaOps:
         nrhs, ldx = rhs.shape
         self._call("asb_delta_rhs", self._p(idx), n, nrhs, ldx, self._p(rhs))
 
+    # ------------------------------------------------------------------ snapshot producer (PD local step)
+    def pd_project(self, kind, q, elems, rest, sigma_min, sigma_max, out):
+        """out[f][d][rows * t + j] = get_pi of element t in frame f (asb_pd_project); q (F, 3, ldq), out (F, 3, ldo)."""
+        F, _, ldq = q.shape
+        self._call("asb_pd_project", int(kind), self._p(q), ldq, F, self._p(elems), self._p(rest), elems.shape[0],
+                   float(sigma_min), float(sigma_max), self._p(out), out.shape[2])
+        return out
+
     # ------------------------------------------------------------------ alignment
     def align(self, frames, rigid):
         """frames: (F, N, 3) float32 on the device -> aligned float32 (F, N, 3) and the (F, 12) transforms."""

@@ -274,6 +274,18 @@ int asb_align_solve(const double* M, const double* cent, int64_t F, int rigid, d
 /* out[f][n] = float32(T[f] * [v; 1])   (:198-208, stored float32 :246). */
 int asb_align_apply(const float* frames, int64_t F, int64_t N, const double* T, float* out, asb_stream_t stream);
 
+/* ---- snapshot producer: projective-dynamics local step ----------------------------------
+ * Per element and frame the projection `get_pi` of projective_dynamics/Constraint_projections.py, stacked like
+ * Simulators.get_group_ST_p (:354-356) into the planar snapshot frame out[f][d][rows * t + j]:
+ *   kind 0  tets_deformation_gradient (:669-687)  3 rows: R^T, R = U V^T of F = Ds DmInv, third column negated if det R < 0
+ *   kind 1  tets_strain               (:534-554)  3 rows: U clip(s) V^T, smallest value negated if det F < 0
+ *   kind 2  tris_strain               (:407-426)  2 rows: (P U clip(s) V^T)^T in the triangle's rest frame P
+ *   kind 3  edge_spring               (:291-312)  1 row:  half the edge vector at the mean of current and rest length
+ * q: frames x 3 x ldq planar positions; elems: e x (4 | 4 | 3 | 2) vertex ids; rest: e x (9 | 9 | 10 | 1) doubles
+ * (tets: DmInv row-major; triangles: P (3 x 2) then DmInv (2 x 2); edges: rest length).  ldo >= rows * e. */
+int asb_pd_project(int kind, const double* q, int64_t ldq, int64_t frames, const int32_t* elems, const double* rest, int64_t e,
+                   double sigma_min, double sigma_max, double* out, int64_t ldo, asb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

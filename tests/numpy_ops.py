@@ -411,6 +411,39 @@ class NumpyOps:
             xx[:, s0:s0 + n1] = acc
 
     # alignment ------------------------------------------------------------------------------------
+    def pd_project(self, kind, q, elems, rest, sigma_min, sigma_max, out):
+        """numpy statement of asb_pd_project through LAPACK's SVD (the kernel uses Jacobi eigen-pairs of F^T F instead)."""
+        el, rs = elems.numpy(), rest.numpy()
+        e = len(el)
+        for f in range(q.shape[0]):
+            x = q.numpy()[f].T                                            # (|V| padded, 3)
+            if kind in (0, 1):
+                Ds = np.stack([x[el[:, c]] - x[el[:, 3]] for c in range(3)], axis=2)
+                Fm = Ds @ rs.reshape(e, 3, 3)
+                U, s, Vt = np.linalg.svd(Fm)
+                if kind == 0:
+                    R = U @ Vt
+                    R[np.linalg.det(R) < 0, :, 2] *= -1
+                    rows = np.swapaxes(R, 1, 2)
+                else:
+                    s = np.clip(s, sigma_min, sigma_max)
+                    s[np.linalg.det(Fm) < 0, 2] *= -1
+                    rows = (U * s[:, None, :]) @ Vt
+                rows = rows.reshape(3 * e, 3)
+            elif kind == 2:
+                P, Di = rs[:, :6].reshape(e, 3, 2), rs[:, 6:].reshape(e, 2, 2)
+                Ds = np.stack([x[el[:, 1]] - x[el[:, 0]], x[el[:, 2]] - x[el[:, 0]]], axis=2)
+                U, s, Vt = np.linalg.svd(np.swapaxes(P, 1, 2) @ Ds @ Di)
+                Fh = (U * np.clip(s, sigma_min, sigma_max)[:, None, :]) @ Vt
+                rows = np.swapaxes(P @ Fh, 1, 2).reshape(2 * e, 3)
+            else:
+                sp = x[el[:, 1]] - x[el[:, 0]]
+                ln = np.linalg.norm(sp, axis=1)
+                rows = 0.5 * rs[:, 0:1] * sp / np.where(ln == 0, 1.0, ln)[:, None]
+                rows[ln == 0] = 0.0
+            out.numpy()[f, :, :rows.shape[0]] = rows.T
+        return out
+
     def align(self, frames, rigid):
         v = frames.numpy().astype(np.float64)
         F = v.shape[0]

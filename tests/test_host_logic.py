@@ -109,6 +109,58 @@ def test_verts_geometric_deim_host_logic():
     assert pipeline_checks.check_verts_geom(NumpyOps(), engine.Comm(enabled=False))
 
 
+def test_pd_local_snapshot_producer_host_logic(tmp_path):
+    """pd_local.ConstraintGroup over the numpy statement of asb_pd_project == the reference's constraint classes."""
+    assert pipeline_checks.check_pd_local(NumpyOps(), engine.Comm(enabled=False), tmp_path)
+
+
+def test_pd_math_on_host(tmp_path):
+    """The arithmetic of the asb_pd_project kernel (csrc/pd_elements.cuh + pd_math.cuh: Jacobi eigen-pairs of F^T F instead of
+    LAPACK's SVD, host + device inline functions) compiled for the CPU and compared with get_pi of the reference's
+    constraint classes (tests/golden/pd_local.npz, some tets inverted) -- a check of the kernel's math that needs no GPU."""
+    import ctypes
+    import shutil
+    from conftest import golden, rel
+    from oracle import pd_local as oracle_pd
+    if shutil.which("g++") is None:
+        pytest.skip("no host compiler")
+    so = str(tmp_path / "libpd_host.so")
+    r = subprocess.run(["g++", "-O2", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-shared", "-fPIC", "-I",
+                        os.path.join(ROOT, "animsnapbases_b200", "csrc"), os.path.join(ROOT, "tools", "host", "pd_host.cpp"), "-o", so],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    lib = ctypes.CDLL(so)
+    g = golden("pd_local")
+    wi, (smin, smax) = float(g["wi"]), g["sigma"]
+
+    def run(kind, nv, elems, rest, q, rows):
+        ld = (nv + 31) // 32 * 32
+        qp = np.zeros((1, 3, ld))
+        qp[0, :, :nv] = q.T
+        e = len(elems)
+        ldo = (rows * e + 31) // 32 * 32
+        out = np.zeros((1, 3, ldo))
+        el = np.ascontiguousarray(elems, dtype=np.int32)
+        rs = np.ascontiguousarray(rest, dtype=np.float64)
+        vp = ctypes.c_void_p
+        lib.pd_host(ctypes.c_int(kind), qp.ctypes.data_as(vp), ctypes.c_int64(ld), ctypes.c_int64(1), el.ctypes.data_as(vp),
+                    rs.ctypes.data_as(vp), ctypes.c_int64(e), ctypes.c_double(smin), ctypes.c_double(smax), out.ctypes.data_as(vp),
+                    ctypes.c_int64(ldo))
+        return out[0, :, :rows * e].T
+
+    dg = oracle_pd.TetDeformationGradient(g["bar_verts"], g["bar_tets"], wi)
+    ts = oracle_pd.TriStrain(g["grid_verts"], g["grid_tris"], wi, smin, smax)
+    es = oracle_pd.EdgeSpring(g["grid_verts"], g["grid_edges"], wi)
+    nb, ng = len(g["bar_verts"]), len(g["grid_verts"])
+    assert np.any(np.linalg.det(np.stack([g["bar_q"][g["bar_tets"][:, c]] - g["bar_q"][g["bar_tets"][:, 3]] for c in range(3)], axis=2)
+                                @ dg.DmInv) < 0), "the fixture exercises the inverted-element branches"
+    assert rel(run(0, nb, g["bar_tets"], dg.DmInv.reshape(-1, 9), g["bar_q"], 3), g["tet_dg_p"]) < 1e-11
+    assert rel(run(1, nb, g["bar_tets"], dg.DmInv.reshape(-1, 9), g["bar_q"], 3), g["tet_strain_p"]) < 1e-11
+    assert rel(run(2, ng, g["grid_tris"], np.concatenate([ts.P.reshape(-1, 6), ts.DmInv.reshape(-1, 4)], axis=1), g["grid_q"], 2),
+               g["tri_strain_p"]) < 1e-11
+    assert rel(run(3, ng, g["grid_edges"], es.d.reshape(-1, 1), g["grid_q"], 1), g["edge_spring_p"]) < 1e-13
+
+
 def test_zero_residual_host_logic():
     assert pipeline_checks.check_zero_residual(NumpyOps(), engine.Comm(enabled=False))
 

@@ -43,3 +43,9 @@ def test_pos_protocol_with_figure_tables(cuda_ops, tmp_path):
 def test_zero_residual(cuda_ops):
     """Vanishing DEIM residual: print + no result, like the reference, in all three selections."""
     assert pipeline_checks.check_zero_residual(cuda_ops, engine.Comm(enabled=False))
+
+
+@pytest.mark.xfail(strict=False, reason="asb_pd_project was written after the last GPU session of r01: its arithmetic is checked on "
+                                        "the host (test_pd_math_on_host), the kernel itself has not run on a B200 yet")
+def test_pd_local_snapshot_producer(cuda_ops, tmp_path):
+    assert pipeline_checks.check_pd_local(cuda_ops, engine.Comm(enabled=False), tmp_path)

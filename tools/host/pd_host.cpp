@@ -1,0 +1,12 @@
+// CPU build of the projective-dynamics local-step arithmetic (animsnapbases_b200/csrc/pd_elements.cuh, the same inline
+// functions the CUDA kernels call) so that it can be checked against the oracle on a machine without a GPU.
+// Test infrastructure: g++ -O2 -shared -fPIC -I animsnapbases_b200/csrc tools/host/pd_host.cpp -o <tmp>/libpd_host.so
+#include "pd_elements.cuh"
+
+extern "C" void pd_host(int kind, const double* q, int64_t ldq, int64_t frames, const int32_t* elems, const double* rest,
+                        int64_t e, double smin, double smax, double* out, int64_t ldo) {
+    const int nodes = asb::pd::kind_nodes(kind), nrest = asb::pd::kind_rest(kind);
+    for (int64_t f = 0; f < frames; ++f)
+        for (int64_t t = 0; t < e; ++t)
+            asb::pd::pd_element(kind, q + f * 3 * ldq, ldq, elems + t * nodes, rest + t * nrest, smin, smax, out + f * 3 * ldo, ldo, t);
+}
