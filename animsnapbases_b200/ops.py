@@ -293,8 +293,15 @@ class CudaOps:
         self._call("asb_deim_gather_rhs", self._p(C), C.shape[2], N, row0, self._p(Pt), k, rhs, self._p(Vp), Vp.shape[1])
 
     def deim_residual_block(self, C, N, k, target, accumulate, a, e, maxabs):
+        """The per-CTA max|r| partials live in `ws` and, with `accumulate`, are carried from one target of a block to the
+        next: they get a buffer of their own -- the shared scratch is rewritten by asb_deim_solve between the targets (on a
+        B200 that turned max|r| of a block into garbage, so a vanishing block residual went unnoticed)."""
+        need = (int(C.shape[2]) + 255) // 256 + 8
+        buf = getattr(self, "_deim_pmax", None)
+        if buf is None or buf.numel() < need:
+            buf = self._deim_pmax = torch.zeros(need, dtype=F64, device=self.device)
         self._call("asb_deim_residual_block", self._p(C), C.shape[2], N, k, target, int(accumulate), self._p(a), a.stride(0),
-                   self._p(e), self._p(maxabs), self._p(self.ws_for(1, C.shape[2])))
+                   self._p(e), self._p(maxabs), self._p(buf))
 
     def deim_solve(self, Vp, k, a, info):
         ws = self.workspace(3 * k * (k + 1) * 8 + 1024)
