@@ -188,7 +188,9 @@ int asb_deim_residual(const double* C, int64_t ld, int64_t N, int64_t k, const d
 
 /* Block variants (deim_blocksForm, snapbases/constraintsComponents.py:733-795): the right-hand side / residual target is
  * component `rhs` / `target` instead of component k (the basis is still components [0, k)), and the per-row energy
- * of the p targets of a block is accumulated into e (accumulate != 0: e += r^2, maxabs = max over the block). */
+ * of the p targets of a block is accumulated into e (accumulate != 0: e += r^2, maxabs = max over the block).
+ * The running maximum is kept as per-CTA partials in ws ((N + 255) / 256 doubles): for the calls of one block pass the SAME
+ * ws and do not let anything else write to it in between. */
 int asb_deim_gather_rhs(const double* C, int64_t ld, int64_t N, int64_t row0, const int64_t* Pt, int64_t k, int64_t rhs,
                         double* Vp, int64_t ldv, asb_stream_t stream);
 int asb_deim_residual_block(const double* C, int64_t ld, int64_t N, int64_t k, int64_t target, int accumulate,
