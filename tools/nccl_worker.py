@@ -25,5 +25,23 @@ pipeline_checks.check_positions(ops, comm, "pos_sphere")
 pipeline_checks.check_bar(ops, comm)
 pipeline_checks.check_bar_geom(ops, comm)
 pipeline_checks.check_bar_reconstruction(ops, comm)
+print(f"RANK{comm.rank}/{comm.world} r01-validated checks OK", flush=True)
+# added after the last multi-GPU session of r01 (green on two and five gloo ranks, not yet run over NCCL)
+pipeline_checks.check_bar_reduced(ops, comm)
+pipeline_checks.check_verts_geom(ops, comm)
+pipeline_checks.check_zero_residual(ops, comm)
+if "--mirror-classes" in sys.argv:           # main.py's two protocols through the drop-in classes, rows sharded over the GPUs
+    import pathlib
+    import tempfile
+    import api_checks
+    base = [tempfile.mkdtemp(prefix="asb_nccl_") if comm.rank == 0 else None]
+    dist.broadcast_object_list(base, src=0)
+    for name, check in (("pos", api_checks.check_pos_protocol), ("con", api_checks.check_constraints_protocol)):
+        tmp = pathlib.Path(base[0]) / name
+        if comm.rank == 0:
+            tmp.mkdir(parents=True, exist_ok=True)
+        dist.barrier()
+        assert check(ops, comm, tmp)
+        dist.barrier()
 print(f"RANK{comm.rank}/{comm.world} OK ({ops.launch_count()} launches)", flush=True)
 dist.destroy_process_group()
