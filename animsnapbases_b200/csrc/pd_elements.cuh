@@ -67,5 +67,28 @@ ASB_HD void pd_element(int kind, const double* __restrict__ q, int64_t ldq, cons
     }
 }
 
+// Vertex bending (Constraint_projections.py:197-216): constrained vertex i = verts[i] with the star nbr[ptr[i] .. ptr[i+1]) and
+// cotangent weights w (already divided by the Voronoi area, :169); rest = [rest mean curvature, rest normal (3), rest
+// normal . rest mean-curvature vector] (:184-187).  One row per constrained vertex.
+ASB_HD void pd_vertex_bending(const double* __restrict__ q, int64_t ldq, int32_t v, const int32_t* __restrict__ nbr,
+                              const double* __restrict__ w, int deg, const double* __restrict__ rest, int prevent_flips,
+                              double* __restrict__ out, int64_t ldo, int64_t i) {
+    double star[3] = {0.0, 0.0, 0.0};
+    const double qv[3] = {q[v], q[ldq + v], q[2 * ldq + v]};
+    for (int j = 0; j < deg; ++j) {
+        const int32_t n = nbr[j];
+        for (int d = 0; d < 3; ++d) star[d] += (qv[d] - q[d * ldq + n]) * w[j];                  // :200-202
+    }
+    const double norm = sqrt(star[0] * star[0] + star[1] * star[1] + star[2] * star[2]);
+    double c[3];
+    if (norm < 1e-10) { for (int d = 0; d < 3; ++d) c[d] = rest[1 + d] * rest[0]; }               // :205-206
+    else { const double s = rest[0] / norm; for (int d = 0; d < 3; ++d) c[d] = star[d] * s; }     // :207-208
+    if (prevent_flips) {                                                                          // :210-213
+        const double dot = rest[1] * c[0] + rest[2] * c[1] + rest[3] * c[2];
+        if (norm > 1e-5 && dot * rest[4] < 0.0) { c[0] = -c[0]; c[1] = -c[1]; c[2] = -c[2]; }
+    }
+    for (int d = 0; d < 3; ++d) out[d * ldo + i] = c[d];
+}
+
 }  // namespace pd
 }  // namespace asb

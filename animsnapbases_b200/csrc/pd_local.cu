@@ -22,6 +22,18 @@ __global__ void __launch_bounds__(128) pd_project_kernel(int kind, const double*
                    out + f * 3 * ldo, ldo, t);
 }
 
+__global__ void __launch_bounds__(128) pd_vertex_bending_kernel(const double* __restrict__ q, int64_t ldq, const int32_t* __restrict__ verts,
+                                                               const int32_t* __restrict__ ptr, const int32_t* __restrict__ nbr,
+                                                               const double* __restrict__ w, const double* __restrict__ rest, int64_t n,
+                                                               int prevent_flips, double* __restrict__ out, int64_t ldo) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t f = blockIdx.y;
+    const int32_t p0 = ptr[i];
+    pd::pd_vertex_bending(q + f * 3 * ldq, ldq, verts[i], nbr + p0, w + p0, ptr[i + 1] - p0, rest + 5 * i, prevent_flips,
+                          out + f * 3 * ldo, ldo, i);
+}
+
 }  // namespace asb
 
 extern "C" {
@@ -34,6 +46,17 @@ int asb_pd_project(int kind, const double* q, int64_t ldq, int64_t frames, const
     ASB_REQUIRE(ldo >= e * pd::kind_rows(kind) && ldq > 0, "pd_project: output plane too short");
     pd_project_kernel<<<dim3((unsigned)cdiv(e, 128), (unsigned)frames), 128, 0, S(stream)>>>(kind, q, ldq, elems, rest, e, sigma_min,
                                                                                            sigma_max, out, ldo);
+    ASB_LAUNCH_CHECK();
+    return ASB_OK;
+}
+
+int asb_pd_vertex_bending(const double* q, int64_t ldq, int64_t frames, const int32_t* verts, const int32_t* star_ptr,
+                          const int32_t* star_nbr, const double* star_w, const double* rest, int64_t n, int prevent_flips,
+                          double* out, int64_t ldo, asb_stream_t stream) {
+    ASB_REQUIRE(q && verts && star_ptr && star_nbr && star_w && rest && out && n > 0 && frames > 0 && frames < 65536 && ldo >= n && ldq > 0,
+                "pd_vertex_bending: bad arguments");
+    pd_vertex_bending_kernel<<<dim3((unsigned)cdiv(n, 128), (unsigned)frames), 128, 0, S(stream)>>>(q, ldq, verts, star_ptr, star_nbr,
+                                                                                                  star_w, rest, n, prevent_flips, out, ldo);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
 }

@@ -386,6 +386,12 @@ class CudaOps:
                    float(sigma_min), float(sigma_max), self._p(out), out.shape[2])
         return out
 
+    def pd_vertex_bending(self, q, verts, ptr, nbr, w, rest, prevent_flips, out):
+        F, _, ldq = q.shape
+        self._call("asb_pd_vertex_bending", self._p(q), ldq, F, self._p(verts), self._p(ptr), self._p(nbr), self._p(w), self._p(rest),
+                   verts.shape[0], int(bool(prevent_flips)), self._p(out), out.shape[2])
+        return out
+
     # ------------------------------------------------------------------ alignment
     def align(self, frames, rigid):
         """frames: (F, N, 3) float32 on the device -> aligned float32 (F, N, 3) and the (F, 12) transforms."""

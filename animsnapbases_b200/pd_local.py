@@ -21,6 +21,72 @@ from .ops import pad_ld
 KINDS = {"tets_deformation_gradient": (0, 4, 3), "tets_strain": (1, 4, 3), "tris_strain": (2, 3, 2), "edge_spring": (3, 2, 1)}
 
 
+def bending_stars(rest_positions, faces, flat_bending=False):
+    """Rest data of the verts_bending group (Constraint_projections.py:132-187, :1086-1104, :1129-1161, :1195-1223), vectorised
+    over the half-edges instead of the reference's per-triangle Python loops: the constrained vertices (every star edge has two
+    triangles), their stars in CSR form with cotangent weights / Voronoi area, and per vertex [rest mean curvature, rest
+    normal, rest normal . rest mean-curvature vector].  Returns (verts, ptr, nbr, w, rest, voronoi_area)."""
+    x, f = np.asarray(rest_positions, dtype=np.float64), np.asarray(faces, dtype=np.int64)
+    n, T = len(x), len(f)
+    nrm = np.cross(x[f[:, 1]] - x[f[:, 0]], x[f[:, 2]] - x[f[:, 0]])
+    nlen = np.linalg.norm(nrm, axis=1)
+    area = np.bincount(f.ravel(), np.repeat(0.5 * nlen / 3.0, 3), minlength=n)
+    area[area < 1e-7] = 1e-7
+    v, nb, o = f[:, [0, 0, 1, 1, 2, 2]].ravel(), f[:, [1, 2, 0, 2, 0, 1]].ravel(), f[:, [2, 1, 2, 0, 1, 0]].ravel()
+    u, w = x[v] - x[o], x[nb] - x[o]
+    cosang = np.clip((u * w).sum(axis=1) / (np.linalg.norm(u, axis=1) * np.linalg.norm(w, axis=1)), -1, 1)
+    half_cot = 0.5 / np.tan(np.arccos(cosang))
+    key, inv, cnt = np.unique(v * n + nb, return_inverse=True, return_counts=True)      # one entry per directed star edge
+    ev, enb = key // n, key % n
+    ecot = np.bincount(inv, half_cot, minlength=len(key))
+    open_edge = np.bincount(ev, cnt != 2, minlength=n) > 0
+    has_star = np.bincount(ev, minlength=n) > 0
+    verts = np.nonzero(has_star & ~open_edge)[0]
+    keep = np.isin(ev, verts)
+    ev, enb, ew = ev[keep], enb[keep], ecot[keep] / area[ev[keep]]
+    ptr = np.concatenate([[0], np.cumsum(np.bincount(ev, minlength=n)[verts])])
+    mc = np.zeros((n, 3))
+    np.add.at(mc, ev, (x[ev] - x[enb]) * ew[:, None])
+    valid = nlen > 1e-10
+    unit = np.where(valid[:, None], nrm / np.where(valid, nlen, 1.0)[:, None], 0.0)
+    nsum, ncnt = np.zeros((n, 3)), np.zeros(n)
+    for c in range(3):
+        np.add.at(nsum, f[:, c], unit)
+        np.add.at(ncnt, f[:, c], valid.astype(np.float64))
+    normal = np.where(ncnt[:, None] > 0, nsum / np.where(ncnt > 0, ncnt, 1.0)[:, None], np.array([0.0, 0.0, 1.0]))
+    rest = np.empty((len(verts), 5))
+    rest[:, 0] = 0.0 if flat_bending else np.linalg.norm(mc[verts], axis=1)
+    rest[:, 1:4] = normal[verts]
+    rest[:, 4] = (normal[verts] * mc[verts]).sum(axis=1)
+    return verts, ptr, enb, ew, rest, area
+
+
+class VertexBendingGroup:
+    """verts_bending: one row per constrained vertex (`verts`, the reference's verts_bending_indicies)."""
+    name, rows = "verts_bending", 1
+
+    def __init__(self, rest_positions, faces, prevent_bending_flips=True, flat_bending=False):
+        self.verts, ptr, nbr, w, rest, self.voronoi_area = bending_stars(rest_positions, faces, flat_bending)
+        self.n_verts, self.num_elements, self.prevent = len(rest_positions), len(self.verts), bool(prevent_bending_flips)
+        ops, _ = runtime.get()
+        self._dev = [ops.to_device(np.ascontiguousarray(a, dtype=t)) for a, t in
+                     ((self.verts, np.int32), (ptr, np.int32), (nbr, np.int32), (w, np.float64), (rest, np.float64))]
+
+    def project(self, frames):
+        ops, _ = runtime.get()
+        if isinstance(frames, np.ndarray):
+            assert frames.ndim == 3 and frames.shape[1:] == (self.n_verts, 3)
+            q = ops.ingest(ops.to_device(np.ascontiguousarray(frames, dtype=np.float64)), None, pad_ld(self.n_verts))
+        else:
+            q = frames
+        out = ops.zeros((q.shape[0], 3, pad_ld(self.num_elements)))
+        return ops.pd_vertex_bending(q, *self._dev, self.prevent, out)
+
+    def project_host(self, frames):
+        ops, _ = runtime.get()
+        return ops.export_aos(self.project(frames), None, self.num_elements).cpu().numpy()
+
+
 class ConstraintGroup:
     def __init__(self, name, rest_positions, elems, sigma_min=0.95, sigma_max=1.05):
         if name not in KINDS:

@@ -287,6 +287,12 @@ int asb_align_apply(const float* frames, int64_t F, int64_t N, const double* T, 
  * (tets: DmInv row-major; triangles: P (3 x 2) then DmInv (2 x 2); edges: rest length).  ldo >= rows * e. */
 int asb_pd_project(int kind, const double* q, int64_t ldq, int64_t frames, const int32_t* elems, const double* rest, int64_t e,
                    double sigma_min, double sigma_max, double* out, int64_t ldo, asb_stream_t stream);
+/* verts_bending (Constraint_projections.py:197-216): one row per constrained vertex i = verts[i]; its star in CSR form
+ * (star_ptr n + 1, star_nbr, star_w = cotangent weights / Voronoi area, :156-169); rest: n x 5 doubles = [rest mean
+ * curvature, rest normal (3), rest normal . rest mean-curvature vector] (:184-187); prevent_flips as the constructor flag. */
+int asb_pd_vertex_bending(const double* q, int64_t ldq, int64_t frames, const int32_t* verts, const int32_t* star_ptr,
+                          const int32_t* star_nbr, const double* star_w, const double* rest, int64_t n, int prevent_flips,
+                          double* out, int64_t ldo, asb_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -473,6 +473,11 @@ def pd_local_inputs():
     return dict(bar_verts=bv, bar_tets=bt, bar_q=qb, grid_verts=gv, grid_tris=gt, grid_edges=ge, grid_q=qg)
 
 
+def m_sphere():
+    m = np.load(os.path.join(GOLD, "meshes.npz"))
+    return m["sphere_verts"].astype(np.float64), m["sphere_tris"].astype(np.int64)
+
+
 def pd_local_case():
     """get_pi and S_i^T of the reference's constraint classes (projective_dynamics/Constraint_projections.py, unmodified, loaded
     by ref_shim.load_pd_module) per element -> tests/golden/pd_local.npz, and oracle/pd_local.py checked against them."""
@@ -492,6 +497,20 @@ def pd_local_case():
         "edge_spring": (pd_local.EdgeSpring(d["grid_verts"], d["grid_edges"], wi),
                         [cp.EdgeSpringConstraint(list(t), wi, d["grid_verts"]) for t in d["grid_edges"]], d["grid_q"]),
     }
+    # vertex bending on a curved, closed surface: every vertex is constrained; the builder of the reference's model class
+    # (vertex_star / vertex_masses / add_vertex_bending_constraint, :1086-1223) runs unbound on a stand-in `self`
+    sv, sf = m_sphere()
+    rng = np.random.default_rng(23)
+    sq = sv * (1.0 + 0.3 * np.sin(3.0 * sv[:, :1])) + 0.03 * rng.standard_normal(sv.shape)
+    sq[::7] = sv[::7] * 0.6                                                  # dents: some stars flip to the other side
+    Model = [getattr(cp, n) for n in dir(cp) if hasattr(getattr(cp, n), "add_vertex_bending_constraint")][0]
+    model = types.SimpleNamespace(positions=sv, faces=sf, constraints=[], verts_bending_indicies=[], verts_bending_constraints=[],
+                                  triangle_area=lambda tri, pos: Model.triangle_area(None, tri, pos))
+    model.vertex_masses = lambda tris, pos: Model.vertex_masses(model, tris, pos)
+    model.vertex_star = lambda: Model.vertex_star(model)
+    Model.add_vertex_bending_constraint(model, wi)
+    d.update(sphere_verts=sv, sphere_tris=sf, sphere_q=sq)
+    groups["vert_bending"] = (pd_local.VertBending(sv, sf, wi), model.verts_bending_constraints, sq)
     out = dict(d, wi=wi, sigma=np.array([smin, smax]))
     for name, (mine, theirs, q) in groups.items():
         p_ref = np.concatenate([c.get_pi(q.reshape(-1)) for c in theirs], axis=0)
@@ -503,6 +522,12 @@ def pd_local_case():
         for c in theirs:
             c.project_wi_SiT_pi(q.reshape(-1), rhs_ref)                   # the assembled local-step term S^T p
         assert rel(St_mine @ p_mine, rhs_ref) < 1e-12, name
+        if name == "vert_bending":
+            assert np.array_equal(mine.verts, model.verts_bending_indicies) and len(mine.verts) == len(sv)
+            free = pd_local.VertBending(sv, sf, wi, prevent_bending_flips=False).project(q)
+            flips = int((np.abs(free - p_mine).max(axis=1) > 0).sum())
+            assert 0 < flips < len(sv), "the fixture must exercise both sides of the flip test (:211-214)"
+            print(f"pd_local vert_bending: {flips} of {len(sv)} corrections flipped back")
         out[name + "_p"], out[name + "_StP"] = p_ref, rhs_ref
         print(f"pd_local {name}: {len(theirs)} elements, port vs reference p {rel(p_mine, p_ref):.1e}, S^T p {rel(St_mine @ p_mine, rhs_ref):.1e}")
     np.savez_compressed(os.path.join(GOLD, "pd_local.npz"), **out)

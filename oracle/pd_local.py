@@ -130,3 +130,100 @@ class EdgeSpring:
         out = 0.5 * (pi2 - pi1)                                                      # :311
         out[length == 0] = 0.0
         return out
+
+
+# ------------------------------------------------------------------------------------------ vertices: bending
+class VertBending:
+    """VertBendingConstraint (:116-216) for every vertex whose star edges all have two triangles (add_vertex_bending_constraint,
+    :1195-1223): one row per constrained vertex, the cotangent-weighted star sum rescaled to the rest mean-curvature length
+    (optionally flipped back to the rest side of the surface)."""
+    rows = 1
+
+    def __init__(self, positions, faces, wi=1.0, prevent_bending_flips=True, flat_bending=False):
+        x, faces = np.asarray(positions, dtype=np.float64), np.asarray(faces)
+        n = len(x)
+        area = np.zeros(n)                                                            # vertex_masses :1086-1104
+        for tri in faces:
+            a = 0.5 * np.linalg.norm(np.cross(x[tri[1]] - x[tri[0]], x[tri[2]] - x[tri[0]])) / 3.0
+            for vi in tri:
+                area[vi] += a
+        area[area < 1e-7] = 1e-7
+        stars = [[] for _ in range(n)]                                                # vertex_star :1129-1161: [v2, vOtherT1, t1, vOtherT2, t2]
+        for t, tri in enumerate(faces):
+            for v in range(3):
+                for ov in range(3):
+                    if v == ov:
+                        continue
+                    nb, third = tri[ov], tri[3 - (v + ov)]
+                    for edge in stars[tri[v]]:
+                        if edge[0] == nb:
+                            edge[4], edge[3] = t, third
+                            break
+                    else:
+                        stars[tri[v]].append([nb, third, t, -1, -1])
+
+        def angle(a, b, c):                                                           # :138-143, angle at b
+            u, w = a - b, c - b
+            return np.arccos(np.clip(np.dot(u, w) / (np.linalg.norm(u) * np.linalg.norm(w)), -1, 1))
+
+        self.verts, self.nbrs, self.weights, self.rest_mc, self.normal, self.dot_n, self.scale = [], [], [], [], [], [], []
+        for v in range(n):
+            star = stars[v]
+            if not star or any(e[4] < 0 for e in star):                               # :1207-1212
+                continue
+            w, tris_seen, tris = [], set(), []
+            for v2, o1, t1, o2, t2 in star:                                           # :156-175
+                cot = 0.5 / np.tan(angle(x[v], x[o1], x[v2]))
+                if t2 >= 0:
+                    cot += 0.5 / np.tan(angle(x[v], x[o2], x[v2]))
+                w.append(cot / area[v])
+                for t in (t1, t2):
+                    if t >= 0 and t not in tris_seen:
+                        tris.append(faces[t])
+                        tris_seen.add(t)
+            w = np.array(w)
+            mc = np.zeros(3)
+            for e, wi_e in zip(star, w):                                              # :180-182
+                mc += (x[v] - x[e[0]]) * wi_e
+            normals = []
+            for tri in tris:                                                          # :145-154
+                nrm = np.cross(x[tri[1]] - x[tri[0]], x[tri[2]] - x[tri[0]])
+                ln = np.linalg.norm(nrm)
+                if ln > 1e-10:
+                    normals.append(nrm / ln)
+            nm = np.mean(normals, axis=0) if normals else np.array([0.0, 0.0, 1.0])
+            self.verts.append(v)
+            self.nbrs.append(np.array([e[0] for e in star]))
+            self.weights.append(w)
+            self.rest_mc.append(0.0 if flat_bending else np.linalg.norm(mc))          # :184
+            self.normal.append(nm)
+            self.dot_n.append(nm @ mc)                                                # :187
+            self.scale.append(wi * area[v])                                           # super().__init__([v], wi * voronoi_area) :119
+        self.verts = np.array(self.verts, dtype=np.int64)
+        self.prevent, self.n_verts = prevent_bending_flips, n
+
+    def assembly(self):
+        """|V| x (constrained vertices): column i = wi_i (sum_j w_ij at v_i, -w_ij at its neighbours) (:190-197, :1220-1222)."""
+        r, c, val = [], [], []
+        for i, v in enumerate(self.verts):
+            r += [v] + list(self.nbrs[i])
+            c += [i] * (1 + len(self.nbrs[i]))
+            val += [self.scale[i] * self.weights[i].sum()] + list(-self.scale[i] * self.weights[i])
+        return sparse.csr_matrix((val, (r, c)), shape=(self.n_verts, len(self.verts)))
+
+    def project(self, q):
+        out = np.zeros((len(self.verts), 3))
+        for i, v in enumerate(self.verts):                                            # :197-216
+            star_sum = np.zeros(3)
+            for nb, w in zip(self.nbrs[i], self.weights[i]):
+                star_sum += (q[v] - q[nb]) * w
+            norm = np.linalg.norm(star_sum)
+            if norm < 1e-10:
+                corr = self.normal[i] * self.rest_mc[i]
+            else:
+                corr = star_sum * (self.rest_mc[i] / norm)
+            if self.prevent:
+                if norm > 1e-5 and (self.normal[i] @ corr) * self.dot_n[i] < 0:
+                    corr = -corr
+            out[i] = corr
+        return out

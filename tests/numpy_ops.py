@@ -444,6 +444,22 @@ class NumpyOps:
             out.numpy()[f, :, :rows.shape[0]] = rows.T
         return out
 
+    def pd_vertex_bending(self, q, verts, ptr, nbr, w, rest, prevent_flips, out):
+        vs, pt, nb, ww, rs = (t.numpy() for t in (verts, ptr, nbr, w, rest))
+        seg = np.repeat(np.arange(len(vs)), np.diff(pt))
+        for f in range(q.shape[0]):
+            x = q.numpy()[f].T
+            star = np.zeros((len(vs), 3))
+            np.add.at(star, seg, (x[vs[seg]] - x[nb]) * ww[:, None])
+            norm = np.linalg.norm(star, axis=1)
+            small = norm < 1e-10
+            c = np.where(small[:, None], rs[:, 1:4] * rs[:, 0:1], star * (rs[:, 0] / np.where(small, 1.0, norm))[:, None])
+            if prevent_flips:
+                flip = (norm > 1e-5) & ((rs[:, 1:4] * c).sum(axis=1) * rs[:, 4] < 0)
+                c[flip] = -c[flip]
+            out.numpy()[f, :, :len(vs)] = c.T
+        return out
+
     def align(self, frames, rigid):
         v = frames.numpy().astype(np.float64)
         F = v.shape[0]

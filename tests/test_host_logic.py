@@ -159,6 +159,20 @@ def test_pd_math_on_host(tmp_path):
     assert rel(run(2, ng, g["grid_tris"], np.concatenate([ts.P.reshape(-1, 6), ts.DmInv.reshape(-1, 4)], axis=1), g["grid_q"], 2),
                g["tri_strain_p"]) < 1e-11
     assert rel(run(3, ng, g["grid_edges"], es.d.reshape(-1, 1), g["grid_q"], 1), g["edge_spring_p"]) < 1e-13
+    # vertex bending: rest data from the product's vectorised set-up, projection by the kernel's inline code
+    from animsnapbases_b200.pd_local import bending_stars
+    sv, sq = g["sphere_verts"], g["sphere_q"]
+    verts, ptr, nbr, w, rest, _ = bending_stars(sv, g["sphere_tris"])
+    ld = (len(sv) + 31) // 32 * 32
+    qp = np.zeros((1, 3, ld))
+    qp[0, :, :len(sv)] = sq.T
+    out = np.zeros((1, 3, ld))
+    arrs = [np.ascontiguousarray(a, dtype=t) for a, t in ((verts, np.int32), (ptr, np.int32), (nbr, np.int32), (w, np.float64),
+                                                          (rest, np.float64))]
+    vp = ctypes.c_void_p
+    lib.pd_host_vertex_bending(qp.ctypes.data_as(vp), ctypes.c_int64(ld), ctypes.c_int64(1), *[a.ctypes.data_as(vp) for a in arrs],
+                               ctypes.c_int64(len(verts)), ctypes.c_int(1), out.ctypes.data_as(vp), ctypes.c_int64(ld))
+    assert rel(out[0, :, :len(verts)].T, g["vert_bending_p"]) < 1e-12
 
 
 def test_zero_residual_host_logic():

@@ -127,6 +127,7 @@ def test_pd_local_step_golden():
              "tet_strain": (pd_local.TetStrain(g["bar_verts"], g["bar_tets"], wi, smin, smax), g["bar_q"]),
              "tri_strain": (pd_local.TriStrain(g["grid_verts"], g["grid_tris"], wi, smin, smax), g["grid_q"]),
              "edge_spring": (pd_local.EdgeSpring(g["grid_verts"], g["grid_edges"], wi), g["grid_q"])}
+    cases["vert_bending"] = (pd_local.VertBending(g["sphere_verts"], g["sphere_tris"], wi), g["sphere_q"])
     for name, (group, q) in cases.items():
         p = group.project(q)
         assert p.shape == g[name + "_p"].shape == (group.rows * len(p) // group.rows, 3)
