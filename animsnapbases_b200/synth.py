@@ -179,20 +179,26 @@ def bar_deformation(verts0: np.ndarray, t: float, seed_vec: np.ndarray) -> np.nd
     return out
 
 
+def bar_motion_frames(verts0: np.ndarray, frames: int, seed: int = 0) -> np.ndarray:
+    """(F, |V|, 3) positions of the synthetic bar motion: bend / twist / sag along a smooth, non-periodic parameter path, so
+    that the snapshot matrix built from it has a decaying spectrum."""
+    rng = np.random.default_rng(seed)
+    path = np.cumsum(rng.standard_normal((frames, 3)), axis=0) / np.sqrt(frames)
+    path += np.linspace(0, 1, frames)[:, None] * np.array([1.2, 2.0, 0.3])
+    return np.stack([bar_deformation(verts0, 1.0, path[f]) for f in range(frames)])
+
+
 def tet_rotation_snapshots(verts0: np.ndarray, tets: np.ndarray, frames: int, seed: int = 0) -> np.ndarray:
     """(F, 3e, 3) float64: for each frame and tet, `R^T` of the polar decomposition of the deformation
     gradient `Ds Dm^{-1}` (restates Constraint_projections.py:669-687; det-fix flips the last column)."""
-    rng = np.random.default_rng(seed)
     e = len(tets)
     v = verts0
     Dm = np.stack([v[tets[:, 0]] - v[tets[:, 3]], v[tets[:, 1]] - v[tets[:, 3]], v[tets[:, 2]] - v[tets[:, 3]]], axis=2)
     DmInv = np.linalg.inv(Dm)
-    # smooth, non-periodic parameter path so that the snapshot matrix has a decaying spectrum
-    path = np.cumsum(rng.standard_normal((frames, 3)), axis=0) / np.sqrt(frames)
-    path += np.linspace(0, 1, frames)[:, None] * np.array([1.2, 2.0, 0.3])
+    positions = bar_motion_frames(verts0, frames, seed)
     out = np.empty((frames, 3 * e, 3))
     for f in range(frames):
-        q = bar_deformation(verts0, 1.0, path[f])
+        q = positions[f]
         Ds = np.stack([q[tets[:, 0]] - q[tets[:, 3]], q[tets[:, 1]] - q[tets[:, 3]], q[tets[:, 2]] - q[tets[:, 3]]], axis=2)
         Fg = Ds @ DmInv
         U, _, Vt = np.linalg.svd(Fg)

@@ -22,5 +22,6 @@ pipeline_checks.check_bar_reconstruction(ops, comm)
 pipeline_checks.check_bar_reduced(ops, comm)
 pipeline_checks.check_verts_geom(ops, comm)
 pipeline_checks.check_zero_residual(ops, comm)
+pipeline_checks.check_pd_local(ops, comm)
 print(f"RANK{comm.rank} OK", flush=True)
 dist.destroy_process_group()
