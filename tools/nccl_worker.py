@@ -30,6 +30,7 @@ print(f"RANK{comm.rank}/{comm.world} r01-validated checks OK", flush=True)
 pipeline_checks.check_bar_reduced(ops, comm)
 pipeline_checks.check_verts_geom(ops, comm)
 pipeline_checks.check_zero_residual(ops, comm)
+pipeline_checks.check_pd_local(ops, comm)
 if "--mirror-classes" in sys.argv:           # main.py's two protocols through the drop-in classes, rows sharded over the GPUs
     import pathlib
     import tempfile
