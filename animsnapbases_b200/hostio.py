@@ -211,6 +211,60 @@ def load_off(filename, no_colors=False):
     return (vertex_data, faces) if no_colors else (vertex_data, colors, faces)
 
 
+_PLY_TYPES = {"char": "i1", "uchar": "u1", "short": "i2", "ushort": "u2", "int": "i4", "uint": "u4", "float": "f4", "double": "f8",
+              "int8": "i1", "uint8": "u1", "int16": "i2", "uint16": "u2", "int32": "i4", "uint32": "u4", "float32": "f4", "float64": "f8"}
+
+
+def load_ply(filename):
+    """-> (verts (N, 3) float, tris (T, 3) int) of a triangle-mesh PLY file, ascii or binary (utils/process.py:30-44 reads it
+    through TVTK's PLYReader, a third-party dependency that is absent here; this reader needs none).  Vertex properties
+    other than x, y, z are skipped; every face must be a triangle, as the reference asserts (:43)."""
+    with open(filename, "rb") as f:
+        assert f.readline().strip() == b"ply", "PLY header missing"
+        fmt, elements = None, []
+        while True:
+            tok = f.readline().decode("ascii", "replace").split()
+            if not tok or tok[0] == "comment" or tok[0] == "obj_info":
+                continue
+            if tok[0] == "format":
+                fmt = tok[1]
+            elif tok[0] == "element":
+                elements.append((tok[1], int(tok[2]), []))
+            elif tok[0] == "property":
+                elements[-1][2].append(tok[1:])
+            elif tok[0] == "end_header":
+                break
+        assert fmt in ("ascii", "binary_little_endian", "binary_big_endian"), "unknown PLY format"
+        end = ">" if fmt == "binary_big_endian" else "<"
+        verts = tris = None
+        for name, count, props in elements:
+            is_list = any(p[0] == "list" for p in props)
+            if fmt == "ascii":
+                rows = [f.readline().split() for _ in range(count)]
+                if name == "vertex":
+                    names = [p[-1] for p in props]
+                    cols = [names.index(c) for c in ("x", "y", "z")]
+                    verts = np.array([[float(r[c]) for c in cols] for r in rows], dtype=np.float64)
+                elif name == "face":
+                    assert all(int(r[0]) == 3 for r in rows), "only triangle meshes"
+                    tris = np.array([[int(v) for v in r[1:4]] for r in rows], dtype=np.int64)
+            elif not is_list:
+                dt = np.dtype([(p[-1], end + _PLY_TYPES[p[0]]) for p in props])
+                data = np.frombuffer(f.read(dt.itemsize * count), dtype=dt)
+                if name == "vertex":
+                    verts = np.stack([data["x"], data["y"], data["z"]], axis=1).astype(np.float64)
+            else:
+                assert len(props) == 1 or name != "face", "faces with extra properties are not supported"
+                _, ct, it, _ = props[0]
+                dt = np.dtype([("n", end + _PLY_TYPES[ct]), ("v", end + _PLY_TYPES[it], (3,))])
+                data = np.frombuffer(f.read(dt.itemsize * count), dtype=dt)
+                assert np.all(data["n"] == 3), "only triangle meshes"
+                if name == "face":
+                    tris = data["v"].astype(np.int64)
+    assert verts is not None and tris is not None, "PLY file without vertex / face elements"
+    return verts, tris
+
+
 def filter_reindex(condition, target):
     """utils/process.py:94-106: indices `target` re-numbered after dropping the entries where `condition` is False."""
     if condition.dtype != bool:

@@ -415,3 +415,35 @@ def test_mirror_error_behaviour(tmp_path):
     finally:
         os.chdir(cwd)
         runtime.install(None, None)
+
+
+def test_ply_reader(tmp_path):
+    """hostio.load_ply (main.py:52-58 `.ply` snapshots; the reference needs TVTK for it): ascii and binary files, extra vertex
+    properties skipped, non-triangle faces refused."""
+    from animsnapbases_b200 import hostio, synth
+    verts, tris = synth.grid_mesh(5, 4)
+    verts = verts.astype(np.float32)
+    head = "ply\nformat %s 1.0\ncomment made by a test\nelement vertex %d\nproperty float x\nproperty float y\nproperty float z\n" \
+           "property uchar red\nelement face %d\nproperty list uchar int vertex_indices\nend_header\n"
+    with open(tmp_path / "a.ply", "w") as f:
+        f.write(head % ("ascii", len(verts), len(tris)))
+        f.writelines("%.9g %.9g %.9g 7\n" % tuple(v) for v in verts)
+        f.writelines("3 %d %d %d\n" % tuple(t) for t in tris)
+    for fmt, end in (("binary_little_endian", "<"), ("binary_big_endian", ">")):
+        with open(tmp_path / (fmt + ".ply"), "wb") as f:
+            f.write((head % (fmt, len(verts), len(tris))).encode())
+            vt = np.empty(len(verts), dtype=[("x", end + "f4"), ("y", end + "f4"), ("z", end + "f4"), ("red", "u1")])
+            vt["x"], vt["y"], vt["z"], vt["red"] = verts[:, 0], verts[:, 1], verts[:, 2], 7
+            f.write(vt.tobytes())
+            ft = np.empty(len(tris), dtype=[("n", "u1"), ("v", end + "i4", (3,))])
+            ft["n"], ft["v"] = 3, tris
+            f.write(ft.tobytes())
+    for name in ("a.ply", "binary_little_endian.ply", "binary_big_endian.ply"):
+        v, t = hostio.load_ply(str(tmp_path / name))
+        assert np.array_equal(v.astype(np.float32), verts) and np.array_equal(t, tris), name
+    with open(tmp_path / "quad.ply", "w") as f:
+        f.write(head % ("ascii", 4, 1))
+        f.writelines("%d %d 0 7\n" % (i % 2, i // 2) for i in range(4))
+        f.write("4 0 1 3 2\n")
+    with pytest.raises(AssertionError):
+        hostio.load_ply(str(tmp_path / "quad.ply"))
