@@ -38,6 +38,25 @@ def grid_mesh(nx: int, ny: int):
     return verts, tris
 
 
+def tet_grid(nx: int, ny: int, nz: int):
+    """Structured tetrahedral block: (nx+1)(ny+1)(nz+1) vertices in the unit cube scaled by the cell counts, every cell
+    split into 6 positively oriented tets around its main diagonal.  Returns (verts (V, 3) float64, tets (6 nx ny nz, 4))."""
+    gx, gy, gz = np.meshgrid(np.arange(nx + 1), np.arange(ny + 1), np.arange(nz + 1), indexing="ij")
+    verts = np.stack([gx.ravel() / max(nx, ny, nz), gy.ravel() / max(nx, ny, nz), gz.ravel() / max(nx, ny, nz)], axis=1).astype(np.float64)
+    vid = lambda i, j, k: (i * (ny + 1) + j) * (nz + 1) + k          # noqa: E731
+    ci, cj, ck = np.meshgrid(np.arange(nx), np.arange(ny), np.arange(nz), indexing="ij")
+    ci, cj, ck = ci.ravel(), cj.ravel(), ck.ravel()
+    c = {(a, b, d): vid(ci + a, cj + b, ck + d) for a in (0, 1) for b in (0, 1) for d in (0, 1)}
+    paths = [((1, 0, 0), (1, 1, 0)), ((1, 0, 0), (1, 0, 1)), ((0, 1, 0), (1, 1, 0)), ((0, 1, 0), (0, 1, 1)),
+             ((0, 0, 1), (1, 0, 1)), ((0, 0, 1), (0, 1, 1))]                 # the 6 monotone paths from corner 000 to 111
+    tets = np.concatenate([np.stack([c[(0, 0, 0)], c[p1], c[p2], c[(1, 1, 1)]], axis=1) for p1, p2 in paths])
+    x = verts
+    vol = np.einsum("ij,ij->i", np.cross(x[tets[:, 1]] - x[tets[:, 0]], x[tets[:, 2]] - x[tets[:, 0]]), x[tets[:, 3]] - x[tets[:, 0]])
+    flip = vol < 0
+    tets[flip] = tets[flip][:, [0, 2, 1, 3]]
+    return verts, tets.astype(np.int64)
+
+
 def read_obj_mesh(path: str):
     """Minimal Wavefront OBJ reader: `v x y z` and triangular `f a b c` (1-based, a/b/c forms)."""
     vs, fs = [], []

@@ -28,6 +28,35 @@ def timed(fn, reps=3, warm=1):
     return best * 1e-3
 
 
+def pd_bench(cells, frames):
+    """asb_pd_project / asb_pd_vertex_bending on a structured block: HBM-bound gather/scatter, one thread per
+    (element, frame).  Algorithmic bytes per element and frame: rest data + node ids + rows * 24 B written +
+    the element's share of the vertex planes."""
+    import numpy as np
+    from animsnapbases_b200 import pd_local, runtime, synth
+    from animsnapbases_b200.engine import Comm
+    ops = CudaOps("cuda:0")
+    runtime.install(ops, Comm(enabled=False))
+    verts, tets = synth.tet_grid(cells, cells, cells)
+    nv, e = len(verts), len(tets)
+    q0 = ops.ingest(ops.to_device(np.ascontiguousarray(verts[None])), None, pad_ld(nv))
+    q = q0.repeat(frames, 1, 1)
+    q += 0.05 * torch.sin(7.0 * q.roll(1, dims=1) + torch.arange(frames, device=q.device, dtype=q.dtype)[:, None, None])
+    for name, rest_b, ids_b in (("tets_deformation_gradient", 72, 16), ("tets_strain", 72, 16)):
+        grp = pd_local.ConstraintGroup(name, verts, tets)
+        out = ops.zeros((frames, 3, pad_ld(3 * e)))
+        t = timed(lambda: ops.pd_project(grp.kind, q, grp._elems, grp._rest, grp.sigma_min, grp.sigma_max, out))
+        byts = frames * (e * (rest_b + ids_b + 3 * 24.0) + nv * 24.0)
+        print(json.dumps({"kernel": "asb_pd_project/" + name, "elements": e, "verts": nv, "frames": frames, "ms": t * 1e3,
+                          "GB/s": byts / t / 1e9, "Melem_frames/s": e * frames / t / 1e6}), flush=True)
+    tris = np.concatenate([tets[:, [0, 1, 2]], tets[:, [0, 1, 3]]])[: 2 * e]
+    es = pd_local.ConstraintGroup("edge_spring", verts, np.unique(np.sort(tris[:, :2], axis=1), axis=0))
+    out = ops.zeros((frames, 3, pad_ld(es.num_elements)))
+    t = timed(lambda: ops.pd_project(es.kind, q, es._elems, es._rest, 0.0, 0.0, out))
+    print(json.dumps({"kernel": "asb_pd_project/edge_spring", "elements": es.num_elements, "frames": frames, "ms": t * 1e3,
+                      "GB/s": frames * (es.num_elements * (8 + 8 + 24.0) + nv * 24.0) / t / 1e9}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--verts", type=int, default=1000000)
@@ -35,7 +64,11 @@ def main():
     ap.add_argument("--comps", type=int, default=200)
     ap.add_argument("--only", default="")
     ap.add_argument("--once", action="store_true", help="one launch per kernel, no warm-up (for ncu --set full captures)")
+    ap.add_argument("--pd", type=int, nargs=2, metavar=("CELLS", "FRAMES"), default=None,
+                    help="time the snapshot-producer kernels instead: CELLS^3 grid cells x 6 tets, FRAMES position frames")
     args = ap.parse_args()
+    if args.pd:
+        return pd_bench(args.pd[0], args.pd[1])
     if args.once:
         global timed
         _t = timed
