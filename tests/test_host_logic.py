@@ -447,3 +447,15 @@ def test_ply_reader(tmp_path):
         f.write("4 0 1 3 2\n")
     with pytest.raises(AssertionError):
         hostio.load_ply(str(tmp_path / "quad.ply"))
+
+
+def test_tet_grid_generator():
+    """synth.tet_grid (the block the snapshot-producer timing runs on): conforming, positively oriented, fills the box."""
+    from animsnapbases_b200 import synth
+    v, t = synth.tet_grid(3, 2, 4)
+    assert v.shape == (4 * 3 * 5, 3) and t.shape == (6 * 24, 4) and len(np.unique(t)) == len(v)
+    vol = np.einsum("ij,ij->i", np.cross(v[t[:, 1]] - v[t[:, 0]], v[t[:, 2]] - v[t[:, 0]]), v[t[:, 3]] - v[t[:, 0]]) / 6
+    assert vol.min() > 0 and abs(vol.sum() - 24 / 4 ** 3) < 1e-12
+    faces = np.sort(np.concatenate([t[:, [0, 1, 2]], t[:, [0, 1, 3]], t[:, [0, 2, 3]], t[:, [1, 2, 3]]]), axis=1)
+    _, counts = np.unique(faces, axis=0, return_counts=True)
+    assert set(counts) == {1, 2}, "every interior face is shared by exactly two tets"
