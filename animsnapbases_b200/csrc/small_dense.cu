@@ -29,6 +29,60 @@ __global__ void gather_traj_kernel(const double* __restrict__ R, int64_t F, int6
     }
 }
 
+// Multi-GPU pick, step 1: this rank's candidate packed for ONE all-gather: cand[0] = local maximum, cand[1] = its global
+// index (int64 bit pattern), cand[2 + d F + f] = the candidate vertex's trajectory (corrected for the pending block).
+__global__ void gather_candidate_kernel(const double* __restrict__ R, int64_t F, int64_t N, int64_t ld,
+                                        const double* __restrict__ val_dev, const int64_t* __restrict__ idx_dev, int64_t row0,
+                                        const double* __restrict__ Wp, int64_t ldw, const double* __restrict__ Cp,
+                                        int64_t npend, double* __restrict__ cand) {
+    __shared__ double cp[16 * 3];
+    const int64_t idx = idx_dev[0] - row0;
+    const bool live = idx >= 0 && idx < N;
+    if (threadIdx.x == 0) {
+        cand[0] = live ? val_dev[0] : -INFINITY;
+        cand[1] = __longlong_as_double(live ? (long long)idx_dev[0] : 0x7fffffffffffffffLL);
+    }
+    if (!live) {
+        for (int64_t t = threadIdx.x; t < 3 * F; t += blockDim.x) cand[2 + t] = 0.0;
+        return;
+    }
+    for (int t = threadIdx.x; t < npend * 3; t += blockDim.x) cp[t] = Cp[(int64_t)t * ld + idx];
+    __syncthreads();
+    for (int64_t f = threadIdx.x; f < F; f += blockDim.x) {
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            double v = R[(f * 3 + d) * ld + idx];
+            for (int j = 0; j < npend; ++j) v = __dsub_rn(v, __dmul_rn(Wp[f * ldw + j], cp[j * 3 + d]));
+            cand[2 + d * F + f] = v;
+        }
+    }
+}
+
+// step 2 (after the all-gather): the winner over the ranks -- largest value, ties to the lowest global index (np.argmax) --
+// and its trajectory.  One block.
+__global__ void select_candidate_kernel(const double* __restrict__ all, int64_t world, int64_t stride, int64_t F,
+                                        double* __restrict__ out_val, int64_t* __restrict__ out_idx, double* __restrict__ traj) {
+    __shared__ int win;
+    if (threadIdx.x == 0) {
+        ArgMax a;
+        a.v = -INFINITY;
+        a.i = 0x7fffffffffffffffLL;
+        int w = 0;
+        for (int64_t r = 0; r < world; ++r) {
+            ArgMax t;
+            t.v = all[r * stride];
+            t.i = __double_as_longlong(all[r * stride + 1]);
+            if (t.v > a.v || (t.v == a.v && t.i < a.i)) { a = t; w = (int)r; }
+        }
+        win = w;
+        out_val[0] = a.v;
+        out_idx[0] = (int64_t)a.i;
+    }
+    __syncthreads();
+    const double* src = all + (int64_t)win * stride + 2;
+    for (int64_t t = threadIdx.x; t < 3 * F; t += blockDim.x) traj[t] = src[t];
+}
+
 // one block; traj: 3 x F
 __global__ void traj_rank1_kernel(const double* __restrict__ traj, int64_t F, int local_support,
                                   double* __restrict__ wout, int64_t ldw, const double* __restrict__ Wp,
@@ -450,6 +504,24 @@ int asb_gather_traj(const double* R, int64_t F, int64_t N, int64_t ld, const int
     ASB_REQUIRE(R && idx_dev && traj && F > 0 && N > 0 && npend >= 0 && npend <= 16, "gather_traj: bad arguments");
     ASB_REQUIRE(npend == 0 || (Wp && Cp), "gather_traj: pending block pointers");
     gather_traj_kernel<<<1, 256, 0, S(stream)>>>(R, F, N, ld, idx_dev, row0, Wp, ldw, Cp, npend, traj);
+    ASB_LAUNCH_CHECK();
+    return ASB_OK;
+}
+
+int asb_gather_candidate(const double* R, int64_t F, int64_t N, int64_t ld, const double* val_dev, const int64_t* idx_dev,
+                         int64_t row0, const double* Wp, int64_t ldw, const double* Cp, int64_t npend, double* cand,
+                         asb_stream_t stream) {
+    ASB_REQUIRE(R && val_dev && idx_dev && cand && F > 0 && N >= 0 && npend >= 0 && npend <= 16, "gather_candidate: bad arguments");
+    ASB_REQUIRE(npend == 0 || (Wp && Cp), "gather_candidate: pending block pointers");
+    gather_candidate_kernel<<<1, 256, 0, S(stream)>>>(R, F, N, ld, val_dev, idx_dev, row0, Wp, ldw, Cp, npend, cand);
+    ASB_LAUNCH_CHECK();
+    return ASB_OK;
+}
+
+int asb_select_candidate(const double* all, int64_t world, int64_t stride, int64_t F, double* out_val, int64_t* out_idx,
+                         double* traj, asb_stream_t stream) {
+    ASB_REQUIRE(all && out_val && out_idx && traj && world > 0 && F > 0 && stride >= 2 + 3 * F, "select_candidate: bad arguments");
+    select_candidate_kernel<<<1, 256, 0, S(stream)>>>(all, world, stride, F, out_val, out_idx, traj);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
 }

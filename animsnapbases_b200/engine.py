@@ -42,18 +42,32 @@ class Comm:
         lowest index (np.argmax).  val: (B,) f64, idx: (B,) i64; both are overwritten with the global result."""
         if self.world == 1:
             return val, idx
-        vals = [torch.empty_like(val) for _ in range(self.world)]
-        idxs = [torch.empty_like(idx) for _ in range(self.world)]
-        self.dist.all_gather(vals, val)
-        self.dist.all_gather(idxs, idx)
-        V = torch.stack(vals)                      # (world, B)
-        J = torch.stack(idxs)
+        B = val.numel()
+        pack = torch.empty((2, B), dtype=torch.float64, device=val.device)     # ONE collective: values and index bit patterns
+        pack[0] = val
+        pack[1] = idx.view(torch.float64)
+        allp = self.all_gather_rows(pack.view(-1)).view(self.world, 2, B)
+        V = allp[:, 0]                             # (world, B)
+        J = allp[:, 1].contiguous().view(torch.int64)
         m = V.max(dim=0).values
         big = torch.iinfo(torch.int64).max
         cand = torch.where(V == m[None], J, torch.full_like(J, big))
         val.copy_(m)
         idx.copy_(cand.min(dim=0).values)
         return val, idx
+
+    def all_gather_rows(self, t, out=None):
+        """t: contiguous 1-D tensor, equal length on every rank -> (world, len) tensor holding every rank's copy."""
+        if out is None:
+            out = torch.empty((self.world, t.numel()), dtype=t.dtype, device=t.device)
+        if self.world == 1:
+            out[0].copy_(t)
+            return out
+        try:
+            self.dist.all_gather_into_tensor(out.view(-1), t)
+        except (RuntimeError, NotImplementedError):                 # back ends without the flat variant
+            self.dist.all_gather([out[r] for r in range(self.world)], t)
+        return out
 
     def barrier(self):
         if self.world > 1:
@@ -185,15 +199,12 @@ def deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1
     val = ops.zeros((1,))
     idx = ops.zeros((1,), I64)
     s = ops.zeros((1, ld)) if local_support else None
+    pick = _Picker(ops, comm, F)
     k0 = 0
     for k in range(K):
         ops.argmax_first(e, N, row0, val, idx)
-        comm.argmax_pairs(val, idx)
+        pick(R, N, val, idx, row0, W, k0, C, k - k0, traj)
         picked[k:k + 1].copy_(idx)
-        if comm.world > 1:
-            traj.zero_()
-        ops.gather_traj(R, N, idx, row0, W, k0, C, k - k0, traj)
-        comm.allreduce_sum(traj)
         ops.traj_rank1(traj, F, local_support, W, k, k0, coef, scal)
         if local_support:
             with ops.fork():      # the heat-method query (60 small launches, latency bound) runs beside the HBM-bound pass
@@ -201,13 +212,58 @@ def deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1
         ops.deflate_gemv(R, N, W, k, g)
         ops.join()
         ops.deflate_finish(g, C, k, k0, coef, s[0] if local_support else None, scal, e, N, meas[k])
-        if comm.world > 1:
-            comm.allreduce_sum(meas[k, 2:3])
-            meas[k, 1:2] = torch.sqrt(meas[k, 2:3])
         if k - k0 + 1 == block or k == K - 1:
             ops.rank_update(R, N, W, C, k0, k - k0 + 1, e)
             k0 = k + 1
+    _reduce_norms(comm, meas)
     return C, W, meas, picked, (R if keep_residual else None)
+
+
+class _Picker:
+    """The exchange step of a deflation pick on row shards: ONE all-gather per component carries every rank's
+    (local maximum, global index, trajectory of that vertex); asb_select_candidate then leaves the winner's index and
+    trajectory on every rank.  Replaces two pair all-gathers plus a zero-fill + all-reduce of the trajectory (r01)."""
+
+    def __init__(self, ops, comm, F):
+        self.ops, self.comm = ops, comm
+        if comm.world > 1:
+            self.cand = ops.zeros((2 + 3 * F,))
+            self.all = ops.zeros((comm.world, 2 + 3 * F))
+
+    def __call__(self, R, N, val, idx, row0, W, k0, C, npend, traj):
+        """val / idx: this rank's local pick on entry, the global pick on return; traj (3, F): its trajectory."""
+        ops, comm = self.ops, self.comm
+        if comm.world == 1:
+            ops.gather_traj(R, N, idx, row0, W, k0, C, npend, traj)
+            return
+        ops.gather_candidate(R, N, val, idx, row0, W, k0, C, npend, self.cand)
+        comm.all_gather_rows(self.cand, out=self.all)
+        ops.select_candidate(self.all, R.shape[0], val, idx, traj)
+
+    def rows(self, R, N, row_idx, row0, W, k0, C, npend, traj):
+        """Trajectory of a row every rank already agrees on (block deflation: rows of the picked element)."""
+        ops, comm = self.ops, self.comm
+        if comm.world == 1:
+            ops.gather_traj(R, N, row_idx, row0, W, k0, C, npend, traj)
+            return
+        self.val1 = getattr(self, "val1", None)
+        if self.val1 is None:
+            self.val1 = ops.zeros((1,))
+            self.idx1 = ops.zeros((1,), I64)
+        self.idx1.copy_(row_idx)
+        ops.gather_candidate(R, N, self.val1, self.idx1, row0, W, k0, C, npend, self.cand)   # owner: value 0, others: -inf
+        comm.all_gather_rows(self.cand, out=self.all)
+        ops.select_candidate(self.all, R.shape[0], self.val1, self.idx1, traj)
+
+
+def _reduce_norms(comm, meas):
+    """meas[:, 2] holds this shard's part of |R|_F^2 after every component: one all-reduce of the K-vector after the loop
+    (it is a logged value; r01 reduced it once per component)."""
+    if comm.world > 1:
+        col = meas[:, 2].contiguous()
+        comm.allreduce_sum(col)
+        meas[:, 2] = col
+        meas[:, 1] = torch.sqrt(col)
 
 
 def deflate_blocks(ops, comm, X, shard, p, num_blocks, block=8, keep_residual=False):
@@ -236,31 +292,24 @@ def deflate_blocks(ops, comm, X, shard, p, num_blocks, block=8, keep_residual=Fa
     scal = ops.zeros((2,))
     val = ops.zeros((1,))
     idx = ops.zeros((1,), I64)
+    pick = _Picker(ops, comm, F)
     k0 = 0
     for kb in range(num_blocks):
-        if N:
-            ops.group_sum(e, N, p, eg)
-            ops.argmax_first(eg, N // p, row0 // p, val, idx)
-        else:
-            val.fill_(-float("inf"))
+        ops.group_sum(e, N, p, eg)
+        ops.argmax_first(eg, N // p, row0 // p, val, idx)
         comm.argmax_pairs(val, idx)
         elems[kb:kb + 1].copy_(idx)
         for i in range(p):
             k = kb * p + i
             rows[k:k + 1] = idx * p + i                       # index bookkeeping only
-            if comm.world > 1:
-                traj.zero_()
-            ops.gather_traj(R, N, rows[k:k + 1], row0, W, k0, C, k - k0, traj)
-            comm.allreduce_sum(traj)
+            pick.rows(R, N, rows[k:k + 1], row0, W, k0, C, k - k0, traj)
             ops.traj_rank1(traj, F, False, W, k, k0, coef, scal)
             ops.deflate_gemv(R, N, W, k, g)
             ops.deflate_finish(g, C, k, k0, coef, None, scal, e, N, meas[k])
-            if comm.world > 1:
-                comm.allreduce_sum(meas[k, 2:3])
-                meas[k, 1:2] = torch.sqrt(meas[k, 2:3])
             if k - k0 + 1 == block or k == K - 1:
                 ops.rank_update(R, N, W, C, k0, k - k0 + 1, e)
                 k0 = k + 1
+    _reduce_norms(comm, meas)
     m = meas.cpu().numpy().reshape(num_blocks, p, 3)
     el = elems.cpu().numpy()
     table = np.concatenate([np.arange(num_blocks, dtype=float)[:, None], el[:, None].astype(float), m[:, p - 1, 1:2], m[:, :, 0]],
@@ -317,19 +366,41 @@ def splocs(ops, comm, X, shard, C, W, K, geodesic, num_iters, num_admm, lam, rho
         if with_sparsity:
             comm.allreduce_sum(sp)
 
+    # Host traffic of the loop: the K centre ids of an iteration are the memoisation key of the support maps and decide how
+    # many heat solves are launched, so the host has to see them -- through a pinned buffer filled by an async copy that was
+    # queued behind `centres()`, and only AFTER the weight sweep and the B0 GEMM of the next iteration are in the queue (the
+    # GPU is busy while the host waits).  Energies and the Cholesky status go to pinned memory the same way and are read
+    # once, after the loop (r01: three blocking reads per iteration).
+    pinned = ops.device.type == "cuda"
+    ids_host = torch.empty((K,), dtype=I64, pin_memory=pinned)
+    ids_ready = torch.cuda.Event() if pinned else None
+    scal_host = torch.empty((num_iters, 3), dtype=F64, pin_memory=pinned)
+    info_host = torch.empty((num_iters,), dtype=I32, pin_memory=pinned)
+    Pp = ops.zeros((F, Kp)) if Kp != K else None
+
+    def post_ids():
+        ids_host.copy_(idx, non_blocking=True)
+        if ids_ready is not None:
+            ids_ready.record()
+
     P, Q = grams()
     centres(False)
-    hist, centre_hist = [], []
+    post_ids()
+    centre_hist = []
     for it in range(num_iters):
         ops.weights_sweep(P, Q, W, F, K)
-        ids = idx.tolist()                                              # K ints -> host (memoisation key)
-        centre_hist.append(ids)
-        with ops.fork():          # support maps of the new centres: side stream, beside the B0 GEMM (Lambda is read by ADMM only)
-            geodesic.support(idx, 1, lam, dmin, dmax, row0, N, Lambda, ids_host=ids, comm=comm)
         ops.gram_small(W, F, K, rho, H)                                 # H = W^T W + rho I
         ops.spd_inverse(H, K, Hinv, info)
         ops.small_gemm(0, 1, K, F, K, 1.0, Hinv, W, Aw)                 # Aw = H^-1 W^T   (K x F)
         ops.gemm_nn(Aw, K, F, Xm, M, 1.0, B0.view(K, M))                # B0 = H^-1 (W^T X)
+        if ids_ready is not None:
+            ids_ready.synchronize()
+        ids = ids_host.tolist()                                         # K ints (memoisation key)
+        centre_hist.append(ids)
+        # support maps of the new centres on the side stream, ordered after `centres()` of the previous iteration only (not
+        # after the B0 GEMM just queued): they run beside it; Lambda is read by the ADMM launch below, after the join
+        with ops.fork(after=ids_ready):
+            geodesic.support(idx, 1, lam, dmin, dmax, row0, N, Lambda, ids_host=ids, comm=comm)
         ops.join()
         if K8 == Kp:
             ops.axpby(Hr[:K].view(1, -1), rho, Hinv.view(1, -1), None, 0.0, None, K * Kp)
@@ -339,58 +410,127 @@ def splocs(ops, comm, X, shard, C, W, K, geodesic, num_iters, num_admm, lam, rho
         ops.admm_solve(Hr, B0, C, U, Lambda, K, N, 1.0 / rho, num_admm)
         P, Q = grams()
         centres(True)
+        post_ids()
         # energy = |X - W C|^2 + sum Lambda |c|  via  |X|^2 - 2 <W, P> + <W Q, W>
         ops.small_gemm(0, 0, F, K, K, 1.0, W, Q, WQ)
-        ops.batched_dot(W.view(1, -1), P_pad(ops, P, Kp).view(1, -1), F * Kp, scal3[0:1])
+        if Pp is not None:
+            Pp[:, :K] = P
+        ops.batched_dot(W.view(1, -1), (P if Pp is None else Pp).view(1, -1), F * Kp, scal3[0:1])
         ops.batched_dot(W.view(1, -1), WQ.view(1, -1), F * Kp, scal3[1:2])
         scal3[2:3] = sp.sum()
-        wp, wqw, sparsity = (float(v) for v in scal3.tolist())
+        scal_host[it].copy_(scal3, non_blocking=True)
+        info_host[it:it + 1].copy_(info, non_blocking=True)
+    ops.synchronize()
+    hist = []
+    for it in range(num_iters):
+        if int(info_host[it]) != 0:
+            raise FloatingPointError("SPLOCS: W^T W + rho I is not positive definite")
+        wp, wqw, sparsity = (float(v) for v in scal_host[it].tolist())
         r2 = max(xnorm2 - 2.0 * wp + wqw, 0.0)
         e_rms = np.sqrt(r2) / np.sqrt(3.0 * shard.n_global * F)
         energy = r2 + sparsity
         hist.append((energy, e_rms))
-        if int(info.item()) != 0:
-            raise FloatingPointError("SPLOCS: W^T W + rho I is not positive definite")
         if log is not None and comm.rank == 0:
             log("itr %03d, Energy =%f, Error =%f" % (it, energy, e_rms))
     return np.array(hist), np.array(centre_hist)
 
 
-def P_pad(ops, P, Kp):
-    """P is (F, K) contiguous; W is (F, Kp). Return P with Kp columns (zero padded) for element-wise dots."""
-    if P.shape[1] == Kp:
-        return P
-    out = ops.zeros((P.shape[0], Kp))
-    out[:, :P.shape[1]] = P
-    return out
-
-
 # ====================================================================================== POD (k15)
-def pod(ops, comm, X, shard, k_desired):
-    """Tall-skinny PCA of the (3 ep x F) snapshot matrix (snapbases/constraintsComponents.py:298-320):
-    Gram X X^T on the DMMA pipe (+ all-reduce), F x F symmetric eigensolve (replicated), back-projection
-    U^T = S^-1 V^T X.  Returns comps (K,3,ld) planar, all F singular values (host, descending)."""
+def pod(ops, comm, X, shard, k_desired, max_passes=4, theta=1e-3):
+    """Tall-skinny PCA of the (3 ep x F) snapshot matrix (snapbases/constraintsComponents.py:298-320): Gram X X^T on the DMMA
+    pipe (+ all-reduce), F x F symmetric eigensolve (replicated), back-projection U^T = S^-1 V^T X.
+
+    One Gram resolves sigma_i only down to ~theta * sigma_1 at the 1e-10 the north star asks for (forming X X^T squares the
+    condition number: relative error eps (sigma_1 / sigma_i)^2), while the reference keeps ALL F modes and runs DEIM
+    on them (the bar: sigma_1 / sigma_69 = 1e8).  So the spectrum is peeled in passes: a pass accepts the modes with
+    sigma_i >= theta * (largest sigma of the pass), back-projects them, re-orthogonalises them against the modes of earlier
+    passes, removes their span from a working copy of X (X <- X - (X U^T) U, two skinny GEMMs) and forms the Gram of what is
+    left, whose largest singular value is now theta times smaller.  Leakage of the removed modes enters the next Gram at second
+    order only.  A well-conditioned snapshot matrix takes one pass and never copies X.
+    Returns comps (K,3,ld) planar, all F singular values (host, descending).  Modes whose sigma is below F eps sigma_1
+    (rest_shape='first' makes frame 0 identically zero: at least one) have no defined direction and are returned as zero."""
     F, _, ld = X.shape
     M = 3 * ld
-    Xm = X.view(F, M)
     Fp = (F + 1) // 2 * 2
-    G = ops.zeros((F, Fp))
-    ops.gemm_nt(Xm, F, Xm, F, M, symmetric=True, out=G)
-    comm.allreduce_sum(G)
-    evals, info = ops.syevd(G, F)                       # rows of G = eigenvectors, ascending eigenvalues
-    ev = evals.cpu().numpy()
-    if int(info.item()) != 0:
-        raise FloatingPointError("syevd failed")
-    lam = ev[::-1].copy()
-    sig = np.sqrt(np.maximum(lam, 0.0))
     K = min(int(k_desired), F)
-    floor = F * np.finfo(np.float64).eps * lam[0]      # Gram accuracy floor (SURVEY H2): modes below are undefined
-    inv = np.where(lam[:K] > floor, 1.0 / np.where(sig[:K] > 0, sig[:K], 1.0), 0.0)
-    order = ops.to_device(np.arange(F - 1, F - 1 - K, -1).astype(np.int64))
-    A = torch.index_select(G, 0, order).contiguous()    # descending order (data movement only)
-    comps = ops.empty((K, 3, ld))
-    ops.gemm_nn(A, K, F, Xm, M, 1.0, comps.view(K, M), row_scale=ops.to_device(inv))
-    return comps, sig
+    eps = np.finfo(np.float64).eps
+    comps = ops.zeros((K, 3, ld))
+    Cm = comps.view(K, M)
+    sig_all = np.zeros(F)
+    Xw, owned = X.view(F, M), False
+    small = F * M * 8 <= (1 << 31)                      # all F singular values are worth extra passes only on small problems
+    done, sig1 = 0, None
+    for it in range(max_passes):
+        G = ops.zeros((F, Fp))
+        ops.gemm_nt(Xw, F, Xw, F, M, symmetric=True, out=G)
+        comm.allreduce_sum(G)
+        evals, info = ops.syevd(G, F)                   # rows of G = eigenvectors, ascending eigenvalues
+        ev = evals.cpu().numpy()
+        if int(info.item()) != 0:
+            raise FloatingPointError("syevd failed")
+        lam = ev[::-1].copy()[:F - done]                # descending; the `done` removed directions sit at the bottom (noise)
+        sig = np.sqrt(np.maximum(lam, 0.0))
+        if sig1 is None:
+            sig1 = sig[0]
+        null = F * eps * sig1
+        last = it == max_passes - 1
+        if sig[0] <= null:                              # nothing but round-off is left
+            sig_all[done:] = sig
+            break
+        r = int((sig >= theta * sig[0]).sum())
+        more = (not last) and done + r < F and sig[r] > null and (done + r < K or small) if r < len(sig) else False
+        if not more:
+            r = len(sig)                                # final pass: everything that is left, with the Gram floor of this pass
+        sig_all[done:done + r] = sig[:r]
+        nm = max(0, min(K - done, r))                   # modes of this pass that the caller asked for
+        nu = r if more else nm                          # modes to back-project (all accepted ones if they must be removed)
+        if nu > 0:
+            floor = max(F * eps * lam[0], null * null)
+            inv = np.where(lam[:nu] > floor, 1.0 / np.where(sig[:nu] > 0, sig[:nu], 1.0), 0.0)
+            order = ops.to_device(np.arange(F - 1, F - 1 - nu, -1).astype(np.int64))
+            A = torch.index_select(G, 0, order).contiguous()          # descending order (data movement only)
+            U = Cm[done:done + nu] if (nu <= nm and done == 0) else ops.empty((nu, M))
+            ops.gemm_nn(A, nu, F, Xw, M, 1.0, U, row_scale=ops.to_device(inv))
+            if done > 0:
+                nprev = min(done, K)
+                if nprev > 0:                           # first-order leakage of earlier modes: one CGS step + renormalisation
+                    H = ops.gemm_nt(U, nu, Cm[:nprev], nprev, M)
+                    comm.allreduce_sum(H)
+                    Hp = ops.zeros((nu, (nprev + 1) // 2 * 2))
+                    Hp[:, :nprev] = H
+                    corr = ops.empty((nu, M))
+                    ops.gemm_nn(Hp, nu, nprev, Cm[:nprev], M, 1.0, corr)
+                    ops.axpby(U, 1.0, U, None, -1.0, corr, M)
+                    del corr
+                Gu = ops.gemm_nt(U, nu, U, nu, M, symmetric=True)
+                comm.allreduce_sum(Gu)
+                nrm2 = torch.diagonal(Gu).cpu().numpy()
+                sc = np.where((inv > 0) & (nrm2 > 0), 1.0 / np.sqrt(np.where(nrm2 > 0, nrm2, 1.0)), 0.0)
+                eye = ops.zeros((nu, (nu + 1) // 2 * 2))
+                eye[:, :nu] = torch.eye(nu, dtype=F64, device=eye.device)
+                Un = ops.empty((nu, M))
+                ops.gemm_nn(eye, nu, nu, U, M, 1.0, Un, row_scale=ops.to_device(sc))
+                U = Un
+            if nm > 0 and U.data_ptr() != Cm[done].data_ptr():
+                Cm[done:done + nm].copy_(U[:nm])
+        if not more:
+            break
+        # ---- remove the accepted span from the working copy:  Xw <- Xw - (Xw U^T) U
+        if not owned:
+            Xw, owned = X.clone().view(F, M), True
+        P1 = ops.gemm_nt(Xw, F, U, r, M)
+        comm.allreduce_sum(P1)
+        P1p = ops.zeros((F, (r + 1) // 2 * 2))
+        P1p[:, :r] = P1
+        fc = max(1, min(F, (1 << 28) // max(M, 1)))     # frames per chunk: 2 GB of scratch at most
+        for f0 in range(0, F, fc):
+            f1 = min(F, f0 + fc)
+            tmp = ops.empty((f1 - f0, M))
+            ops.gemm_nn(P1p[f0:f1], f1 - f0, r, U, M, 1.0, tmp)
+            ops.axpby(Xw[f0:f1], 1.0, Xw[f0:f1], None, -1.0, tmp, M)
+            del tmp
+        done += r
+    return comps, sig_all
 
 
 def pod_per_row(ops, comm, X, shard, p, k_desired):
@@ -453,10 +593,24 @@ def orthogonalize_rows(ops, comm, T, shard, K):
 
 
 # ====================================================================================== DEIM (k19)
-def deim(ops, comm, C, shard, K):
+def _lstsq_coeffs(Vp, k, a):
+    """a[d, :k] = minimum-norm least-squares solution of Vp[d, :k, :k] x = Vp[d, :k, k] per dimension, like the reference's
+    np.linalg.lstsq(V[Pt, :, i], vk[Pt, i], rcond=None) (constraintsComponents.py:826, :752): singular values below
+    eps * k * sigma_max are dropped.  Replicated k x k work (batched SVD through torch / cuSOLVER)."""
+    A, b = Vp[:, :k, :k], Vp[:, :k, k]
+    x = torch.linalg.pinv(A, rtol=float(np.finfo(np.float64).eps) * k) @ b[:, :, None]
+    a[:, :k] = x[:, :, 0]
+
+
+def deim(ops, comm, C, shard, K, robust=False):
     """Classical DEIM point selection shared by x/y/z (snapbases/constraintsComponents.py:797-860).
     C: (K, 3, ld) planar post-processed basis.  Returns Pt (K,) global row ids (host int64) or None if a residual
-    vanished (the reference prints an error and returns, :832-834)."""
+    vanished (the reference prints an error and returns, :832-834).
+
+    The k x k interpolation systems are solved by LU on one CTA per dimension without any host synchronisation.  A basis
+    whose selected rows are rank deficient in one dimension (e.g. a coordinate that is identically zero on the picked rows: the
+    rows of a rotation that never leaves a plane) makes LU hit a zero pivot, where the reference's lstsq returns the minimum
+    norm solution: the loop is then repeated with `robust` coefficients (_lstsq_coeffs)."""
     N, row0 = shard.n, shard.row0
     ld = C.shape[2]
     Kp = (K + 3) // 4 * 4
@@ -475,29 +629,34 @@ def deim(ops, comm, C, shard, K):
                 Vp.zero_()
             ops.deim_gather(C, N, row0, Pt, k, Vp)
             comm.allreduce_sum(Vp)
-            ops.deim_solve(Vp, k, a, info)
+            if robust:
+                _lstsq_coeffs(Vp, k, a)
+            else:
+                ops.deim_solve(Vp, k, a, info)
         ops.deim_residual(C, N, k, a, e, maxabs[k:k + 1])
         ops.argmax_first(e, N, row0, val, idx)
         comm.argmax_pairs(val, idx)
         Pt[k:k + 1].copy_(idx)
     comm.allreduce_max(maxabs)
     mx = maxabs.cpu().numpy()
+    if not robust and int(info.item()) != 0:
+        # a zero pivot: the selected rows are rank deficient in some dimension (or a basis member repeats: the robust pass
+        # then finds the vanishing residual exactly where the reference does)
+        return deim(ops, comm, C, shard, K, robust=True)
     # np.allclose(r, 0) <=> max|r| <= 1e-8.  The reference stops at the first vanishing residual (:832-834); the loop above
-    # runs on without host synchronisation, so whatever the later steps did with a repeated row (a singular interpolation
-    # matrix, flagged in `info`) is a consequence of it and is discarded with them.
+    # runs on without host synchronisation, so whatever the later steps did with a repeated row is discarded with them.
     if K > 1 and np.any(mx[1:] <= 1e-8):
         print("ERROR!: zero residual!!")
         return None
-    if int(info.item()) != 0:
-        raise FloatingPointError("DEIM: singular interpolation matrix (zero pivot in column %d)" % int(info.item()))
     return Pt.cpu().numpy()
 
 
-def deim_blocks(ops, comm, C, shard, p):
+def deim_blocks(ops, comm, C, shard, p, robust=False):
     """Block DEIM of snapbases/constraintsComponents.py:733-795: C (K p, 3, ld) planar basis, p rows per pick.
     Step k solves V[Pt, :kp] a = v_t[Pt] for each of the p targets t of block k (per dimension), accumulates the row
     energies of the p residuals, picks the first-max row, and appends all p rows of its element.
-    Returns dict(Pt (K p,), alpha (K,), alpha_ranges (K,), idxs (K,)) on the host, or None on a zero residual."""
+    Returns dict(Pt (K p,), alpha (K,), alpha_ranges (K,), idxs (K,)) on the host, or None on a zero residual.
+    `robust`: see deim()."""
     N, row0 = shard.n, shard.row0
     Kc = C.shape[0]
     K = Kc // p
@@ -521,16 +680,19 @@ def deim_blocks(ops, comm, C, shard, p):
                     Vp.zero_()
                 ops.deim_gather_rhs(C, N, row0, Pt, nb, nb + m, Vp)
                 comm.allreduce_sum(Vp)
-                ops.deim_solve(Vp, nb, a, info)
+                if robust:
+                    _lstsq_coeffs(Vp, nb, a)
+                else:
+                    ops.deim_solve(Vp, nb, a, info)
             ops.deim_residual_block(C, N, nb, nb + m, m > 0, a, e, maxabs[k:k + 1])
         ops.argmax_first(e, N, row0, val, idx)
         comm.argmax_pairs(val, idx)
         idxs[k:k + 1].copy_(idx)
         Pt[nb:nb + p] = (idx // p) * p + steps                # all p rows of the picked element (:781-783)
     comm.allreduce_max(maxabs)
-    if int(info.item()) != 0:
-        raise FloatingPointError("block DEIM: singular interpolation matrix at step %d" % int(info.item()))
     mx = maxabs.cpu().numpy()
+    if not robust and int(info.item()) != 0:                  # see deim(): decide everything on the robust pass
+        return deim_blocks(ops, comm, C, shard, p, robust=True)
     if K > 1 and np.any(mx[1:] <= 1e-8):
         print("ERROR!: zero residual!!")
         return None

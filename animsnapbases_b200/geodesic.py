@@ -110,10 +110,22 @@ class HeatGeodesics:
                       "levels": self.heat.stats["levels"],
                       "operator_bytes": self.heat.stats["operator_bytes"] + self.pois.stats["operator_bytes"]}
         self._cache = {}
+        self.cache_rows = 4          # memoised maps kept per request size: at most cache_rows * B rows per key (LRU)
 
     def reset(self):
         """Drop the memoised support maps (a new basis build starts cold)."""
         self._cache = {}
+
+    def _remember(self, cache, ids_now, new_rows):
+        """Insert {id: row} (each row a tensor of its own, not a view into a chunk buffer) and evict the least recently used
+        ids that the current request does not need once the table exceeds cache_rows * len(request) rows."""
+        for i, row in new_rows:
+            cache[i] = row
+        for i in ids_now:
+            cache.move_to_end(i)
+        cap = max(self.cache_rows * len(ids_now), 64)
+        while len(cache) > cap:
+            cache.popitem(last=False)
 
     # ------------------------------------------------------------------ queries
     def distances(self, idx_dev):
@@ -150,28 +162,30 @@ class HeatGeodesics:
                 ops.support_map(phi, self.n, dmin, dmax, mode, lam, row0, nloc, out[sl])
             return out
         key = (mode, float(lam), float(dmin), float(dmax), row0, nloc)
-        cache = self._cache.setdefault(key, {})
-        missing = sorted({int(i) for i in ids_host if int(i) not in cache})
+        from collections import OrderedDict
+        cache = self._cache.setdefault(key, OrderedDict())
+        ids_now = [int(i) for i in ids_host]
+        missing = sorted({i for i in ids_now if i not in cache})
         world = comm.world if comm is not None else 1
         if world > 1 and len(missing) > 1:
-            self._support_sharded(comm, missing, cache, mode, lam, dmin, dmax, row0, nloc, out.shape[1], chunk)
+            new_rows = self._support_sharded(comm, missing, mode, lam, dmin, dmax, row0, nloc, out.shape[1], chunk)
             missing_local = []
         else:
-            missing_local = missing
+            missing_local, new_rows = missing, []
         for b0 in range(0, len(missing_local), chunk):
             ids = missing_local[b0:b0 + chunk]
             idt = ops.to_device(np.asarray(ids, dtype=np.int64))
             phi = self.distances(idt)
             rows = ops.zeros((len(ids), out.shape[1]))
             ops.support_map(phi, self.n, dmin, dmax, mode, lam, row0, nloc, rows)
-            for j, i in enumerate(ids):
-                cache[i] = rows[j]
+            new_rows += [(i, rows[j].clone()) for j, i in enumerate(ids)]
+        self._remember(cache, ids_now, new_rows)
         self.stats["cache_hits"] += B - len(missing)
-        for b, i in enumerate(ids_host):
-            out[b].copy_(cache[int(i)])
+        for b, i in enumerate(ids_now):
+            out[b].copy_(cache[i])
         return out
 
-    def _support_sharded(self, comm, missing, cache, mode, lam, dmin, dmax, row0, nloc, ld, chunk):
+    def _support_sharded(self, comm, missing, mode, lam, dmin, dmax, row0, nloc, ld, chunk):
         """Round-robin the sources over the ranks, solve locally, exchange row slices (see `support`)."""
         ops = self.ops
         world, rank = comm.world, comm.rank
@@ -190,6 +204,4 @@ class HeatGeodesics:
                 if nj > 0:
                     ops.support_map(phi, self.n, dmin, dmax, mode, lam, r0j, nj, send[j][b0:b0 + len(ids)])
         recv = comm.all_to_all(send)
-        for j in range(world):
-            for b, i in enumerate(missing[j::world]):
-                cache[i] = recv[j][b, :ld]
+        return [(i, recv[j][b, :ld].clone()) for j in range(world) for b, i in enumerate(missing[j::world])]

@@ -97,12 +97,16 @@ class CudaOps:
             ws = self._ws[key] = torch.empty(int(nbytes) + 256, dtype=torch.uint8, device=self.device)
         return ws
 
-    def fork(self):
+    def fork(self, after=None):
         """Context manager: run the enclosed launches on the side stream, ordered after everything issued so far on the
-        current stream; `join()` makes the current stream wait for them."""
+        current stream -- or, with `after` (a recorded CUDA event), only after that event; `join()` makes the current
+        stream wait for them."""
         if self._side is None:
             self._side = torch.cuda.Stream(self.device)   # default priority: priority=-1 measured no better (r01: 17.8 s vs 17.6 s)
-        self._side.wait_stream(torch.cuda.current_stream(self.device))
+        if after is not None:
+            self._side.wait_event(after)
+        else:
+            self._side.wait_stream(torch.cuda.current_stream(self.device))
         return torch.cuda.stream(self._side)
 
     def join(self):
@@ -124,6 +128,11 @@ class CudaOps:
     # ------------------------------------------------------------------ boundary
     def ingest(self, src, row_scale, ld):
         R, N, _ = src.shape
+        if N == 0:                                        # empty row shard (more ranks than 32-row blocks)
+            return self.zeros((R, 3, ld))
+        if src.dtype not in (torch.float32, torch.float64):
+            src = src.to(torch.float64)                   # the reference converts everything with .astype(float)
+        src = src.contiguous()
         X = self.empty((R, 3, ld))
         fn = "asb_ingest_f32" if src.dtype == torch.float32 else "asb_ingest_f64"
         self._call(fn, self._p(src), self._p(row_scale), self._p(X), R, N, ld)
@@ -132,11 +141,15 @@ class CudaOps:
     def export_aos(self, T, row_scale, N):
         R, _, ld = T.shape
         out = self.empty((R, N, 3))
+        if N == 0:
+            return out
         self._call("asb_export_aos", self._p(T), self._p(row_scale), self._p(out), R, N, ld)
         return out
 
     def pack_bin(self, T, K, N):
         out = self.empty((3, K, N))
+        if N == 0:
+            return out
         self._call("asb_pack_bin", self._p(T), self._p(out), K, N, T.shape[2])
         return out
 
@@ -150,38 +163,67 @@ class CudaOps:
     def center_stats(self, X, mean, N):
         F, _, ld = X.shape
         out = self.empty((2,))
+        if N == 0:
+            return out.zero_()
         self._call("asb_center_stats", self._p(X), self._p(mean), F, N, ld, self._p(out), self._p(self.ws_for(F, 3 * ld)))
         return out
 
     def center_apply(self, X, mean, scale, N):
         F, _, ld = X.shape
+        if N == 0:
+            return
         self._call("asb_center_apply", self._p(X), self._p(mean), float(scale), F, N, ld)
 
     def unstandardize(self, T, mean, scale, N):
         R, _, ld = T.shape
+        if N == 0:
+            return
         self._call("asb_unstandardize", self._p(T), self._p(mean), float(scale), R, N, ld)
 
     # ------------------------------------------------------------------ deflation
     def vertex_energy(self, R, N, out=None):
         F, _, ld = R.shape
         e = self.empty((ld,)) if out is None else out
+        if N == 0:
+            return e.zero_()
         self._call("asb_vertex_energy", self._p(R), self._p(e), F, N, ld, self._p(self.ws_for(F, 3 * ld)))
         return e
 
     def argmax_first(self, v, n, index_offset, out_val, out_idx):
+        if n == 0:                                        # empty shard: never wins a pair reduction
+            out_val.fill_(-float("inf"))
+            out_idx.fill_(torch.iinfo(torch.int64).max)
+            return
         self._call("asb_argmax_first", self._p(v), n, index_offset, self._p(out_val), self._p(out_idx),
                    self._p(self.ws_for(1, n)))
 
     def group_sum(self, v, n, group, out):
+        if n == 0:
+            return
         self._call("asb_group_sum", self._p(v), n, group, self._p(out))
 
     def gather_traj(self, R, N, idx_dev, row0, W, k0, C, npend, traj):
         """W: (F, Kmax) weights, C: (Kmax, 3, ld) components; pending block = columns/rows [k0, k0+npend)."""
         F, _, ld = R.shape
+        if N == 0:
+            return
         Wp = ctypes.c_void_p(W.data_ptr() + 8 * k0) if npend else None
         Cp = ctypes.c_void_p(C.data_ptr() + 8 * k0 * 3 * ld) if npend else None
         self._call("asb_gather_traj", self._p(R), F, N, ld, self._p(idx_dev), row0, Wp, W.shape[1], Cp, npend,
                    self._p(traj))
+
+    def gather_candidate(self, R, N, val, idx, row0, W, k0, C, npend, cand):
+        """This rank's pick packed for one all-gather: cand = [value, index bits, trajectory (3 F)] (asb_gather_candidate)."""
+        F, _, ld = R.shape
+        Wp = ctypes.c_void_p(W.data_ptr() + 8 * k0) if npend else None
+        Cp = ctypes.c_void_p(C.data_ptr() + 8 * k0 * 3 * ld) if npend else None
+        self._call("asb_gather_candidate", self._p(R), F, N, ld, self._p(val), self._p(idx), row0, Wp, W.shape[1], Cp, npend,
+                   self._p(cand))
+
+    def select_candidate(self, cand_all, F, val, idx, traj):
+        """Winner of the gathered candidates (largest value, ties to the lowest global index) and its trajectory."""
+        world, stride = cand_all.shape
+        self._call("asb_select_candidate", self._p(cand_all), world, stride, F, self._p(val), self._p(idx), self._p(traj))
 
     def traj_rank1(self, traj, F, local_support, W, k, k0, coef, scal):
         npend = k - k0
@@ -193,12 +235,18 @@ class CudaOps:
 
     def deflate_gemv(self, R, N, W, k, g):
         F, _, ld = R.shape
+        if N == 0:
+            return
         w = ctypes.c_void_p(W.data_ptr() + 8 * k)
         self._call("asb_deflate_gemv", self._p(R), F, N, ld, w, W.shape[1], self._p(g), self._p(self.ws_for(F, 3 * ld)))
 
     def deflate_finish(self, g, C, k, k0, coef, s, scal, e, N, meas):
         ld = C.shape[2]
         npend = k - k0
+        if N == 0:                                        # C[k] stays zero; sigma0 is replicated, the norm partial is 0
+            meas.zero_()
+            meas[0:1].copy_(scal[0:1])
+            return
         Cp = ctypes.c_void_p(C.data_ptr() + 8 * k0 * 3 * ld) if npend else None
         cout = ctypes.c_void_p(C.data_ptr() + 8 * k * 3 * ld)
         self._call("asb_deflate_finish", self._p(g), Cp, npend, self._p(coef) if npend else None, self._p(s), self._p(scal),
@@ -206,6 +254,8 @@ class CudaOps:
 
     def rank_update(self, R, N, W, C, k0, nb, e):
         F, _, ld = R.shape
+        if N == 0:
+            return
         Wb = ctypes.c_void_p(W.data_ptr() + 8 * k0)
         Cb = ctypes.c_void_p(C.data_ptr() + 8 * k0 * 3 * ld)
         self._call("asb_rank_update", self._p(R), F, N, ld, Wb, W.shape[1], Cb, nb, self._p(e),
@@ -236,6 +286,8 @@ class CudaOps:
         """`iters` fused ADMM iterations in one launch (Z, U in place).  The kernel wants Hr zero-padded to
         ceil16(K) x ceil16(K); a tensor that is not (tests, ad-hoc callers) is copied into a padded one here."""
         ld = Z.shape[2]
+        if N == 0:
+            return
         k8 = (K + 15) // 16 * 16
         if Hr.shape[0] < k8 or Hr.stride(0) < k8:
             Hp = self.zeros((k8, k8))
@@ -262,6 +314,12 @@ class CudaOps:
 
     def component_centers(self, C, Lambda, K, N, index_offset, val, idx, sp):
         ld = C.shape[2]
+        if N == 0:
+            val.fill_(-float("inf"))
+            idx.fill_(torch.iinfo(torch.int64).max)
+            if Lambda is not None:
+                sp.zero_()
+            return
         self._call("asb_component_centers", self._p(C), self._p(Lambda), K, N, ld, index_offset, self._p(val), self._p(idx),
                    self._p(sp), self._p(self.workspace(8 * (64 * K * 3 + 1024))))
 
@@ -277,9 +335,15 @@ class CudaOps:
         return w, info
 
     def cgs_dots(self, T, k, d, N, h):
+        if N == 0:
+            h[:k].zero_()
+            return
         self._call("asb_cgs_dots", self._p(T), k, d, N, T.shape[2], self._p(h), self._p(self.workspace(8 * (2 * self.sm_count * max(k, 1) + 1024))))
 
     def cgs_project(self, T, k, d, N, h, nrm2):
+        if N == 0:
+            nrm2.zero_()
+            return
         self._call("asb_cgs_project", self._p(T), k, d, N, T.shape[2], self._p(h), self._p(nrm2), self._p(self.workspace(8 * (T.shape[2] // 256 + 1024))))
 
     def row_scale(self, T, k, d, nrm2):
@@ -296,6 +360,11 @@ class CudaOps:
         """The per-CTA max|r| partials live in `ws` and, with `accumulate`, are carried from one target of a block to the
         next: they get a buffer of their own -- the shared scratch is rewritten by asb_deim_solve between the targets (on a
         B200 that turned max|r| of a block into garbage, so a vanishing block residual went unnoticed)."""
+        if N == 0:
+            if not accumulate:
+                e.zero_()
+                maxabs.zero_()
+            return
         need = (int(C.shape[2]) + 255) // 256 + 8
         buf = getattr(self, "_deim_pmax", None)
         if buf is None or buf.numel() < need:
@@ -308,6 +377,10 @@ class CudaOps:
         self._call("asb_deim_solve", self._p(Vp), Vp.shape[1], k, self._p(a), a.stride(0), self._p(ws), self._p(info))
 
     def deim_residual(self, C, N, k, a, e, maxabs):
+        if N == 0:
+            e.zero_()
+            maxabs.zero_()
+            return
         self._call("asb_deim_residual", self._p(C), C.shape[2], N, k, self._p(a), a.stride(0), self._p(e), self._p(maxabs),
                    self._p(self.ws_for(1, C.shape[2])))
 
@@ -371,6 +444,8 @@ class CudaOps:
 
     def support_map(self, phi, n, dmin, dmax, mode, lam, row0, nloc, out):
         nrhs, ldx = phi.shape
+        if nloc == 0:
+            return
         self._call("asb_support_map", self._p(phi), n, nrhs, ldx, float(dmin), float(dmax), int(mode), float(lam), row0, nloc,
                    self._p(out), out.stride(0), self._p(self.workspace(8 * (66 * nrhs + 1024))))
 

@@ -91,6 +91,17 @@ int asb_argmax_first(const double* v, int64_t n, int64_t index_offset, double* o
 int asb_gather_traj(const double* R, int64_t F, int64_t N, int64_t ld, const int64_t* idx_dev, int64_t row0,
                     const double* Wp, int64_t ldw, const double* Cp, int64_t npend, double* traj,
                     asb_stream_t stream);
+/* Row-sharded pick of the deflation vertex with ONE collective ("(value,index) allgather+reduce, bcast w").
+ * asb_gather_candidate packs this rank's local argmax for an all-gather:  cand[0] = *val_dev, cand[1] = bit pattern of the
+ * int64 global index *idx_dev, cand[2 + d*F + f] = the trajectory asb_gather_traj would return for it; a rank whose index
+ * is outside [row0, row0 + N) (empty shard) sends (-inf, INT64_MAX, zeros).  After the all-gather of the `world` records
+ * (`stride` doubles apart), asb_select_candidate picks the largest value, ties to the lowest global index (np.argmax,
+ * snapbases/posComponents.py:79), and copies the winner's trajectory: out_val[0], out_idx[0], traj[3][F]. */
+int asb_gather_candidate(const double* R, int64_t F, int64_t N, int64_t ld, const double* val_dev, const int64_t* idx_dev,
+                         int64_t row0, const double* Wp, int64_t ldw, const double* Cp, int64_t npend, double* cand,
+                         asb_stream_t stream);
+int asb_select_candidate(const double* all, int64_t world, int64_t stride, int64_t F, double* out_val, int64_t* out_idx,
+                         double* traj, asb_stream_t stream);
 /* Rank-1 SVD of the 3 x F trajectory in closed form (3x3 Gram -> Jacobi eigen):  w = sigma0 * Vt[0]
  * (:83-85); if local_support: w = project_weight(+-w) with the larger 2-norm (:90-94, :52-58).
  * Writes w to wout[f*ldw] (a column of the F x K weight matrix), scal[0]=sigma0, scal[1]=w.w,

@@ -27,7 +27,7 @@ class NumpyOps:
         self.launches = 0
 
     # plumbing -------------------------------------------------------------------------------------
-    def fork(self):
+    def fork(self, after=None):
         import contextlib
         return contextlib.nullcontext()
 
@@ -102,6 +102,10 @@ class NumpyOps:
         return e
 
     def argmax_first(self, v, n, index_offset, out_val, out_idx):
+        if n == 0:
+            out_val[0] = -np.inf
+            out_idx[0] = np.iinfo(np.int64).max
+            return
         a = v.numpy()[:n]
         i = int(np.argmax(a))
         out_val[0] = float(a[i])
@@ -118,6 +122,32 @@ class NumpyOps:
         for j in range(npend):
             t -= np.outer(C.numpy()[k0 + j, :, i], W.numpy()[:, k0 + j])
         traj.numpy()[:] = t
+
+    def gather_candidate(self, R, N, val, idx, row0, W, k0, C, npend, cand):
+        F = R.shape[0]
+        i = int(idx[0]) - row0
+        c = cand.numpy()
+        if i < 0 or i >= N:
+            c[0] = -np.inf
+            c[1:2].view(np.int64)[0] = np.iinfo(np.int64).max
+            c[2:2 + 3 * F] = 0.0
+            return
+        c[0] = float(val[0])
+        c[1:2].view(np.int64)[0] = int(idx[0])
+        t = torch.zeros((3, F), dtype=F64)
+        self.gather_traj(R, N, idx, row0, W, k0, C, npend, t)
+        c[2:2 + 3 * F] = t.numpy().ravel()
+
+    def select_candidate(self, cand_all, F, val, idx, traj):
+        a = cand_all.numpy()
+        best, bi, bw = -np.inf, np.iinfo(np.int64).max, 0
+        for r in range(a.shape[0]):
+            v, i = float(a[r, 0]), int(a[r, 1:2].view(np.int64)[0])
+            if v > best or (v == best and i < bi):
+                best, bi, bw = v, i, r
+        val[0] = best
+        idx[0] = bi
+        traj.numpy()[:] = a[bw, 2:2 + 3 * F].reshape(3, F)
 
     def traj_rank1(self, traj, F, local_support, W, k, k0, coef, scal):
         T = traj.numpy()
@@ -235,6 +265,12 @@ class NumpyOps:
             w[:F, k] = x
 
     def component_centers(self, C, Lambda, K, N, index_offset, val, idx, sp):
+        if N == 0:
+            val.numpy()[:K] = -np.inf
+            idx.numpy()[:K] = np.iinfo(np.int64).max
+            if Lambda is not None:
+                sp.numpy()[:K] = 0.0
+            return
         c = C.numpy()[:K, :, :N]
         v = (c[:, 0] ** 2 + c[:, 1] ** 2) + c[:, 2] ** 2
         ii = np.argmax(v, axis=1)

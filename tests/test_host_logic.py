@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 import torch
 
-from conftest import ROOT
+from conftest import GOLDEN, ROOT
 from numpy_ops import NumpyOps
 import pipeline_checks
 from animsnapbases_b200 import _lib, engine
@@ -459,3 +459,27 @@ def test_tet_grid_generator():
     faces = np.sort(np.concatenate([t[:, [0, 1, 2]], t[:, [0, 1, 3]], t[:, [0, 2, 3]], t[:, [1, 2, 3]]]), axis=1)
     _, counts = np.unique(faces, axis=0, return_counts=True)
     assert set(counts) == {1, 2}, "every interior face is shared by exactly two tets"
+
+
+# ---- BASELINE configs at their own sizes (tests/golden/scale_*.npz): host logic of the checks over the numpy statement
+def test_scale_inputs_are_reproducible():
+    """configs.build_inputs regenerates, bit for bit, the inputs the at-scale fixtures were computed on (IEEE-only arithmetic)."""
+    from animsnapbases_b200 import configs
+    for name in ("bunny_splocs", "bar_deim", "armadillo_splocs"):
+        f = os.path.join(GOLDEN, f"scale_{name}.npz")
+        if os.path.exists(f):
+            assert configs.build_inputs(name)["digest"] == str(np.load(f)["digest"]), name
+
+
+def test_scale_bar_end_to_end_numpy():
+    """Full bar (3 120 tets, F = 70, K = 70): multi-pass Gram POD resolves sigma_1 / sigma_69 = 1e8, DEIM end to end."""
+    import pipeline_checks
+    rep = {}
+    assert pipeline_checks.check_scale_bar(NumpyOps(), engine.Comm(enabled=False), rep)
+    assert rep["sigma"] < 1e-10 and rep["modes"] < 1e-8
+
+
+def test_scale_bunny_prefix_numpy():
+    """First components of the bunny F = 200 fixture (the deflation prefix does not depend on K)."""
+    import pipeline_checks
+    assert pipeline_checks.check_scale_pos(NumpyOps(), engine.Comm(enabled=False), "bunny_splocs", K=6)

@@ -9,8 +9,6 @@ from animsnapbases_b200 import engine
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.xfail(strict=False, reason="added when the r01 GPU budget was spent: green over the numpy statement of the kernels with "
-                                        "margins of 1e-13 against tolerances of 1e-7 .. 1e-8, not yet run on a B200")
 @pytest.mark.parametrize("mesh,F,K,splocs,seed", [("bunny", 40, 12, (2, 5, 2.0, 10.0), 2),
                                                   ("armadillo", 60, 24, (2, 10, 2.0, 10.0), 4)])
 def test_real_mesh_against_live_oracle(cuda_ops, mesh, F, K, splocs, seed):
@@ -42,15 +40,10 @@ def test_pos_protocol_with_figure_tables(cuda_ops, tmp_path):
     assert api_checks.check_pos_protocol(cuda_ops, engine.Comm(enabled=False), tmp_path, extended=True)
 
 
-@pytest.mark.xfail(strict=False, reason="the last GPU seconds of r01 ran this check: plain DEIM behaved, the block variant did not "
-                                        "(its max|r| partials shared scratch with asb_deim_solve, profiles/r01_late_gpu_tests2.log); "
-                                        "fixed host-side in ops.deim_residual_block afterwards, the fix has not run on a B200 yet")
 def test_zero_residual(cuda_ops):
     """Vanishing DEIM residual: print + no result, like the reference, in all three selections."""
     assert pipeline_checks.check_zero_residual(cuda_ops, engine.Comm(enabled=False))
 
 
-@pytest.mark.xfail(strict=False, reason="asb_pd_project was written after the last GPU session of r01: its arithmetic is checked on "
-                                        "the host (test_pd_math_on_host), the kernel itself has not run on a B200 yet")
 def test_pd_local_snapshot_producer(cuda_ops, tmp_path):
     assert pipeline_checks.check_pd_local(cuda_ops, engine.Comm(enabled=False), tmp_path)
