@@ -29,7 +29,12 @@ __device__ __forceinline__ double gather_children(const int32_t* __restrict__ sr
     return f;
 }
 
-// grid.x = work item (front, first row), grid.y = right-hand side.  256 threads = 8 warps x 4 rows.
+// grid.x = work item (front, first row), grid.y = right-hand side.  RPW rows per warp: 256 threads = 8 warps x 4 rows for the
+// wide levels (thousands of CTAs, bandwidth bound), 1024 threads = 32 warps x 1 row for the top of the tree, where a level has
+// fewer CTAs than the machine has SMs and the pass is bound by the latency of one CTA (r01: 15 of the 30 launches of a
+// single-source solve ran 32..128 CTAs for 20-30 us each).  The rows of a warp advance together, so their loads are in
+// flight at the same time.
+template <int RPW>
 __device__ __forceinline__ void mf_forward_block(const FrontDesc& d, const int r0, const int64_t b, double* fs,
                                                  const double* __restrict__ vals, const int32_t* __restrict__ src,
                                                  int64_t slots, const double* __restrict__ rhs, double* __restrict__ y,
@@ -40,15 +45,17 @@ __device__ __forceinline__ void mf_forward_block(const FrontDesc& d, const int r
     const int32_t* src1 = src + slots + d.slot_off;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n1 = (int)d.n1, n = (int)(d.n1 + d.n2);
-    double acc[4] = {0.0, 0.0, 0.0, 0.0};
-    const double* rowp[4];
-    int jmax[4];
+    double acc[RPW];
+    const double* rowp[RPW];
+    int jmax[RPW], jall = 0;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int r = r0 + warp * 4 + i;
+    for (int i = 0; i < RPW; ++i) {
+        const int r = r0 + warp * RPW + i;
         const long long srow = r < n1 ? r : d.row2 + (r - n1);
-        rowp[i] = vals + d.mt_off + srow * d.ldm;
+        rowp[i] = vals + d.mt_off + (r < n ? srow : 0) * d.ldm;
         jmax[i] = r >= n ? 0 : (r < n1 ? r + 1 : n1);   // L11^-1 is lower triangular
+        jall = max(jall, jmax[i]);
+        acc[i] = 0.0;
     }
     // columns needed by this CTA: own rows only reach column r0 + MF_ROWS - 1
     const int cmax = (r0 + MF_ROWS <= n1) ? r0 + MF_ROWS : n1;
@@ -57,19 +64,21 @@ __device__ __forceinline__ void mf_forward_block(const FrontDesc& d, const int r
         __syncthreads();
         for (int j = threadIdx.x; j < len; j += blockDim.x) fs[j] = rb[c0 + j] + gather_children(src0, src1, ub, c0 + j);
         __syncthreads();
+        const int je = min(len, jall - c0);
+#pragma unroll 2
+        for (int j = lane; j < je; j += 32) {
+            const double f = fs[j];
+            double a[RPW];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int je = min(len, jmax[i] - c0);
-            const double* p = rowp[i] + c0;
-            double a = acc[i];
-            for (int j = lane; j < je; j += 32) a = fma(p[j], fs[j], a);
-            acc[i] = a;
+            for (int i = 0; i < RPW; ++i) a[i] = (c0 + j < jmax[i]) ? rowp[i][c0 + j] : 0.0;
+#pragma unroll
+            for (int i = 0; i < RPW; ++i) acc[i] = fma(a[i], f, acc[i]);
         }
     }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < RPW; ++i) {
         const double s = warp_sum(acc[i]);
-        const int r = r0 + warp * 4 + i;
+        const int r = r0 + warp * RPW + i;
         if (lane == 0 && r < n) {
             if (r < n1)
                 y[b * ldx + d.own_start + r] = s;
@@ -79,21 +88,22 @@ __device__ __forceinline__ void mf_forward_block(const FrontDesc& d, const int r
     }
 }
 
-__global__ void __launch_bounds__(256) mf_forward_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
-                                                        const int32_t* __restrict__ src, int64_t slots,
-                                                        const int32_t* __restrict__ work, const double* __restrict__ rhs,
-                                                        double* __restrict__ y, double* __restrict__ upd, int64_t ldx,
-                                                        int64_t ldu) {
+template <int RPW>
+__global__ void __launch_bounds__(1024 / RPW) mf_forward_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
+                                                               const int32_t* __restrict__ src, int64_t slots,
+                                                               const int32_t* __restrict__ work, const double* __restrict__ rhs,
+                                                               double* __restrict__ y, double* __restrict__ upd, int64_t ldx,
+                                                               int64_t ldu) {
     __shared__ double fs[MF_CHUNK];
     const FrontDesc d = desc[work[2 * blockIdx.x]];
-    mf_forward_block(d, work[2 * blockIdx.x + 1], blockIdx.y, fs, vals, src, slots, rhs, y, upd, ldx, ldu);
+    mf_forward_block<RPW>(d, work[2 * blockIdx.x + 1], blockIdx.y, fs, vals, src, slots, rhs, y, upd, ldx, ldu);
 }
 
 // Forward pass of a DELTA right-hand side: only the fronts on the path from the source's front to the root see a
 // non-zero vector (everything else of y and upd stays at its memset zero), so a level is at most one front per
 // right-hand side.  pathfront[b][level] = that front or -1 (mf_path_kernel); grid.x = row blocks of the largest front of
 // the level, grid.y = right-hand side.
-__global__ void __launch_bounds__(256) mf_forward_path_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
+__global__ void __launch_bounds__(1024) mf_forward_path_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
                                                              const int32_t* __restrict__ src, int64_t slots,
                                                              const int32_t* __restrict__ pathfront, int level, int nlevels,
                                                              const double* __restrict__ rhs, double* __restrict__ y,
@@ -104,7 +114,7 @@ __global__ void __launch_bounds__(256) mf_forward_path_kernel(const FrontDesc* _
     const FrontDesc d = desc[f];
     const int r0 = blockIdx.x * MF_ROWS;
     if (r0 >= d.n1 + d.n2) return;
-    mf_forward_block(d, r0, blockIdx.y, fs, vals, src, slots, rhs, y, upd, ldx, ldu);
+    mf_forward_block<1>(d, r0, blockIdx.y, fs, vals, src, slots, rhs, y, upd, ldx, ldu);
 }
 
 // One thread per right-hand side: unit entry at the source's elimination position, and the chain of fronts above it.
@@ -124,12 +134,14 @@ __global__ void mf_path_kernel(const int64_t* __restrict__ idx, const int32_t* _
     for (int f = (int)lo; f >= 0; f = parent[f]) pathfront[(int64_t)b * nlevels + depth[f]] = f;
 }
 
-// grid.x = work item (front, first column), grid.y = right-hand side.  256 threads = 32 columns x 8 row groups.
-__global__ void __launch_bounds__(256) mf_backward_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
-                                                         const int32_t* __restrict__ bnd, const int32_t* __restrict__ work,
-                                                         const double* __restrict__ y, double* __restrict__ x, int64_t ldx) {
+// grid.x = work item (front, first column), grid.y = right-hand side.  32 columns x RG row groups: RG = 8 (256 threads) for
+// the wide levels, RG = 32 (1024 threads) for the top of the tree (see mf_forward_block).
+template <int RG>
+__global__ void __launch_bounds__(32 * RG) mf_backward_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
+                                                             const int32_t* __restrict__ bnd, const int32_t* __restrict__ work,
+                                                             const double* __restrict__ y, double* __restrict__ x, int64_t ldx) {
     __shared__ double vs[MF_CHUNK];
-    __shared__ double red[8][33];
+    __shared__ double red[RG][33];
     const FrontDesc d = desc[work[2 * blockIdx.x]];
     const int c0 = work[2 * blockIdx.x + 1];
     const int64_t b = blockIdx.y;
@@ -152,9 +164,9 @@ __global__ void __launch_bounds__(256) mf_backward_kernel(const FrontDesc* __res
         __syncthreads();
         if (col < n1) {
             // rows r < col of the own block hold stored zeros (L11^-1 is lower triangular): no skip test, so that the
-            // strided loads of four rows are in flight together (the top fronts have 32..128 CTAs: latency, not bandwidth)
+            // strided loads of four rows are in flight together
 #pragma unroll 4
-            for (int j = ty; j < len; j += 8) {
+            for (int j = ty; j < len; j += RG) {
                 const int r = rb0 + j;
                 const long long srow = r < n1 ? r : d.row2 + (r - n1);
                 acc = fma(mp[srow * d.ldm], vs[j], acc);
@@ -166,7 +178,7 @@ __global__ void __launch_bounds__(256) mf_backward_kernel(const FrontDesc* __res
     if (ty == 0 && col < n1) {
         double s = red[0][tx];
 #pragma unroll
-        for (int k = 1; k < 8; ++k) s += red[k][tx];
+        for (int k = 1; k < RG; ++k) s += red[k][tx];
         xb[d.own_start + col] = s;
     }
 }
@@ -486,6 +498,15 @@ __global__ void gather_rows_kernel(const double* __restrict__ in, const int32_t*
 
 using namespace asb;
 
+// ASB_MF_TALL=0 keeps the 256-thread kernels on every level (A/B switch for profiles/)
+static bool mf_tall() {
+    static const int v = [] {
+        const char* e = std::getenv("ASB_MF_TALL");
+        return e ? std::atoi(e) : 1;
+    }();
+    return v != 0;
+}
+
 extern "C" {
 
 int asb_mf_forward(const int64_t* desc, const double* vals, const int32_t* src, int64_t slots, const int32_t* work,
@@ -502,8 +523,11 @@ int asb_mf_forward(const int64_t* desc, const double* vals, const int32_t* src, 
     else if (nrhs >= MF_MRHS_MIN)
         mf_forward_mrhs_kernel<<<dim3((unsigned)nwork, (unsigned)cdiv(nrhs, MF_NB)), 256, 0, S(stream)>>>(
             reinterpret_cast<const FrontDesc*>(desc), vals, src, slots, work, rhs, y, upd, ldx, ldu, (int)nrhs);
+    else if (nwork * nrhs <= 2LL * sm_count() && mf_tall())
+        mf_forward_kernel<1><<<dim3((unsigned)nwork, (unsigned)nrhs), 1024, 0, S(stream)>>>(
+            reinterpret_cast<const FrontDesc*>(desc), vals, src, slots, work, rhs, y, upd, ldx, ldu);
     else
-        mf_forward_kernel<<<dim3((unsigned)nwork, (unsigned)nrhs), 256, 0, S(stream)>>>(
+        mf_forward_kernel<4><<<dim3((unsigned)nwork, (unsigned)nrhs), 256, 0, S(stream)>>>(
             reinterpret_cast<const FrontDesc*>(desc), vals, src, slots, work, rhs, y, upd, ldx, ldu);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
@@ -522,8 +546,11 @@ int asb_mf_backward(const int64_t* desc, const double* vals, const int32_t* bnd,
     else if (nrhs >= MF_MRHS_MIN)
         mf_backward_mrhs_kernel<<<dim3((unsigned)nwork, (unsigned)cdiv(nrhs, MF_NB)), 256, 0, S(stream)>>>(
             reinterpret_cast<const FrontDesc*>(desc), vals, bnd, work, y, x, ldx, (int)nrhs);
+    else if (nwork * nrhs <= 2LL * sm_count() && mf_tall())
+        mf_backward_kernel<32><<<dim3((unsigned)nwork, (unsigned)nrhs), 1024, 0, S(stream)>>>(
+            reinterpret_cast<const FrontDesc*>(desc), vals, bnd, work, y, x, ldx);
     else
-        mf_backward_kernel<<<dim3((unsigned)nwork, (unsigned)nrhs), 256, 0, S(stream)>>>(
+        mf_backward_kernel<8><<<dim3((unsigned)nwork, (unsigned)nrhs), 256, 0, S(stream)>>>(
             reinterpret_cast<const FrontDesc*>(desc), vals, bnd, work, y, x, ldx);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
@@ -563,7 +590,7 @@ int asb_mf_solve_delta(const int64_t* desc, const double* vals, const int32_t* s
                                                            pathfront, rp, ldx);
     ASB_LAUNCH_CHECK();
     for (int64_t l = nlevels - 1; l >= 0; --l) {
-        mf_forward_path_kernel<<<dim3((unsigned)maxblk[l], (unsigned)nrhs), 256, 0, st>>>(
+        mf_forward_path_kernel<<<dim3((unsigned)maxblk[l], (unsigned)nrhs), 1024, 0, st>>>(
             reinterpret_cast<const FrontDesc*>(desc), vals, src, slots, pathfront, (int)l, (int)nlevels, rp, y, upd, ldx, ldu);
         ASB_LAUNCH_CHECK();
     }

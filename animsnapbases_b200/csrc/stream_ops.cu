@@ -369,6 +369,7 @@ int asb_version(void) { return 100; }
 const char* asb_last_error(void) { return g_err; }
 int64_t asb_launch_count(void) { return (int64_t)g_launches.load(); }
 void asb_reset_launch_count(void) { g_launches.store(0); }
+void asb_add_launch_count(int64_t n) { g_launches.fetch_add((long long)n, std::memory_order_relaxed); }
 
 int asb_device_info(int* sms, int* major, int* minor) {
     int dev = 0;

@@ -206,11 +206,15 @@ def deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1
         pick(R, N, val, idx, row0, W, k0, C, k - k0, traj)
         picked[k:k + 1].copy_(idx)
         ops.traj_rank1(traj, F, local_support, W, k, k0, coef, scal)
-        if local_support:
-            with ops.fork():      # the heat-method query (60 small launches, latency bound) runs beside the HBM-bound pass
-                geodesic.support(idx, 0, 1.0, dmin, dmax, row0, N, s)
+        picked_ev = ops.record_event() if local_support else None
         ops.deflate_gemv(R, N, W, k, g)
-        ops.join()
+        if local_support:
+            # the heat-method query of the picked vertex (single source, latency bound, replicated on every rank) runs on the
+            # side stream beside the HBM-bound pass.  It is queued AFTER the pass (r01 queued its ~75 launches first: 2 ms of
+            # host time per component during which the main stream sat idle) and as ONE CUDA-graph launch.
+            with ops.fork(after=picked_ev):
+                geodesic.support_single(idx, 0, 1.0, dmin, dmax, row0, N, s)
+            ops.join()
         ops.deflate_finish(g, C, k, k0, coef, s[0] if local_support else None, scal, e, N, meas[k])
         if k - k0 + 1 == block or k == K - 1:
             ops.rank_update(R, N, W, C, k0, k - k0 + 1, e)
@@ -986,7 +990,7 @@ def host_rows(ops, comm, T, shard, row_scale=None):
     """Planar (R, 3, ld) row-sharded device tensor -> the reference's host layout (R, n_global, 3), complete on every rank
     (the attribute views `comps`, `snapTensor`, `mean` of the drop-in classes: scripts written against the reference index
     them by global row).  Lazy and only for outputs; nothing on the build path calls it."""
-    out = ops.export_aos(T, row_scale, shard.n).cpu().numpy()
+    out = ops.to_host(ops.export_aos(T, row_scale, shard.n))
     return gather_rows_host(comm, out, shard, axis=1) if comm.world > 1 else out
 
 

@@ -110,7 +110,28 @@ class HeatGeodesics:
                       "levels": self.heat.stats["levels"],
                       "operator_bytes": self.heat.stats["operator_bytes"] + self.pois.stats["operator_bytes"]}
         self._cache = {}
+        self._graphs = {}            # captured single-source queries (support_single); None = capture failed, stay eager
         self.cache_rows = 4          # memoised maps kept per request size: at most cache_rows * B rows per key (LRU)
+
+    _instances = {}              # (device, digest of mesh, leaf size) -> HeatGeodesics: the factorisation depends on the mesh only
+
+    @classmethod
+    def cached(cls, ops, verts, tris, leaf_size: int = 64, keep: int = 2):
+        """The geodesic set-up of a mesh (ordering, symbolic and numeric multifrontal factorisation: ~10 s and 1.9 GB at 1M
+        vertices) built once and shared by every snapshot object on the same rest mesh -- the reference redoes its two
+        `splu` factorisations in every posSnapshots constructor (snapbases/posSnapshots.py:97-99)."""
+        import hashlib
+        v = np.ascontiguousarray(verts, dtype=np.float64)
+        t = np.ascontiguousarray(tris, dtype=np.int64)
+        key = (str(getattr(ops, "device", "")), id(ops), hashlib.sha1(v.tobytes() + t.tobytes()).hexdigest(), int(leaf_size))
+        geo = cls._instances.get(key)
+        if geo is None:
+            while len(cls._instances) >= keep:
+                cls._instances.pop(next(iter(cls._instances)))
+            geo = cls._instances[key] = cls(ops, v, t, leaf_size=leaf_size)
+        else:
+            geo.reset()
+        return geo
 
     def reset(self):
         """Drop the memoised support maps (a new basis build starts cold)."""
@@ -128,6 +149,50 @@ class HeatGeodesics:
             cache.popitem(last=False)
 
     # ------------------------------------------------------------------ queries
+    def support_single(self, idx_dev, mode, lam, dmin, dmax, row0, nloc, out):
+        """`support` for ONE source vertex, replayed from a CUDA graph: the ~75 launches of a single-source query (memsets,
+        tree-path forward pass, one launch per level and direction of two triangular solves, divergence, support map) are
+        captured once per (mode, shard) with buffers the graph owns and cost one launch on the host afterwards.  The 200
+        deflation queries are sequential and latency bound; on 8 GPUs the host time to issue them (2 ms each) was longer than
+        the sharded HBM pass they hide behind (0.9 ms).  out: (1, ld) device tensor; idx_dev: (1,) int64 device tensor."""
+        ops = self.ops
+        if getattr(ops, "name", "") != "cuda" or self._graphs is None:
+            return self.support(idx_dev, mode, lam, dmin, dmax, row0, nloc, out)
+        import torch
+        key = (int(mode), float(lam), float(dmin), float(dmax), int(row0), int(nloc), int(out.shape[1]))
+        ent = self._graphs.get(key)
+        if ent is None:
+            try:
+                sidx = ops.zeros((1,), torch.int64)
+                sout = ops.zeros((1, out.shape[1]))
+                sidx.copy_(idx_dev)
+                self.support(sidx, mode, lam, dmin, dmax, row0, nloc, sout)        # eager warm-up (workspaces, attributes)
+                torch.cuda.current_stream(ops.device).synchronize()
+                n0 = ops.launch_count()
+                graph = torch.cuda.CUDAGraph()
+                timers, ops.timers = ops.timers, None                               # no per-launch timing events inside a capture
+                try:
+                    with torch.cuda.graph(graph):
+                        self.support(sidx, mode, lam, dmin, dmax, row0, nloc, sout)
+                finally:
+                    ops.timers = timers
+                ent = self._graphs[key] = (graph, sidx, sout, ops.launch_count() - n0)
+                self.stats["queries"] -= 2                                          # warm-up + capture are not queries
+                self.stats["solves"] -= 2
+            except Exception as e:                                                  # noqa: BLE001 -- eager launches still work
+                print("[animsnapbases_b200] CUDA-graph capture of the single-source geodesic query failed (%s); "
+                      "queries stay eager" % (e,))
+                self._graphs = None
+                return self.support(idx_dev, mode, lam, dmin, dmax, row0, nloc, out)
+        graph, sidx, sout, nodes = ent
+        sidx.copy_(idx_dev)
+        graph.replay()
+        out.copy_(sout)
+        ops.add_launch_count(nodes)
+        self.stats["queries"] += 1
+        self.stats["solves"] += 1
+        return out
+
     def distances(self, idx_dev):
         """phi (B, ldx) for the B source vertices in idx_dev (int64 device tensor); phi is NOT yet shifted by its
         minimum (asb_support_map does that, utils/support.py:206)."""

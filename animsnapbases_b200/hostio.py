@@ -119,8 +119,49 @@ def _npz_sidecar(path):
     return path if path.endswith(".npz") else os.path.splitext(path)[0] + ".npz"
 
 
+class MemoryAnimation:
+    """An animation handed over in host memory instead of a file (registered under a path with `register_animation`, so the
+    reference's config object keeps naming its snapshot 'files' as before).  `verts`: (F, n_local, 3) float32 / float64, a
+    numpy array or a (pinned) torch tensor holding the rows [row0, row0 + n_local) of the N-vertex animation -- a rank of a
+    row-sharded run registers only its shard; `rest`: the complete frame 0 (N, 3), which the geodesic set-up needs on every
+    rank; `tris` (T, 3)."""
+
+    def __init__(self, verts, tris, rest=None, row0=0, n_global=None):
+        self.verts, self.tris, self.row0 = verts, np.asarray(tris), int(row0)
+        self.frames, self.n_local = int(verts.shape[0]), int(verts.shape[1])
+        self.n_global = self.n_local if n_global is None else int(n_global)
+        self.rest = np.asarray(verts[0], dtype=np.float64) if rest is None else np.asarray(rest, dtype=np.float64)
+        assert self.rest.shape == (self.n_global, 3), "rest must be the complete frame 0"
+        self.shape = (self.frames, self.n_global, 3)
+
+    def rows(self, row0, n):
+        """The stored rows [row0, row0 + n) -- must lie inside what this rank registered."""
+        a = row0 - self.row0
+        assert 0 <= a and a + n <= self.n_local, "this rank did not register the rows of its shard"
+        return self.verts[:, a:a + n]
+
+    def complete(self):
+        assert self.n_local == self.n_global, "only a shard of the animation is in this rank's memory"
+        v = self.verts
+        return v.numpy() if hasattr(v, "numpy") else np.asarray(v)
+
+
+_MEMORY = {}
+
+
+def register_animation(path, animation):
+    """Make `read_animation(path)` return the MemoryAnimation (None removes the entry)."""
+    if animation is None:
+        _MEMORY.pop(path, None)
+    else:
+        _MEMORY[path] = animation
+
+
 def read_animation(path):
-    """-> (verts (F, N, 3) in the stored dtype, tris) from `<path>` (.h5 with h5py) or its `.npz` twin."""
+    """-> (verts (F, N, 3) in the stored dtype, tris) from `<path>` (.h5 with h5py) or its `.npz` twin; a path registered
+    with `register_animation` yields its MemoryAnimation instead of an array."""
+    if path in _MEMORY:
+        return _MEMORY[path], _MEMORY[path].tris
     h5 = _h5py()
     if h5 is not None and os.path.exists(path) and not path.endswith(".npz"):
         with h5.File(path, "r") as f:

@@ -88,6 +88,13 @@ class CudaOps:
             t = t.to(dtype)
         return t.to(self.device, non_blocking=True).contiguous()
 
+    def to_host(self, t):
+        """Device tensor -> host numpy array through pinned memory (asynchronous copy + stream synchronise)."""
+        h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+        h.copy_(t, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return h.numpy()
+
     def workspace(self, nbytes: int):
         """Scratch for the reductions of the CURRENT stream (one buffer per stream: the geodesic solves run on a side
         stream next to the streaming / DMMA kernels of the main one)."""
@@ -109,6 +116,12 @@ class CudaOps:
             self._side.wait_stream(torch.cuda.current_stream(self.device))
         return torch.cuda.stream(self._side)
 
+    def record_event(self):
+        """A CUDA event recorded on the current stream (ordering handle for `fork(after=...)`)."""
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        return ev
+
     def join(self):
         if self._side is not None:
             torch.cuda.current_stream(self.device).wait_stream(self._side)
@@ -121,6 +134,10 @@ class CudaOps:
 
     def reset_launch_count(self):
         self.lib.asb_reset_launch_count()
+
+    def add_launch_count(self, n: int):
+        """Kernel nodes of a replayed CUDA graph (captured launches are counted once, at capture time)."""
+        self.lib.asb_add_launch_count(int(n))
 
     def synchronize(self):
         torch.cuda.synchronize(self.device)

@@ -69,6 +69,14 @@ class posComponents:  # Components == bases
     def splocs_weigs(self):
         return None if self._Ws is None else self._Ws.cpu().numpy()[:, :self.numComp]
 
+    def local_components_host(self, splocs=False):
+        """This rank's row shard of `comps` (or of the SPLOCS-optimised components) as a host array (K, n_local, 3), through
+        pinned memory.  `comps` itself is complete on every rank (an all-gather of host objects when the rows are sharded),
+        which is a convenience for scripts written against the reference, not something a sharded pipeline wants to pay."""
+        ops, _ = runtime.get()
+        T = self._Cs if splocs else self._C
+        return None if T is None else ops.to_host(ops.export_aos(T, None, self.pos_snapshots.shard.n))
+
     # ------------------------------------------------------------------ small host statics (API parity)
     @staticmethod
     def project_weight(x):
@@ -105,6 +113,7 @@ class posComponents:  # Components == bases
     def extract_k_components(self, writer, num_iters_max=20, num_admm_iterations=10):
         ops, comm = runtime.get()
         snaps = self.pos_snapshots
+        snaps._geo.reset()                    # memoised support maps belong to one build (bounded: geodesic.cache_rows)
         local = self.support == 'local'
         block = int(getattr(self.param, "engine_deflation_block", 8))
         keep_r = False

@@ -22,8 +22,10 @@ class posSnapshots:
         self.input_animation_file = input_train_animation_file
         self.input_test_animation_file = input_test_animation_file
         self.rest_shape = rest_shape
-        self.verts = None
-        self.test_verts = None
+        self._stored_verts = None
+        self._stored_test = None
+        self._verts64 = None
+        self._test64 = None
         self.tris = None
         self.test_tris = None
         self.frs = 0
@@ -39,6 +41,26 @@ class posSnapshots:
         self.shard = None
         self._geo = None
         self.do_snapshots_precomputations(standarize, massWeight)
+
+    # ---- the reference keeps float64 host copies of both animations (`verts`, `test_verts`, posSnapshots.py:110-118); here
+    # they are made on first access only: the build reads the stored (float32) frames straight into HBM
+    @staticmethod
+    def _as_float(stored):
+        if isinstance(stored, hostio.MemoryAnimation):
+            stored = stored.complete()
+        return np.asarray(stored).astype(float)
+
+    @property
+    def verts(self):
+        if self._verts64 is None and self._stored_verts is not None:
+            self._verts64 = self._as_float(self._stored_verts)
+        return self._verts64
+
+    @property
+    def test_verts(self):
+        if self._test64 is None and self._stored_test is not None:
+            self._test64 = self._as_float(self._stored_test)
+        return self._test64
 
     # ---- lazily materialised host views of device tensors (reference attribute names)
     @property
@@ -57,17 +79,25 @@ class posSnapshots:
         self.read()
         if massWeight:
             self.read_factorize_masses()
-            assert self.verts.shape[1] == self.massL.shape[0]
+            assert self.nVerts == self.massL.shape[0]
         if self.rest_shape not in ("first", "average"):
             print('Error! unknown rest shape: ', self.rest_shape)
             sys.exit(1)
         self.shard = engine.Shard.make(self.nVerts, comm.world, comm.rank)
         rows = slice(self.shard.row0, self.shard.row0 + self.shard.n)
         # geodesics on the un-weighted rest shape (posSnapshots.py:96-99); the mesh operator is global
-        rest = self.verts[0] if self.rest_shape == "first" else np.mean(self.verts, axis=0)
-        self._geo = HeatGeodesics(ops, np.asarray(rest, dtype=np.float64), self.tris)
+        stored = self._stored_verts
+        if isinstance(stored, hostio.MemoryAnimation):
+            assert self.rest_shape == "first", "an animation handed over in memory carries frame 0 as its rest shape"
+            rest = stored.rest
+            local = stored.rows(self.shard.row0, self.shard.n)
+            src = local if hasattr(local, "is_pinned") else np.ascontiguousarray(local)
+        else:
+            rest = stored[0] if self.rest_shape == "first" else np.mean(self.verts, axis=0)
+            src = np.ascontiguousarray(stored[:, rows])
+        self._geo = HeatGeodesics.cached(ops, np.asarray(rest, dtype=np.float64), self.tris)
         self.compute_geodesic_distance = self._distance_query
-        src = ops.to_device(np.ascontiguousarray(self._stored_verts[:, rows]))
+        src = ops.to_device(src)
         self.state = engine.prepare_snapshots(ops, comm, src, self.mass[rows] if massWeight else None, self.rest_shape,
                                               self.shard, standarize=standarize, mass_weight=massWeight)
         self.pre_scale_factor = self.state.scale
@@ -85,13 +115,11 @@ class posSnapshots:
     def read(self):
         verts, self.tris = hostio.read_animation(self.input_animation_file)
         self._stored_verts = verts                       # float32 on disk (utils/process.py:85,:246)
-        self.verts = verts.astype(float)
-        self.frs, self.nVerts, _ = self.verts.shape
+        self.frs, self.nVerts, _ = verts.shape
         print("Vertices: ", self.nVerts)
         print("Faces: ", self.tris.shape[0])
         print("Frames: ", self.frs)
-        tv, self.test_tris = hostio.read_animation(self.input_test_animation_file)
-        self.test_verts = tv.astype(float)
+        self._stored_test, self.test_tris = hostio.read_animation(self.input_test_animation_file)
 
     @log_time("")
     def read_factorize_masses(self, mass_on_tet_mesh=False):

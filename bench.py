@@ -1,14 +1,18 @@
 #!/usr/bin/env python
-"""bench.py -- PCA (greedy deflation) + SPLOCS basis build time on synthetic snapshot matrices (BASELINE.json).
+"""bench.py -- basis build time on BASELINE.json's configs, one B200 or row-sharded over N.
 
-One step = one full basis build (`compute_components_store_singvalues()` with splocs.compute = true):
-K deflation components (local geodesic support) + I_s SPLOCS outer iterations of I_a fused ADMM iterations each, on a
-standardised snapshot tensor already resident in HBM.  `e2e` times the same build through the public API from pinned
-HOST buffers (H2D of the float32 animation, ingest, standardisation, build, D2H of components and weights).
+Default (`--config synthetic`, the headline): one step = one full basis build, `compute_components_store_singvalues()` with
+splocs.compute = true (unit U1): K deflation components with local geodesic support + I_s SPLOCS outer iterations of I_a
+fused ADMM iterations, on a standardised 1M x 2000 snapshot tensor already resident in HBM.  `e2e` times the same build
+through the drop-in plug-in classes (`posComponents(param)` ... `.comps`) from pinned HOST buffers: H2D of the float32
+animation, ingest, standardisation, build, D2H of components and weights.
 
-    python bench.py                              # 1 GPU, default workload
-    torchrun --nproc-per-node N bench.py --gpus N # row-sharded over N GPUs (strong scaling, same total workload)
-    python bench.py --impl reference             # CPU oracle port of the reference path on a bounded sample
+    python bench.py                                      # 1 GPU, headline workload
+    torchrun --nproc-per-node N bench.py --gpus N        # row-sharded over N GPUs (strong scaling, same total workload)
+    python bench.py --config bunny_splocs                # BASELINE configs 1-4 and the N = 1e5 sample: bunny_pca, bunny_splocs,
+                                                         # bar_deim, armadillo_splocs, synthetic_sample
+    python bench.py --unit pod_deim                      # unit U2: Gram POD + eigensolve + back-projection + DEIM, 3e6 rows x 2000
+    python bench.py --impl reference [--config ...]      # the reference's own CPU code on the same config (oracle/ref_runner.py)
 """
 from __future__ import annotations
 
@@ -17,8 +21,10 @@ import json
 import os
 import subprocess
 import sys
+import tempfile
 import threading
 import time
+import types
 
 import numpy as np
 
@@ -27,6 +33,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "pca_splocs_basis_build_time"
 UNIT = "s"
+PRESET_NAMES = ["synthetic", "bunny_pca", "bunny_splocs", "bar_deim", "armadillo_splocs", "synthetic_sample"]
 
 
 def parse():
@@ -35,6 +42,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=1)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="synthetic", choices=PRESET_NAMES)
+    ap.add_argument("--unit", default="build", choices=["build", "pod_deim"])
     ap.add_argument("--grid", type=int, nargs=2, default=[1000, 1000], help="synthetic planar grid (nx ny) -> N = nx*ny vertices")
     ap.add_argument("--frames", type=int, default=2000)
     ap.add_argument("--comps", type=int, default=200)
@@ -46,8 +55,10 @@ def parse():
     ap.add_argument("--leaf-size", type=int, default=64, help="nested-dissection leaf size of the geodesic factorisation")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-sample", type=int, nargs=5, default=[160, 120, 140, 28, 2],
-                    help="CPU baseline sample: nx ny frames comps splocs_iters")
+    ap.add_argument("--cpu-sample", type=int, nargs=5, default=[400, 250, 500, 12, 1],
+                    help="CPU sample of the synthetic config: nx ny frames comps splocs_iters (N and F as BASELINE.md section 3 "
+                         "item 5 prescribes, fewer components / iterations)")
+    ap.add_argument("--cpu-budget", type=float, default=240.0, help="seconds the --impl reference arm may spend on timed steps")
     return ap.parse_args()
 
 
@@ -59,67 +70,129 @@ def work_units(N, F, K, Is, Ia):
     return defl_bytes, splocs_flops
 
 
-# ====================================================================================== CPU oracle leg
-def cpu_port_build(nx, ny, F, K, Is, Ia, bumps, sigma):
-    """The reference path restated on the CPU (oracle/port.py): returns seconds for one build on this sample."""
-    from animsnapbases_b200 import synth
-    from oracle import port
-    verts0, tris = synth.grid_mesh(nx, ny)
-    anim = synth.bump_animation(verts0, F, n_bumps=min(bumps, 16), sigma=max(sigma, 0.1), seed=0, translate=0.0)
-    mass = synth.lumped_vertex_masses(verts0, tris)
-    prep = port.prepare_snapshots(anim, mass, "first")
-    geo = port.GeodesicHeat(anim[0].astype(float), tris)
-    t0 = time.perf_counter()
-    C, W, meas, picked, R = port.extract_k_components(prep["snapTensor"], K, "local", geo)
-    port.splocs_glob_optimization(prep["snapTensor"], C, W, R, geo, Is, Ia, 2.0, 10.0)
-    return time.perf_counter() - t0
+def resolve(args):
+    """The workload: a dict with kind / sizes, from the preset or (synthetic) from the command line."""
+    from animsnapbases_b200 import configs
+    if args.config == "synthetic":
+        nx, ny = args.grid
+        return dict(name="synthetic", kind="pos", mesh="grid", grid=(nx, ny), vertices=nx * ny, frames=args.frames,
+                    comps=args.comps, splocs=(args.splocs_iters, args.admm_iters, 2.0, 10.0) if args.splocs_iters > 0 else None,
+                    bumps=args.bumps, sigma=args.sigma)
+    cfg = dict(configs.PRESETS[args.config], name=args.config)
+    return cfg
 
 
-def cpu_baseline(args, N, F, K, Is, Ia):
+def workload_config(cfg, N, F, K):
+    sp = cfg.get("splocs")
+    if cfg["kind"] == "bar":
+        text = (f"bar.mesh, 3 120 tets x 3 rows = {N} constraint rows x {F} frames (synthetic bend/twist/sag motion, per-tet polar "
+                f"rotations): pod_vectorized -> post_process_components -> deim, K = min(200, F) = {K}")
+    else:
+        mesh = f"synthetic {cfg['grid'][0]}x{cfg['grid'][1]} grid" if cfg["mesh"] == "grid" else f"{cfg['mesh']} mesh"
+        text = (f"{mesh} (N={N} vertices) x {F} frames, K={K} deflation components with local geodesic support 0.1/0.25"
+                + (f" + {sp[0]} SPLOCS iterations x {sp[1]} ADMM, lambda={sp[2]:g}, rho={sp[3]:g}" if sp else " (PCA only)"))
+    big = 24.0 * N * F > 4 * 126e6
+    return {"workload": text, "preset": cfg["name"], "vertices": N, "frames": F, "components": K,
+            "splocs_iters": int(sp[0]) if sp else 0, "admm_iters": int(sp[1]) if sp else 0, "sharding": "vertex rows over ranks",
+            "l2_policy": "inputs larger than L2 (snapshot tensor >> 126 MB)" if big else
+            "snapshot tensor fits in L2; L2 flushed between timed steps"}
+
+
+# ====================================================================================== CPU legs (reference / port)
+def cpu_synthetic_sample(args, prefer_reference):
+    """The synthetic config on the CPU at BASELINE.md's prescribed N = 1e5, F = 500 with fewer components / iterations (each
+    component is the same sequence of S-sized passes): measured seconds of deflation and SPLOCS, and the sample's sizes."""
+    from animsnapbases_b200 import configs
+    from oracle import ref_runner
     nx, ny, f, k, its = args.cpu_sample
-    secs = cpu_port_build(nx, ny, f, k, its, Ia, args.bumps, args.sigma)
-    # the reference's cost is ~ proportional to N*F per component / per (iteration, component): extrapolate linearly
-    n = nx * ny
-    full = secs * (N * F * (K + Is * K)) / (n * f * (k + its * k))
-    cores = os.cpu_count() or 1
-    return {"value": full, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"oracle/port.py (numpy/scipy restatement of the reference) timed {secs:.2f} s on a {nx}x{ny} grid "
-                      f"(N={n}), F={f}, K={k}, {its} SPLOCS x {Ia} ADMM iterations; value = linear extrapolation in "
-                      f"N*F*K*(1+I_s) to the full workload (the reference cannot hold the full tensor: 4-5 S-sized copies)",
-            "measured_sample_s": secs}
+    configs.PRESETS["_cpu_sample"] = dict(kind="pos", mesh="grid", grid=(nx, ny), frames=f, comps=k, bumps=min(args.bumps, 32),
+                                          sigma=max(args.sigma, 0.08), seed=0, splocs=(its, args.admm_iters, 2.0, 10.0))
+    inp = configs.build_inputs("_cpu_sample")
+    r = ref_runner.run_pos(inp, prefer_reference=prefer_reference)
+    return r, dict(n=nx * ny, f=f, k=k, its=its)
+
+
+def extrapolate(r, s, N, F, K, Is):
+    d = r["t_deflation"] * (N * F * K) / (s["n"] * s["f"] * s["k"])
+    sp = r["t_splocs"] * (N * F * K * Is) / (s["n"] * s["f"] * s["k"] * max(s["its"], 1)) if Is else 0.0
+    return d + sp
+
+
+def prescribed_sample_record():
+    """The full sample BASELINE.md section 3 item 5 prescribes (N = 1e5, F = 500, K = 200, 2 x 10), measured once with the
+    reference's own code in the build container (profiles/r02_reference_cpu_synthetic_sample.json, oracle/make_golden_scale.py)."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r02_reference_cpu_synthetic_sample.json")))
+        return {"build_s": d["build_s"], "t_deflation_s": d["t_deflation_s"], "t_splocs_s": d["t_splocs_s"], "kind": d["kind"],
+                "cores": d["host"]["cores"], "cpu": d["host"]["cpu"], "where": "build container"}
+    except Exception:
+        return None
+
+
+def cpu_leg(args, cfg, N, F, K, prefer_reference, budget, steps):
+    """Times the CPU implementation (the reference's own code when /root/reference is mounted, else oracle/port.py, its
+    restatement pinned bit-equal) on `cfg`: in full for the presets, on the bounded sample for the synthetic headline.
+    Returns (value_s, e2e_s, info dict)."""
+    from animsnapbases_b200 import configs
+    from oracle import ref_runner
+    host = ref_runner.host_info()
+    sp = cfg.get("splocs")
+    Is = int(sp[0]) if sp else 0
+    if cfg["name"] == "synthetic":
+        r, s = cpu_synthetic_sample(args, prefer_reference)
+        val = extrapolate(r, s, N, F, K, Is)
+        info = {"kind": r["kind"], "cores": host["cores"], "cpu": host["cpu"], "extrapolated": True, "steps_run": 1,
+                "measured_sample_s": r["t_deflation"] + r["t_splocs"],
+                "sample": f"{r['kind']} build timed on a {args.cpu_sample[0]}x{args.cpu_sample[1]} grid (N={s['n']}), F={s['f']} "
+                          f"(the N and F BASELINE.md section 3 item 5 prescribes), K={s['k']}, {s['its']} SPLOCS x {args.admm_iters} "
+                          f"ADMM: deflation {r['t_deflation']:.1f} s + SPLOCS {r['t_splocs']:.1f} s; value = linear extrapolation "
+                          f"in N*F*K (deflation) and N*F*K*I_s (SPLOCS) to the config -- the reference cannot hold the full "
+                          f"tensor (4-5 S-sized copies of 48 GB)",
+                "prescribed_sample": prescribed_sample_record()}
+        return val, val, info
+    inp = configs.build_inputs(cfg["name"])
+    vals, e2es, t0 = [], [], time.perf_counter()
+    kind = "port"
+    while len(vals) < max(1, steps) and (not vals or time.perf_counter() - t0 + vals[-1] < budget):
+        if cfg["kind"] == "bar":
+            r = ref_runner.run_bar(inp, prefer_reference=prefer_reference)
+            v = r["t_pod"] + r["t_post"] + r["t_deim"]
+        else:
+            r = ref_runner.run_pos(inp, prefer_reference=prefer_reference)
+            v = r["t_deflation"] + r["t_splocs"]
+        kind = r["kind"]
+        vals.append(v)
+        e2es.append(v + r["t_prepare"])
+    info = {"kind": kind, "cores": host["cores"], "cpu": host["cpu"], "extrapolated": False, "steps_run": len(vals),
+            "sample": f"the config in full, {len(vals)} run(s) of {'the unmodified reference (oracle/ref_shim.py)' if kind == 'reference' else 'oracle/port.py'}"}
+    return float(np.mean(vals)), float(np.mean(e2es)), info
 
 
 def run_reference(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
+    if int(os.environ.get("RANK", "0")) != 0:
         return
-    N = args.grid[0] * args.grid[1]
-    F, K, Is, Ia = args.frames, args.comps, args.splocs_iters, args.admm_iters
-    nx, ny, f, k, its = args.cpu_sample
-    for _ in range(max(args.warmup, 0) and 1):
-        cpu_port_build(max(nx // 4, 8), max(ny // 4, 8), max(f // 4, 8), min(k, 4), 1, 2, args.bumps, args.sigma)
-    times = [cpu_port_build(nx, ny, f, k, its, Ia, args.bumps, args.sigma) for _ in range(max(1, args.steps))]
-    secs = float(np.mean(times))
-    n = nx * ny
-    full = secs * (N * F * (K + Is * K)) / (n * f * (k + its * k))
-    cores = os.cpu_count() or 1
-    line = {"impl": "reference", "metric": METRIC, "value": full, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": full * 1e3, "higher_is_better": False, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(args, N, F, K, Is, Ia),
-            "cpu_baseline": {"value": full, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": f"each step = oracle/port.py build on a {nx}x{ny} grid, F={f}, K={k}, {its}x{Ia} SPLOCS "
-                                       f"({secs:.2f} s measured), linearly extrapolated in N*F*K*(1+I_s) to the config"},
-            "e2e": {"value": full, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    cfg = resolve(args)
+    N, F, K = sizes(cfg)
+    val, e2e, info = cpu_leg(args, cfg, N, F, K, True, args.cpu_budget, args.steps)
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "steps_run": info["steps_run"], "warmup": args.warmup, "warmup_run": 0, "ms_per_step": val * 1e3,
+            "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(cfg, N, F, K), "extrapolated": info["extrapolated"],
+            "cpu_baseline": dict(info, value=val, unit=UNIT),
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
-def workload_config(args, N, F, K, Is, Ia):
-    return {"workload": f"synthetic {args.grid[0]}x{args.grid[1]} grid (N={N} vertices) x {F} frames, K={K} deflation "
-                        f"components with local geodesic support 0.1/0.25 + {Is} SPLOCS iterations x {Ia} ADMM, lambda=2, rho=10",
-            "vertices": N, "frames": F, "components": K, "splocs_iters": Is, "admm_iters": Ia,
-            "sharding": "vertex rows over ranks", "l2_policy": "inputs larger than L2 (snapshot tensor >> 126 MB)"
-            if 24.0 * N * F > 4 * 126e6 else "snapshot tensor fits in L2; L2 flushed between timed steps"}
+def sizes(cfg):
+    """(rows N, frames F, components K) of a workload."""
+    if cfg["kind"] == "bar":
+        return 3 * 3120, int(cfg["frames"]), min(int(cfg["comps"]), int(cfg["frames"]))
+    if cfg["mesh"] == "grid":
+        N = cfg["grid"][0] * cfg["grid"][1]
+    else:
+        from animsnapbases_b200 import synth
+        N = len(synth.golden_mesh(cfg["mesh"])["verts"])
+    return N, int(cfg["frames"]), int(cfg["comps"])
 
 
 # ====================================================================================== clocks
@@ -154,6 +227,30 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def measure_fp64_peak(torch, device):
+    """fp64 is not in MEASURED_PEAKS.json: cuBLAS DGEMM 8192^3 measured here (the library kernel to beat)."""
+    a = torch.randn(8192, 8192, dtype=torch.float64, device=device)
+    b = torch.randn(8192, 8192, dtype=torch.float64, device=device)
+    best = 1e30
+    for i in range(6):
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        torch.matmul(a, b)
+        s1.record()
+        torch.cuda.synchronize()
+        if i:
+            best = min(best, s0.elapsed_time(s1))
+    return 2 * 8192.0 ** 3 / (best * 1e-3) / 1e12
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+
+
 # ====================================================================================== GPU arm
 def main():
     args = parse()
@@ -162,7 +259,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from animsnapbases_b200 import engine, synth
+    from animsnapbases_b200 import configs, engine, hostio, runtime, synth
     from animsnapbases_b200.geodesic import HeatGeodesics
     from animsnapbases_b200.ops import CudaOps
 
@@ -174,17 +271,35 @@ def main():
     ops = CudaOps(f"cuda:{local_rank}")
     comm = engine.Comm()
     rank = comm.rank
+    runtime.install(ops, comm)
+    if args.unit == "pod_deim":
+        return bench_pod_deim(args, torch, dist, ops, comm, engine, world, local_rank)
+    cfg = resolve(args)
+    if cfg["kind"] == "bar":
+        return bench_bar(args, cfg, torch, dist, ops, comm, engine, configs, hostio, world, local_rank)
 
-    nx, ny = args.grid
-    N, F, K, Is, Ia = nx * ny, args.frames, args.comps, args.splocs_iters, args.admm_iters
+    N, F, K = sizes(cfg)
+    sp = cfg.get("splocs")
+    Is, Ia = (int(sp[0]), int(sp[1])) if sp else (0, 0)
+    lam, rho = (float(sp[2]), float(sp[3])) if sp else (2.0, 10.0)
     sh = engine.Shard.make(N, world, rank)
-    verts0, tris = synth.grid_mesh(nx, ny)
-    mass = synth.lumped_vertex_masses(verts0, tris)
-    centres, amps, _ = synth.bump_parameters(verts0, F, args.bumps, seed=0)
     rows = slice(sh.row0, sh.row0 + sh.n)
-    v_loc = ops.to_device(verts0[rows])
-    anim_dev = synth.device_bump_animation_from_params(v_loc, verts0[centres], amps, args.sigma)   # (F, n_loc, 3) f32
-    geo = HeatGeodesics(ops, verts0, tris, leaf_size=args.leaf_size)
+    if cfg["name"] == "synthetic":
+        verts0, tris = synth.grid_mesh(*cfg["grid"])
+        mass = synth.lumped_vertex_masses(verts0, tris)
+        centres, amps, _ = synth.bump_parameters(verts0, F, cfg["bumps"], seed=0)
+        v_loc = ops.to_device(verts0[rows])
+        anim_dev = synth.device_bump_animation_from_params(v_loc, verts0[centres], amps, cfg["sigma"])   # (F, n_loc, 3) f32
+        rest = verts0.astype(np.float32).astype(np.float64)      # frame 0 of the float32 animation (amplitudes start at 0)
+    else:
+        inp = configs.build_inputs(cfg["name"])
+        tris, mass, rest = inp["tris"], inp["mass"], inp["rest"]
+        anim_dev = ops.to_device(np.ascontiguousarray(inp["anim"][:, rows]))
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    geo = HeatGeodesics.cached(ops, rest, tris, leaf_size=args.leaf_size)
+    torch.cuda.synchronize()
+    geodesic_setup_s = time.perf_counter() - t0
     mass_loc = mass[rows]
 
     def prepare(src_dev):
@@ -198,7 +313,8 @@ def main():
         ev[0].record()
         C, W, meas, picked, _ = engine.deflate(ops, comm, st.X, sh, K, True, geo, block=args.block, keep_residual=False)
         ev[1].record()
-        engine.splocs(ops, comm, st.X, sh, C, W, K, geo, Is, Ia, 2.0, 10.0, log=None)
+        if Is:
+            engine.splocs(ops, comm, st.X, sh, C, W, K, geo, Is, Ia, lam, rho, log=None)
         ev[2].record()
         phase_ev.append(ev)
         return C, W, meas
@@ -245,33 +361,72 @@ def main():
     phase_ev.clear()
     geo_stats = dict(geo.stats)
 
-    # ---- e2e: host float32 animation (pinned) -> H2D -> ingest -> standardise -> build -> D2H comps + weights
+    # ---- e2e through the drop-in classes: pinned host float32 animation -> posComponents(param) [read = H2D, ingest,
+    # standardise] -> compute_components_store_singvalues() -> .comps / .weigs (+ the SPLOCS pair) back on the host
     e2e = None
     if not args.no_e2e:
+        from animsnapbases_b200.snapbases.posComponents import posComponents
         host_in = torch.empty(anim_dev.shape, dtype=torch.float32, pin_memory=True)
         host_in.copy_(anim_dev)
         del anim_dev, st                                   # one resident snapshot tensor at a time (48 GB at 1M x 2000)
         torch.cuda.empty_cache()
-        host_C = torch.empty((K, 3, sh.ld), dtype=torch.float64, pin_memory=True)
-        host_W = torch.empty((F, (K + 3) // 4 * 4), dtype=torch.float64, pin_memory=True)
+        tmp = tempfile.mkdtemp(prefix="asb_bench_") if rank == 0 else None
+        if world > 1:
+            box = [tmp]
+            dist.broadcast_object_list(box, src=0)
+            tmp = box[0]
+        mass_file = os.path.join(tmp, "mass.bin")
+        if rank == 0:
+            hostio.write_mass_bin(mass_file, mass)
+        sync_all()
+        mem = hostio.MemoryAnimation(host_in, tris, rest=rest, row0=sh.row0, n_global=N)
+        hostio.register_animation("mem://bench/train", mem)
+        hostio.register_animation("mem://bench/test", mem)
+        param = types.SimpleNamespace(
+            vertPos_bases_type="SPLOCS" if Is else "PCA", aligned_snapshots_directory="mem://bench",
+            train_aligned_snapshots_animation_file="train", test_aligned_snapshots_animation_file="test",
+            vertPos_rest_shape="first", vertPos_masses_file=mass_file, tet_mesh_file="", q_standarize=True, q_massWeight=True,
+            vertPos_numComponents=K, q_support="local", store_vertPos_PCA_sing_val=False, vertPos_smooth_min_dist=0.1,
+            vertPos_smooth_max_dist=0.25, splocs_max_itrs=Is, splocs_admm_num_itrs=Ia, splocs_lambda=lam, splocs_rho=rho,
+            q_orthogonal=False, vertPos_output_directory=tmp, name="bench", engine_deflation_block=args.block,
+            engine_geodesic_leaf_size=args.leaf_size)
         n_e2e = max(1, min(args.steps, 2))
-        sync_all()
-        t0 = time.perf_counter()
-        for _ in range(n_e2e):
-            d_in = host_in.to(ops.device, non_blocking=True)
-            st2 = prepare(d_in)
-            del d_in
-            C, W, meas = build(st2)
-            host_C.copy_(C, non_blocking=True)
-            host_W.copy_(W, non_blocking=True)
-            torch.cuda.synchronize()
-            del st2, C, W
-        sync_all()
-        t = torch.tensor([(time.perf_counter() - t0) / n_e2e], dtype=torch.float64, device=ops.device)
+        d2h = 0
+        cwd = os.getcwd()
+        os.chdir(tmp)                                      # log_time("") appends to function_timings.txt in the CWD
+        devnull = open(os.devnull, "w")
+        times = []
+        try:
+            for i in range(n_e2e + 1):                     # the first pass is untimed (pinned staging buffers, graph capture)
+                sync_all()
+                t0 = time.perf_counter()
+                out_stdout, sys.stdout = sys.stdout, devnull
+                try:
+                    pc = posComponents(param)
+                    pc.compute_components_store_singvalues()
+                    got = [pc.local_components_host(), pc.weigs]
+                    if Is:
+                        got += [pc.local_components_host(splocs=True), pc.splocs_weigs]
+                finally:
+                    sys.stdout = out_stdout
+                torch.cuda.synchronize()
+                d2h = sum(int(a.nbytes) for a in got)
+                del pc, got
+                sync_all()
+                if i:
+                    times.append(time.perf_counter() - t0)
+        finally:
+            os.chdir(cwd)
+        t = torch.tensor([float(np.mean(times))], dtype=torch.float64, device=ops.device)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e = {"value": float(t.item()), "unit": UNIT, "h2d_bytes_per_step": int(host_in.numel() * 4 * world),
-               "d2h_bytes_per_step": int((host_C.numel() + host_W.numel()) * 8 * world), "steps": n_e2e}
+               "d2h_bytes_per_step": int(d2h * world), "steps": n_e2e,
+               "api": "posComponents(param); compute_components_store_singvalues(); .comps / .weigs"
+                      + (" / .splocs_comps / .splocs_weigs" if Is else "") + " (row shard of this rank when sharded)",
+               "excludes": "geodesic factorisation (geodesic_factorisation_s: built once per mesh, cached across builds)"}
+        hostio.register_animation("mem://bench/train", None)
+        hostio.register_animation("mem://bench/test", None)
 
     if rank != 0:
         if world > 1:
@@ -279,28 +434,9 @@ def main():
         return
 
     # ---- roofline of the dominant kernel (by device time inside the timed region)
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    hbm_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback 6.65 TB/s (B200_PROFILING.md)"
-    # fp64 peak is not in MEASURED_PEAKS.json: measure cuBLAS DGEMM here (the library kernel to beat)
-    a = torch.randn(8192, 8192, dtype=torch.float64, device=ops.device)
-    b = torch.randn(8192, 8192, dtype=torch.float64, device=ops.device)
-    best = 1e30
-    for i in range(6):
-        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s0.record()
-        torch.matmul(a, b)
-        s1.record()
-        torch.cuda.synchronize()
-        if i:
-            best = min(best, s0.elapsed_time(s1))
-    fp64_peak = 2 * 8192.0 ** 3 / (best * 1e-3) / 1e12
-    del a, b
-    n_loc, ld = sh.n, sh.ld
+    hbm_peak, hbm_src = peaks()
+    fp64_peak = measure_fp64_peak(torch, ops.device)
+    ld = sh.ld
     M = 3.0 * ld
     # ALGORITHMIC work of all launches of one entry point in one step (local shard)
     per_step = {
@@ -308,22 +444,26 @@ def main():
         "asb_rank_update": ("hbm", -(-K // args.block) * 2 * 8.0 * F * M),   # read + write pass per block of components
         "asb_admm_solve": ("tensor", Is * Ia * 2.0 * K * K * M),             # Hr (Z - U), Ia iterations fused per launch
         "asb_gemm_nn": ("tensor", Is * 2.0 * K * F * M),                     # B0 = (H^-1 W^T) X
-        "asb_gemm_nt": ("tensor", (Is + 1) * (2.0 * F * K + K * (K + 1.0)) * M),   # P = X C^T and the symmetric Q = C C^T
+        "asb_gemm_nt": ("tensor", (Is + 1) * (2.0 * F * K + K * (K + 1.0)) * M if Is else 0.0),   # P = X C^T, symmetric Q = C C^T
     }
-    dom = max(ktimes.items(), key=lambda kv: kv[1][1])[0] if ktimes else None
+    cand = {k: v for k, v in ktimes.items() if k in per_step and per_step[k][1] > 0 and v[0]}
+    dom = max(cand.items(), key=lambda kv: kv[1][1])[0] if cand else None
     roof = None
-    if dom in per_step and ktimes[dom][0]:
+    if dom:
         bound, work = per_step[dom]
         work *= args.steps
         tot_s = ktimes[dom][1] * 1e-3
         traffic = None      # measured DRAM bytes per launch (ncu capture of the same kernel at this shape), if we have one
-        try:
-            tr = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
-            w = tr["workload"]
-            if world == 1 and (w["vertices"], w["frames"], w["components"], w["admm_iters"]) == (N, F, K, Ia):
-                traffic = tr["per_launch_bytes"].get(dom)
-        except Exception:
-            pass
+        for tf in ("r02_traffic.json", "r01_traffic.json"):
+            try:
+                tr = json.load(open(os.path.join(ROOT, "profiles", tf)))
+                w = tr["workload"]
+                if world == 1 and (w["vertices"], w["frames"], w["components"], w["admm_iters"]) == (N, F, K, Ia) \
+                        and dom in tr["per_launch_bytes"]:
+                    traffic = tr["per_launch_bytes"][dom]
+                    break
+            except Exception:
+                pass
         common = {"kernel": dom, "bound": bound, "traffic": traffic, "avg_launch_ms": ktimes[dom][1] / ktimes[dom][0],
                   "launches": ktimes[dom][0], "work_per_launch": work / ktimes[dom][0]}
         if bound == "hbm":
@@ -339,17 +479,238 @@ def main():
     line = {
         "metric": METRIC, "value": ms_per_step / 1e3, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": workload_config(args, N, F, K, Is, Ia), "gpu_launches": int(launches),
+        "data": "synthetic", "config": workload_config(cfg, N, F, K), "gpu_launches": int(launches),
         "clocks": clk, "e2e": e2e, "roofline": roof,
         "path_roofline": {"ideal_s": ideal, "frac": ideal / (ms_per_step / 1e3), "hbm_gbs": hbm_peak, "fp64_tflops": fp64_peak,
                           "algorithmic": {"deflation_bytes": defl_bytes, "splocs_flops": splocs_flops}},
         "phase_ms_per_step": phase_ms,
+        "geodesic_factorisation_s": geodesic_setup_s,
         "kernel_ms_per_step": {k: v[1] / args.steps for k, v in ktimes.items()},
         "kernel_launches_per_step": {k: v[0] / args.steps for k, v in ktimes.items()},
+        "kernel_ms_note": "CUDA events around each launch on the launching stream; the single-source geodesic queries of the "
+                          "deflation are CUDA-graph replays on the side stream (beside asb_deflate_gemv) and are not in this list",
         "geodesic": geo_stats,
     }
     if not args.no_cpu_baseline and world == 1:
-        line["cpu_baseline"] = cpu_baseline(args, N, F, K, Is, Ia)
+        if cfg["name"] == "synthetic":                     # bounded sample, timed here on this box's host cores
+            val, _, info = cpu_leg(args, cfg, N, F, K, True, args.cpu_budget, 1)
+            line["cpu_baseline"] = dict(info, value=val, unit=UNIT)
+        else:                                              # ~10 minutes of CPU: the committed full run of the reference
+            line["cpu_baseline"] = preset_cpu_record(cfg["name"])
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def preset_cpu_record(name):
+    """CPU time of a preset that takes ~10 minutes on the CPU (bunny / armadillo 20 x 10 SPLOCS, the N = 1e5 sample): the
+    committed full run of the reference's own code (oracle/make_golden_scale.py -> profiles/r02_reference_cpu_<preset>.json);
+    `bench.py --impl reference --config <preset>` re-measures it on this box."""
+    src = {"bunny_pca": "bunny_splocs"}.get(name, name)
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", f"r02_reference_cpu_{src}.json")))
+    except Exception:
+        return None
+    v = d["t_deflation_s"] if name == "bunny_pca" else d["build_s"]
+    return {"value": v, "unit": UNIT, "cores": d["host"]["cores"], "cpu": d["host"]["cpu"], "kind": d["kind"], "extrapolated": False,
+            "sample": f"the config in full, unmodified reference through oracle/ref_shim.py, measured in the build container "
+                      f"(profiles/r02_reference_cpu_{src}.json); re-measure here with --impl reference --config {name}"}
+
+
+# ====================================================================================== config 3: bar, POD + DEIM
+def bench_bar(args, cfg, torch, dist, ops, comm, engine, configs, hostio, world, local_rank):
+    """pod_vectorized -> post_process_components -> deim on the full bar (BASELINE config 3)."""
+    rank = comm.rank
+    inp = configs.build_inputs(cfg["name"])
+    snaps, mass, p = inp["snaps"], inp["mass"], inp["p"]
+    F, ep, _ = snaps.shape
+    K = min(int(cfg["comps"]), F)
+    sh = engine.Shard.make(ep, world, rank, multiple=96)
+    rows = slice(sh.row0, sh.row0 + sh.n)
+    src = ops.to_device(np.ascontiguousarray(snaps[:, rows]))
+    st = engine.prepare_snapshots(ops, comm, src, mass[rows], "first", sh)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=ops.device)
+    phases = []
+
+    def build():
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        ev[0].record()
+        comps, sig = engine.pod(ops, comm, st.X, sh, K)
+        ev[1].record()
+        ops.unstandardize(comps, st.mean, st.scale, sh.n)
+        engine.orthogonalize_rows(ops, comm, comps, sh, K)
+        Cp = ops.ingest(ops.export_aos(comps, st.invMassL, sh.n), None, sh.ld)
+        ev[2].record()
+        Pt = engine.deim(ops, comm, Cp, sh, K)
+        ev[3].record()
+        phases.append(ev)
+        return Pt
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        build()
+    sync_all()
+    ops.reset_launch_count()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    phases.clear()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    ev0.record()
+    for _ in range(args.steps):
+        flush.fill_(1)
+        build()
+    ev1.record()
+    sync_all()
+    ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=ops.device)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    launches = ops.launch_count()
+    clk = clocks.stop() if rank == 0 else None
+    ms_per_step = float(ms.item()) / args.steps
+    ph = {"pod": sum(e[0].elapsed_time(e[1]) for e in phases) / args.steps,
+          "post_process": sum(e[1].elapsed_time(e[2]) for e in phases) / args.steps,
+          "deim": sum(e[2].elapsed_time(e[3]) for e in phases) / args.steps}
+    # e2e: host arrays -> H2D -> prepare -> build -> indices on the host (engine API; the constraint-projection plug-in reads
+    # per-frame .npz files from disk, which would time the file system)
+    host = torch.from_numpy(np.ascontiguousarray(snaps[:, rows])).pin_memory()
+    times = []
+    for i in range(3):
+        sync_all()
+        t0 = time.perf_counter()
+        st = engine.prepare_snapshots(ops, comm, host.to(ops.device, non_blocking=True), mass[rows], "first", sh)
+        Pt = build()
+        torch.cuda.synchronize()
+        if i:
+            times.append(time.perf_counter() - t0)
+    if rank != 0:
+        return
+    hbm_peak, hbm_src = peaks()
+    fp64_peak = measure_fp64_peak(torch, ops.device)
+    deim_bytes = sum(3.0 * sh.ld * (k + 1) * 8 for k in range(K))
+    line = {"metric": METRIC, "value": ms_per_step / 1e3, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": workload_config(cfg, ep, F, K), "gpu_launches": int(launches), "clocks": clk,
+            "e2e": {"value": float(np.mean(times)), "unit": UNIT, "h2d_bytes_per_step": int(host.numel() * 8 * world),
+                    "d2h_bytes_per_step": int(K * 8), "steps": len(times), "api": "engine.prepare_snapshots / pod / deim"},
+            "phase_ms_per_step": ph,
+            "roofline": {"kernel": "engine.deim (asb_deim_residual passes)", "bound": "hbm", "achieved": deim_bytes / (ph["deim"] * 1e-3) / 1e9,
+                         "peak": hbm_peak, "unit": "GB/s", "frac": deim_bytes / (ph["deim"] * 1e-3) / 1e9 / hbm_peak, "traffic": None,
+                         "peak_source": hbm_src,
+                         "note": "15 MB basis: every pass is launch-latency bound (K = 70 steps x ~6 launches), not bandwidth bound"},
+            "fp64_tflops": fp64_peak}
+    if not args.no_cpu_baseline and world == 1:
+        val, _, info = cpu_leg(args, cfg, ep, F, K, True, args.cpu_budget, 1)
+        line["cpu_baseline"] = dict(info, value=val, unit=UNIT)
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ====================================================================================== unit U2 at scale: POD + DEIM
+def bench_pod_deim(args, torch, dist, ops, comm, engine, world, local_rank):
+    """SURVEY 8(d) U2 at the synthetic shape: ep = 3e6 constraint rows (grid 1000 x 1000 x 3), F = 2000 frames, K = 200:
+    symmetric Gram on the DMMA pipe (against cuBLAS DSYRK / DGEMM on the same box), F x F eigensolve (cuSOLVER syevd,
+    replicated), back-projection GEMM, DEIM greedy (HBM: sum_k 3 ep (k+1) 8 bytes)."""
+    rank = comm.rank
+    nx, ny = args.grid
+    ep, F, K = nx * ny * 3 // 1, args.frames, args.comps
+    ep = nx * ny                                        # rows of the planar tensor (3 planes each): 1e6 x 3 = 3e6 scalar rows
+    sh = engine.Shard.make(ep, world, rank, multiple=96)
+    ld, n = sh.ld, sh.n
+    M = 3 * ld
+    g = torch.Generator(device=ops.device)
+    g.manual_seed(1234 + rank)
+    X = ops.empty((F, 3, ld))
+    # decaying spectrum: X = sum_j s_j a_j b_j^T with s_j = 0.97^j plus noise (generated by chunks of frames)
+    R = 64
+    A = torch.randn((F, R), generator=g, dtype=torch.float64, device=ops.device) * (0.9 ** torch.arange(R, device=ops.device, dtype=torch.float64))
+    Bm = torch.randn((R, M), generator=g, dtype=torch.float64, device=ops.device)
+    for f0 in range(0, F, 100):
+        X.view(F, M)[f0:f0 + 100] = A[f0:f0 + 100] @ Bm
+        X.view(F, M)[f0:f0 + 100] += 1e-3 * torch.randn((min(100, F - f0), M), generator=g, dtype=torch.float64, device=ops.device)
+    if n < ld:
+        X[:, :, n:] = 0
+    del Bm
+    Xm = X.view(F, M)
+    Fp = (F + 1) // 2 * 2
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, reps):
+        fn()
+        sync_all()
+        best = []
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            best.append(a.elapsed_time(b))
+        t = torch.tensor([float(np.mean(best))], dtype=torch.float64, device=ops.device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) * 1e-3
+
+    reps = max(1, args.steps)
+    G = ops.zeros((F, Fp))
+    t_gram = timed(lambda: (ops.gemm_nt(Xm, F, Xm, F, M, symmetric=True, out=G), comm.allreduce_sum(G)), reps)
+    # library kernels on the same box: DSYRK through cuBLAS is not exposed by torch; torch.matmul(X, X^T) dispatches to cuBLAS
+    # DGEMM (full square, 2 F^2 M flops).  Timed on a column slice that fits next to X, scaled to M.
+    cols = min(M, 600000)
+    xs = Xm[:, :cols]
+    t_cublas = timed(lambda: torch.matmul(xs, xs.t()), reps) * (M / cols)
+    G.zero_()
+    ops.gemm_nt(Xm, F, Xm, F, M, symmetric=True, out=G)
+    comm.allreduce_sum(G)
+    Gc = G.clone()
+    t_eig = timed(lambda: (G.copy_(Gc), ops.syevd(G, F)), reps)
+    comps = ops.empty((K, 3, ld))
+    Aw = ops.empty((K, Fp)).normal_()
+    t_back = timed(lambda: ops.gemm_nn(Aw, K, F, Xm, M, 1.0, comps.view(K, M)), reps)
+    t_pod = timed(lambda: engine.pod(ops, comm, X, sh, K, max_passes=1), reps)
+    comps, sig = engine.pod(ops, comm, X, sh, K, max_passes=1)
+    engine.orthogonalize_rows  # noqa: B018 -- DEIM below runs on the POD modes as they are (orthonormal)
+    ops.reset_launch_count()
+    t_deim = timed(lambda: engine.deim(ops, comm, comps, sh, K), reps)
+    launches = ops.launch_count()
+    if rank != 0:
+        return
+    hbm_peak, hbm_src = peaks()
+    fp64_peak = measure_fp64_peak(torch, ops.device)
+    gram_flops = 1.0 * F * (F + 1) * M
+    back_flops = 2.0 * K * F * M
+    deim_bytes = sum(8.0 * M * (k + 1) for k in range(K))
+    total = t_pod + t_deim
+    line = {"metric": "pod_deim_build_time", "value": total, "unit": UNIT, "n_gpus": world, "steps": reps, "warmup": 1,
+            "ms_per_step": total * 1e3, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "gpu_launches": int(launches),
+            "config": {"workload": f"unit U2 (SURVEY 8(d)): rank-64 + noise snapshot matrix, {3 * ep} scalar rows x {F} frames "
+                                   f"(1M elements x 3 planes), pod (one Gram pass) + DEIM, K = {K}", "rows": 3 * ep, "frames": F,
+                       "components": K, "l2_policy": "inputs larger than L2"},
+            "phases_s": {"gram_syrk_allreduce": t_gram, "syevd_F%d" % F: t_eig, "back_projection": t_back, "pod_total": t_pod,
+                         "deim": t_deim},
+            "roofline": {"kernel": "gemm_nt_kernel (symmetric Gram X X^T)", "bound": "tensor", "achieved": gram_flops / world / t_gram / 1e12,
+                         "peak": fp64_peak, "unit": "TFLOP/s", "frac": gram_flops / world / t_gram / 1e12 / fp64_peak, "traffic": None,
+                         "work": "F (F + 1) M flops (symmetric half)", "peak_source": "cuBLAS DGEMM 8192^3 measured in this run"},
+            "roofline_deim": {"kernel": "deim_residual_kernel (+ gather / solve / argmax per step)", "bound": "hbm",
+                              "achieved": deim_bytes / t_deim / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                              "frac": deim_bytes / t_deim / 1e9 / hbm_peak, "work": "sum_k 8 M (k + 1) bytes (residual passes over "
+                              "the growing basis)", "peak_source": hbm_src},
+            "library": {"cublas_dgemm_XXt_full_square_s": t_cublas, "cublas_TFLOPs_full_flops": 2.0 * F * F * M / t_cublas / 1e12,
+                        "ours_over_cublas_time": t_gram / t_cublas,
+                        "note": "torch exposes no DSYRK; cuBLAS DGEMM computes the full square (2 F^2 M flops), timed on a "
+                                f"{cols}-column slice and scaled to M; ours computes the symmetric half"},
+            "back_projection_TFLOPs": back_flops / world / t_back / 1e12, "fp64_tflops": fp64_peak}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

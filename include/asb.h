@@ -42,6 +42,9 @@ int asb_device_info(int* sm_count, int* cc_major, int* cc_minor);
 /* Number of kernel launches issued through this library since the last reset (bench `gpu_launches`). */
 int64_t asb_launch_count(void);
 void asb_reset_launch_count(void);
+/* Adds n to the counter: the kernel nodes of a CUDA graph replay (launches captured into a graph are counted once, when
+ * they are captured; the host adds them again for every replay). */
+void asb_add_launch_count(int64_t n);
 /* Scratch bytes every reducing entry point may need for (rows x cols)-sized problems. */
 int64_t asb_workspace_bytes(int64_t rows, int64_t cols);
 

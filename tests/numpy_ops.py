@@ -34,6 +34,9 @@ class NumpyOps:
     def join(self):
         pass
 
+    def record_event(self):
+        return None
+
     def empty(self, shape, dtype=F64):
         return torch.zeros(shape, dtype=dtype)
 
@@ -43,6 +46,9 @@ class NumpyOps:
     def to_device(self, a, dtype=None):
         t = torch.as_tensor(np.ascontiguousarray(a))
         return t.to(dtype) if dtype is not None else t.clone()
+
+    def to_host(self, t):
+        return t.numpy()
 
     def launch_count(self):
         return self.launches

@@ -57,8 +57,42 @@ def pd_bench(cells, frames):
                       "GB/s": frames * (es.num_elements * (8 + 8 + 24.0) + nv * 24.0) / t / 1e9}), flush=True)
 
 
+def geo_bench(nx, ny, leaf_size=64):
+    """Heat-method geodesics on an nx x ny grid: factorisation set-up, single-source queries (the 200 sequential deflation
+    queries: latency bound, replicated on every rank) and a batch of 40 (the new centres of a SPLOCS iteration)."""
+    import time
+    import numpy as np
+    from animsnapbases_b200 import synth
+    from animsnapbases_b200.geodesic import HeatGeodesics
+    ops = CudaOps("cuda:0")
+    verts, tris = synth.grid_mesh(nx, ny)
+    t0 = time.perf_counter()
+    geo = HeatGeodesics(ops, verts, tris, leaf_size=leaf_size)
+    torch.cuda.synchronize()
+    setup = time.perf_counter() - t0
+    n = nx * ny
+    rng = np.random.default_rng(0)
+    out = ops.zeros((1, geo.ldx))
+    srcs = [ops.to_device(np.array([int(i)], dtype=np.int64)) for i in rng.integers(0, n, size=16)]
+    state = {"i": 0}
+
+    def one():
+        geo.support(srcs[state["i"] % len(srcs)], 0, 1.0, 0.1, 0.25, 0, n, out)
+        state["i"] += 1
+    t1 = timed(one, reps=12, warm=3)
+    ids = ops.to_device(rng.integers(0, n, size=40).astype(np.int64))
+    outb = ops.zeros((40, geo.ldx))
+    tb = timed(lambda: geo.support(ids, 1, 2.0, 0.1, 0.25, 0, n, outb), reps=3, warm=1)
+    ob = geo.stats["operator_bytes"]
+    print(json.dumps({"kernel": "geodesic_query", "grid": [nx, ny], "setup_s": setup, "operator_bytes": ob, "levels": geo.stats["levels"],
+                      "single_source_ms": t1 * 1e3, "single_source_GB/s": 1.5 * ob / t1 / 1e9, "batch40_ms": tb * 1e3,
+                      "batch40_ms_per_query": tb * 1e3 / 40, "mf_tall": os.environ.get("ASB_MF_TALL", "1"),
+                      "note": "single source: 3 of the 4 triangular passes stream every operator once (1.5 x operator bytes)"}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--geo", type=int, nargs=2, metavar=("NX", "NY"), default=None, help="time heat-method geodesic queries on a grid")
     ap.add_argument("--verts", type=int, default=1000000)
     ap.add_argument("--frames", type=int, default=2000)
     ap.add_argument("--comps", type=int, default=200)
@@ -69,6 +103,8 @@ def main():
     args = ap.parse_args()
     if args.pd:
         return pd_bench(args.pd[0], args.pd[1])
+    if args.geo:
+        return geo_bench(args.geo[0], args.geo[1])
     if args.once:
         global timed
         _t = timed
