@@ -296,6 +296,243 @@ __device__ __forceinline__ void admm_body(double* smem, const double* __restrict
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Bulk-copy (TMA) variant of the Pair layout.  Same tile, same fragments, same epilogue; what changes is how the left operand
+// reaches shared memory and how the warps of a CTA meet:
+//   * Hr is re-laid once per launch into slab-major order  Hpk[slab][row][12]  (8 columns + 4 padding doubles: the padded row
+//     stride the A-fragment reads are conflict-free with), so a slab is ONE contiguous 19.2 KB block and ONE thread moves it
+//     with `cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes` (SASS UBLKCP) instead of every thread issuing 7
+//     16-byte cp.async per slab;
+//   * slabs are handed over through mbarriers (full[stage]: armed with expect_tx by the issuing thread, completed by the copy
+//     engine; empty[stage]: one arrival per warp), so there is NO CTA-wide barrier per slab: a warp waits for data, never for
+//     its neighbours.  Two __syncthreads per ADMM iteration remain (D = Z - U is read by every warp and rewritten by the
+//     epilogue);
+//   * the ring never drains: Hr is the same for every vertex tile, so the slab stream runs on across iterations AND tiles
+//     (the r01 kernel refilled its ring from empty at every tile).
+// The refill of the stage that held slab g-1 is issued by thread 0 at the start of step g, when the other warps have had a
+// whole slab of slack to release it.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* b, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
+    const uint32_t a = smem_u32(b);
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}"
+            : "=r"(ok)
+            : "r"(a), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+struct AdmmTma {
+    static constexpr int WM = 4, WN = 1, CTAS = 2, BK = 8, STAGES = 3, ALD = 12, THREADS = 128, NV = 8, NC = 24, DLD = 28;
+};
+
+// Hpk[slab][row][0..11]: columns 8 slab .. 8 slab + 7 of Hr row `row`, then 4 zeros
+__global__ void admm_pack_kernel(const double* __restrict__ Hr, int64_t ldh, int rows8, int nslab, double* __restrict__ Hpk) {
+    const int total = nslab * rows8 * AdmmTma::ALD;
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+        const int c = t % AdmmTma::ALD, r = (t / AdmmTma::ALD) % rows8, sl = t / (AdmmTma::ALD * rows8);
+        Hpk[t] = c < AdmmTma::BK ? Hr[(int64_t)r * ldh + sl * AdmmTma::BK + c] : 0.0;
+    }
+}
+
+template <int MT, int MTN>
+__device__ __forceinline__ void admm_tma_body(double* smem, const double* __restrict__ Hpk, const double* __restrict__ B0,
+                                              double* __restrict__ Z, double* __restrict__ U, const double* __restrict__ Lambda,
+                                              int K, int64_t N, int64_t ld, double inv_rho, int iters, int64_t ntiles, int mt0,
+                                              bool live) {
+    using Cfg = AdmmTma;
+    constexpr int DLD = Cfg::DLD, ALD = Cfg::ALD, STAGES = Cfg::STAGES;
+    const int rows8 = (K + 7) & ~7;
+    const int nslab = rows8 >> 3;
+    const int astage = rows8 * ALD;
+    const uint32_t slab_bytes = (uint32_t)astage * 8u;
+    double* Ds = smem;                                   // [rows8][DLD]  Z - U (rows >= K zero)
+    double* As = Ds + (size_t)rows8 * DLD;               // STAGES x [rows8][ALD]
+    uint64_t* full = reinterpret_cast<uint64_t*>(As + (size_t)STAGES * astage);
+    uint64_t* empty = full + STAGES;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, lr = lane >> 2, lc = lane & 3;
+    const int64_t C3 = 3 * ld;
+    const int64_t my_tiles = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int64_t total_all = my_tiles * iters * nslab;  // slabs this CTA consumes over its whole life
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < STAGES; ++i) {
+            mbar_init(full + i, 1);
+            mbar_init(empty + i, Cfg::WM * Cfg::WN);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    // producer state (thread 0): next slab to issue
+    int64_t issued = 0;
+    int pst = 0, pslab = 0;
+    uint32_t pwrap = 0;
+    auto issue = [&]() {   // slab `issued` -> stage pst; from the second lap on the stage must have been released
+        if (issued >= STAGES) mbar_wait(empty + pst, pwrap ^ 1u);
+        mbar_arrive_expect_tx(full + pst, slab_bytes);
+        bulk_g2s(As + (size_t)pst * astage, Hpk + (size_t)pslab * astage, slab_bytes, full + pst);
+        ++issued;
+        if (++pst == STAGES) { pst = 0; pwrap ^= 1u; }
+        if (++pslab == nslab) pslab = 0;
+    };
+    if (threadIdx.x == 0)
+        for (int i = 0; i < STAGES && issued < total_all; ++i) issue();
+    // consumer state: next slab to use
+    int cst = 0;
+    uint32_t cwrap = 0;
+    bool first = true;   // no refill before the very first step (the prologue filled every stage)
+    const double* afrag = As + (mt0 * 8 + lr) * ALD + lc;
+    const double* bfrag = Ds + lc * DLD + lr;
+    double* down = Ds + 2 * lc;   // + k * DLD + d * 8: the thread's own entries of D
+
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const int64_t n = tile * Cfg::NV + 2 * lc;   // the thread's two vertices
+        const bool ok0 = n < N, ok1 = n + 1 < N;
+        const bool inb = live && n < ld;
+        // ---- tile load: every thread fetches its own (k, 2 vertices, xyz) entries of Z and U
+        double u[MTN][3][2];
+#pragma unroll
+        for (int i = 0; i < MTN; ++i) {
+            const int k = (mt0 + i) * 8 + lr;
+#pragma unroll
+            for (int d = 0; d < 3; ++d) {
+                double2 z = make_double2(0.0, 0.0), uu = z;
+                if (inb && k < K) {
+                    const int64_t off = (int64_t)k * C3 + (int64_t)d * ld + n;
+                    z = ld2(Z + off);
+                    uu = ld2(U + off);
+                }
+                u[i][d][0] = uu.x;
+                u[i][d][1] = uu.y;
+                if (live && k < rows8) st2(down + k * DLD + d * 8, make_double2(z.x - uu.x, z.y - uu.y));   // k >= K: zeros
+            }
+        }
+        double acc[MTN][3][2];
+        auto load_b0 = [&](int i) {
+            const int k = (mt0 + i) * 8 + lr;
+#pragma unroll
+            for (int d = 0; d < 3; ++d) {
+                double2 b0 = make_double2(0.0, 0.0);
+                if (inb && k < K) b0 = ld2(B0 + (int64_t)k * C3 + (int64_t)d * ld + n);
+                acc[i][d][0] = b0.x;
+                acc[i][d][1] = b0.y;
+            }
+        };
+#pragma unroll
+        for (int i = 0; i < MTN; ++i) load_b0(i);
+        __syncthreads();   // D of this tile is complete (and every warp is done with the previous tile's D)
+        for (int it = 0; it < iters; ++it) {
+            for (int s = 0; s < nslab; ++s) {
+                if (threadIdx.x == 0 && !first && issued < total_all) issue();   // refill the stage released one step ago
+                first = false;
+                mbar_wait(full + cst, cwrap);
+                const double* as = afrag + cst * astage;
+                const double* ds = bfrag + s * Cfg::BK * DLD;
+#pragma unroll
+                for (int kk = 0; kk < Cfg::BK / 4; ++kk) {
+                    double b[3];
+#pragma unroll
+                    for (int d = 0; d < 3; ++d) b[d] = ds[kk * 4 * DLD + d * 8];
+#pragma unroll
+                    for (int i = 0; i < MTN; ++i) {
+                        const double a = as[i * 8 * ALD + kk * 4];
+#pragma unroll
+                        for (int d = 0; d < 3; ++d) dmma(acc[i][d][0], acc[i][d][1], a, b[d]);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(empty + cst);
+                if (++cst == STAGES) { cst = 0; cwrap ^= 1u; }
+            }
+            __syncthreads();  // every warp has finished reading D for this iteration
+
+            // ---- epilogue: prox + dual update on the thread's own entries
+            const bool last = it == iters - 1;
+            double2 lam[MTN];
+#pragma unroll
+            for (int i = 0; i < MTN; ++i) {
+                const int k = (mt0 + i) * 8 + lr;
+                lam[i] = (inb && k < K) ? ld2(Lambda + (int64_t)k * ld + n) : make_double2(0.0, 0.0);
+            }
+#pragma unroll
+            for (int i = 0; i < MTN; ++i) {
+                const int k = (mt0 + i) * 8 + lr;
+                const bool on = inb && k < K;
+                const int64_t base = (int64_t)k * C3 + n;
+                double2 v[3];
+#pragma unroll
+                for (int d = 0; d < 3; ++d) {   // V = C + U
+                    v[d].x = acc[i][d][0] + u[i][d][0];
+                    v[d].y = acc[i][d][1] + u[i][d][1];
+                }
+                if (!last) load_b0(i);          // acc[i] is consumed: start the next iteration's C = B0 + ...
+                if (on) {
+                    const double sh0 = prox_shrink(v[0].x, v[1].x, v[2].x, lam[i].x, inv_rho);
+                    const double sh1 = prox_shrink(v[0].y, v[1].y, v[2].y, lam[i].y, inv_rho);
+#pragma unroll
+                    for (int d = 0; d < 3; ++d) {
+                        double2 z, u2;
+                        z.x = ok0 ? v[d].x * sh0 : 0.0;
+                        z.y = ok1 ? v[d].y * sh1 : 0.0;
+                        u2.x = ok0 ? v[d].x - z.x : 0.0;
+                        u2.y = ok1 ? v[d].y - z.y : 0.0;
+                        u[i][d][0] = u2.x;
+                        u[i][d][1] = u2.y;
+                        if (last) {
+                            st2(U + base + (int64_t)d * ld, u2);
+                            st2(Z + base + (int64_t)d * ld, z);
+                        } else {
+                            st2(down + k * DLD + d * 8, make_double2(z.x - u2.x, z.y - u2.y));
+                        }
+                    }
+                }
+            }
+            if (!last) __syncthreads();  // the new D is complete before any warp multiplies with it
+        }
+    }
+}
+
+template <int MT>
+__global__ void __launch_bounds__(AdmmTma::THREADS, AdmmTma::CTAS)
+admm_tma_kernel(const double* __restrict__ Hpk, const double* __restrict__ B0, double* __restrict__ Z, double* __restrict__ U,
+                const double* __restrict__ Lambda, int K, int64_t N, int64_t ld, double inv_rho, int iters, int64_t ntiles) {
+    extern __shared__ __align__(128) double smem[];
+    int mt0, mtn;
+    int wm = threadIdx.x >> 5;
+    const int slot = (blockIdx.x / max(1u, gridDim.x / 2)) & 1;   // co-resident CTAs: 7-tile warps on different sub-partitions
+    wm = (wm + 2 * slot) % AdmmTma::WM;
+    mtile_range(((K + 7) & ~7) >> 3, AdmmTma::WM, wm, mt0, mtn);
+    const bool live = mtn > 0;
+    if (!live) mt0 = 0;
+    if (mtn == MT) admm_tma_body<MT, MT>(smem, Hpk, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live);
+    else admm_tma_body<MT, (MT > 1 ? MT - 1 : 1)>(smem, Hpk, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live);
+}
+
+static size_t admm_tma_smem_bytes(int64_t K) {
+    const int64_t rows8 = (K + 7) & ~7LL;
+    return ((size_t)rows8 * AdmmTma::DLD + (size_t)rows8 * AdmmTma::STAGES * AdmmTma::ALD) * sizeof(double) + 2 * AdmmTma::STAGES * 8;
+}
+
 template <class Cfg, int MT>
 __global__ void __launch_bounds__(Cfg::THREADS, Cfg::CTAS)
 admm_solve_kernel(const double* __restrict__ Hr, int64_t ldh, const double* __restrict__ B0, double* __restrict__ Z,
@@ -362,10 +599,47 @@ static int launch_admm_layout(const double* Hr, int64_t ldh, const double* B0, d
     }
 }
 
+template <int MT>
+static int launch_admm_tma_mt(const double* Hpk, const double* B0, double* Z, double* U, const double* Lambda, int64_t K, int64_t N,
+                              int64_t ld, double inv_rho, int iters, cudaStream_t st) {
+    const size_t smem = admm_tma_smem_bytes(K);
+    ASB_CUDA(cudaFuncSetAttribute(admm_tma_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t ntiles = cdiv(ld, AdmmTma::NV);
+    const unsigned grid = (unsigned)std::min<int64_t>(ntiles, (int64_t)AdmmTma::CTAS * sm_count());
+    admm_tma_kernel<MT><<<grid, AdmmTma::THREADS, smem, st>>>(Hpk, B0, Z, U, Lambda, (int)K, N, ld, inv_rho, iters, ntiles);
+    ASB_LAUNCH_CHECK();
+    return ASB_OK;
+}
+
+// bytes of the slab-major copy of Hr the TMA layout streams from
+static size_t admm_pack_bytes(int64_t K) {
+    const int64_t rows8 = (K + 7) & ~7LL;
+    return (size_t)(rows8 / 8) * rows8 * AdmmTma::ALD * sizeof(double);
+}
+
+static int launch_admm_tma(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda, int64_t K,
+                           int64_t N, int64_t ld, double inv_rho, int iters, double* pack, cudaStream_t st) {
+    const int rows8 = (int)((K + 7) & ~7LL), nslab = rows8 / 8;
+    admm_pack_kernel<<<64, 256, 0, st>>>(Hr, ldh, rows8, nslab, pack);
+    ASB_LAUNCH_CHECK();
+    switch ((int)cdiv(cdiv(K, 8), AdmmTma::WM)) {
+#define ASB_ADMM_CASE(MT) case MT: return launch_admm_tma_mt<MT>(pack, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+        ASB_ADMM_CASE(1) ASB_ADMM_CASE(2) ASB_ADMM_CASE(3) ASB_ADMM_CASE(4) ASB_ADMM_CASE(5) ASB_ADMM_CASE(6) ASB_ADMM_CASE(7)
+        default: return launch_admm_tma_mt<8>(pack, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+#undef ASB_ADMM_CASE
+    }
+}
+
+static int admm_layout() {
+    static const int layout = env_int("ASB_ADMM_LAYOUT", ASB_ADMM_LAYOUT_DEFAULT);   // 5: TMA Pair, 4 / 416: Pair, 12 / 1216: Wide, 16: Tall
+    return layout;
+}
+
 static int launch_admm(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda,
-                       int64_t K, int64_t N, int64_t ld, double inv_rho, int iters, cudaStream_t st) {
-    static const int layout = env_int("ASB_ADMM_LAYOUT", ASB_ADMM_LAYOUT_DEFAULT);   // 4 / 416: Pair, 12 / 1216: Wide, 16: Tall
+                       int64_t K, int64_t N, int64_t ld, double inv_rho, int iters, double* pack, cudaStream_t st) {
+    const int layout = admm_layout();
     constexpr size_t SMEM_MAX = 227 * 1024;   // a layout whose tile does not fit at this K falls through to Pair (139 KB at K = 256)
+    if (layout == 5 && pack) return launch_admm_tma(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, pack, st);
     if (layout == 16 && admm_smem_bytes<AdmmTall>(K) <= SMEM_MAX)
         return launch_admm_layout<AdmmTall>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
     if (layout == 8) return launch_admm_layout<AdmmDuo>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
@@ -384,17 +658,27 @@ using namespace asb;
 
 extern "C" {
 
-int asb_admm_solve(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda, int64_t K,
-                   int64_t N, int64_t ld, double inv_rho, int64_t iters, asb_stream_t stream) {
+int64_t asb_admm_workspace_bytes(int64_t K) { return K > 0 && K <= 256 ? (int64_t)admm_pack_bytes(K) : 0; }
+
+int asb_admm_solve_ws(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda, int64_t K,
+                      int64_t N, int64_t ld, double inv_rho, int64_t iters, void* ws, asb_stream_t stream) {
     ASB_REQUIRE(Hr && B0 && Z && U && Lambda && K > 0 && K <= 256 && N > 0 && ld >= N && ld % 32 == 0,
                 "admm_solve: bad arguments (K <= 256)");
     ASB_REQUIRE(ldh % 2 == 0 && ((uintptr_t)Hr % 16 == 0), "admm_solve: Hr must be 16-byte aligned with even ldh");
     ASB_REQUIRE(ldh >= ((K + 15) & ~15LL), "admm_solve: Hr must be zero-padded to ceil8(K) rows x ceil16(K) columns");
     ASB_REQUIRE(iters >= 0 && iters < (1 << 20), "admm_solve: bad iteration count");
+    ASB_REQUIRE(!ws || (uintptr_t)ws % 16 == 0, "admm_solve: workspace must be 16-byte aligned");
     if (iters == 0) return ASB_OK;
-    const cudaStream_t st = S(stream);
-    const int it = (int)iters;
-    return launch_admm(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, it, st);
+    return launch_admm(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, (int)iters, reinterpret_cast<double*>(ws), S(stream));
+}
+
+int asb_admm_solve(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda, int64_t K,
+                   int64_t N, int64_t ld, double inv_rho, int64_t iters, asb_stream_t stream) {
+    // workspace-free form: the slab-major copy of Hr lives in a per-process device buffer (786 KB at K = 256), so calls of
+    // this form must not overlap on different streams; asb_admm_solve_ws has no such restriction
+    static void* pack = nullptr;
+    if (!pack && admm_layout() == 5) ASB_CUDA(cudaMalloc(&pack, admm_pack_bytes(256)));
+    return asb_admm_solve_ws(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, pack, stream);
 }
 
 int asb_admm_iter(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda, int64_t K,

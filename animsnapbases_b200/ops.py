@@ -41,6 +41,7 @@ class CudaOps:
         self._ws = {}          # scratch per stream
         self._side = None      # side stream of fork() / join()
         self._ws2 = None
+        self._admm_ws = None
         self.timers = None
 
     # ------------------------------------------------------------------ plumbing
@@ -310,8 +311,11 @@ class CudaOps:
             Hp = self.zeros((k8, k8))
             Hp[:K, :K] = Hr[:K, :K]
             Hr = Hp
-        self._call("asb_admm_solve", self._p(Hr), Hr.stride(0), self._p(B0), self._p(Z), self._p(U), self._p(Lambda), K, N, ld,
-                   float(inv_rho), int(iters))
+        nb = int(self.lib.asb_admm_workspace_bytes(int(K)))
+        if self._admm_ws is None or self._admm_ws.numel() < nb:
+            self._admm_ws = torch.empty(nb + 256, dtype=torch.uint8, device=self.device)
+        self._call("asb_admm_solve_ws", self._p(Hr), Hr.stride(0), self._p(B0), self._p(Z), self._p(U), self._p(Lambda), K, N, ld,
+                   float(inv_rho), int(iters), self._p(self._admm_ws))
 
     # ------------------------------------------------------------------ small dense
     def gram_small(self, W, F, K, diag_add, G):

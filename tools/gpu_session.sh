@@ -8,6 +8,9 @@ for step in "$@"; do
     scale)  timeout 1500 python -m pytest tests/test_gpu_scale.py -q -m gpu -rxXs > gpurun_out/scale.log 2>&1; echo "scale rc=$?"; tail -15 gpurun_out/scale.log ;;
     geo)    for t in 1 0; do ASB_MF_TALL=$t timeout 600 python tools/kbench.py --geo 1000 1000 >> gpurun_out/geo.log 2>&1; done; cat gpurun_out/geo.log | tail -4 ;;
     bench1) timeout 900 python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/bench1.json 2> gpurun_out/bench1.err; echo "bench1 rc=$?"; tail -c 3000 gpurun_out/bench1.json; tail -5 gpurun_out/bench1.err ;;
+    bench1e) timeout 1200 python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/bench1e.json 2> gpurun_out/bench1e.err; echo "bench1e rc=$?"; tail -c 3500 gpurun_out/bench1e.json; tail -5 gpurun_out/bench1e.err ;;
+    presets) for c in bunny_splocs armadillo_splocs bar_deim synthetic_sample; do timeout 600 python bench.py --config $c --steps 3 --warmup 3 > gpurun_out/bench_$c.json 2> gpurun_out/bench_$c.err; echo "$c rc=$?"; tail -c 1800 gpurun_out/bench_$c.json; tail -3 gpurun_out/bench_$c.err; done ;;
+    u2)     timeout 900 python bench.py --unit pod_deim --steps 2 > gpurun_out/bench_pod_deim.json 2> gpurun_out/bench_pod_deim.err; echo "u2 rc=$?"; tail -c 3000 gpurun_out/bench_pod_deim.json; tail -5 gpurun_out/bench_pod_deim.err ;;
     *) echo "unknown step $step" ;;
   esac
 done
