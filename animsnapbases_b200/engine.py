@@ -8,6 +8,7 @@ kept replicated; argmax steps become a (value, index) pair reduction with the np
 """
 from __future__ import annotations
 
+import os as _os
 from dataclasses import dataclass
 
 import numpy as np
@@ -200,27 +201,74 @@ def deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1
     idx = ops.zeros((1,), I64)
     s = ops.zeros((1, ld)) if local_support else None
     pick = _Picker(ops, comm, F)
+    trace = _Trace(ops) if _os.environ.get("ASB_TRACE_DEFLATE") and getattr(ops, "name", "") == "cuda" else None
     k0 = 0
     for k in range(K):
+        if trace is not None:
+            trace.mark("start")
         ops.argmax_first(e, N, row0, val, idx)
         pick(R, N, val, idx, row0, W, k0, C, k - k0, traj)
         picked[k:k + 1].copy_(idx)
         ops.traj_rank1(traj, F, local_support, W, k, k0, coef, scal)
         picked_ev = ops.record_event() if local_support else None
+        if trace is not None:
+            trace.mark("picked")
         ops.deflate_gemv(R, N, W, k, g)
+        if trace is not None:
+            trace.mark("gemv")
         if local_support:
             # the heat-method query of the picked vertex (single source, latency bound, replicated on every rank) runs on the
             # side stream beside the HBM-bound pass.  It is queued AFTER the pass (r01 queued its ~75 launches first: 2 ms of
             # host time per component during which the main stream sat idle) and as ONE CUDA-graph launch.
             with ops.fork(after=picked_ev):
+                if trace is not None:
+                    trace.mark("geo0")
                 geodesic.support_single(idx, 0, 1.0, dmin, dmax, row0, N, s)
+                if trace is not None:
+                    trace.mark("geo1")
             ops.join()
+        if trace is not None:
+            trace.mark("joined")
         ops.deflate_finish(g, C, k, k0, coef, s[0] if local_support else None, scal, e, N, meas[k])
+        if trace is not None:
+            trace.mark("finished")
         if k - k0 + 1 == block or k == K - 1:
             ops.rank_update(R, N, W, C, k0, k - k0 + 1, e)
             k0 = k + 1
+        if trace is not None:
+            trace.mark("end")
     _reduce_norms(comm, meas)
+    if trace is not None:
+        trace.report()
     return C, W, meas, picked, (R if keep_residual else None)
+
+
+class _Trace:
+    """ASB_TRACE_DEFLATE=1: CUDA events at the stations of a deflation step (on whichever stream is current when they are
+    marked); `report` prints the mean time between consecutive stations.  Diagnostic only."""
+
+    def __init__(self, ops):
+        self.ops, self.rows, self.cur = ops, [], None
+
+    def mark(self, name):
+        import torch
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record(torch.cuda.current_stream(self.ops.device))
+        if name == "start":
+            self.cur = {}
+            self.rows.append(self.cur)
+        self.cur[name] = ev
+
+    def report(self):
+        self.ops.synchronize()
+        pairs = [("start", "picked"), ("picked", "gemv"), ("geo0", "geo1"), ("picked", "geo0"), ("gemv", "joined"),
+                 ("joined", "finished"), ("finished", "end"), ("start", "end")]
+        out = {}
+        for a, b in pairs:
+            v = [r[a].elapsed_time(r[b]) for r in self.rows if a in r and b in r]
+            if v:
+                out[a + "->" + b] = round(float(np.mean(v)), 4)
+        print("[deflate trace, ms per component, %d components] %s" % (len(self.rows), out), flush=True)
 
 
 class _Picker:
@@ -578,13 +626,57 @@ def pod_per_row(ops, comm, X, shard, p, k_desired):
 
 
 # ====================================================================================== post-processing (k18)
-def orthogonalize_rows(ops, comm, T, shard, K):
-    """Per-dimension orthonormalisation of the K rows of T[:, d, :] (economic QR of the (N x K) matrix,
-    snapbases/constraintsComponents.py:431-433) by CGS2: Q equals LAPACK's up to the sign of each column."""
+def orthogonalize_rows(ops, comm, T, shard, K, method="cholqr"):
+    """Per-dimension orthonormalisation of the K rows of T[:, d, :] (economic QR of the (N x K) matrix A = T_d^T,
+    snapbases/constraintsComponents.py:431-433): the rows become Q^T, equal to LAPACK's Q up to the sign of each column.
+
+    Shifted CholeskyQR3: three times { K x K Gram T_d T_d^T on the DMMA pipe, ONE all-reduce, replicated Cholesky
+    G = L L^T, T_d <- L^-1 T_d as a K x K x N DMMA GEMM }.  The first pass factors G + s I with s = 11 (N K + K (K + 1)) eps
+    |A|_2^2, which succeeds for condition numbers up to ~1/eps (un-standardised modes all contain the mean shape:
+    sigma_1 / sigma_K ~ 1e8 is normal here) and leaves a matrix CholeskyQR2 finishes to machine orthogonality.  L^-1 is lower
+    triangular, so every pass is a Gram-Schmidt-ordered recombination and the product of the three factors is the R of the QR
+    factorisation.  9 GEMM launches and 3 all-reduces per dimension instead of the 6 K launches and 4 K all-reduces of the
+    BLAS-2 CGS2 loop (kept as the fallback when the final K x K orthogonality check fails)."""
+    if method == "cgs2" or K < 2:
+        return orthogonalize_rows_cgs2(ops, comm, T, shard, K)
+    ld = T.shape[2]
+    Kp = (K + 1) // 2 * 2
+    eps = float(np.finfo(np.float64).eps)
+    tmp = ops.empty((K, ld))
+    Li = ops.zeros((K, Kp))
+    eye = torch.eye(K, dtype=F64, device=T.device)
+    for d in range(3):
+        A = T[:, d, :]
+        ok = True
+        for it in range(3):
+            G = ops.gemm_nt(A, K, A, K, ld, symmetric=True)
+            comm.allreduce_sum(G)
+            G = G[:, :K]
+            if it == 0:
+                lmax = float(torch.linalg.eigvalsh(G)[-1].item())
+                G = G + (11.0 * (shard.n_global * K + K * (K + 1.0)) * eps * lmax) * eye
+            L, info = torch.linalg.cholesky_ex(G)
+            if int(info.item()) != 0:
+                ok = False
+                break
+            Li[:, :K] = torch.linalg.solve_triangular(L, eye, upper=False)
+            ops.gemm_nn(Li, K, K, A, ld, 1.0, tmp)
+            A.copy_(tmp)
+        if ok:
+            G = ops.gemm_nt(A, K, A, K, ld, symmetric=True)
+            comm.allreduce_sum(G)
+            ok = float((G[:, :K] - eye).abs().max().item()) < 1e-11
+        if not ok:                              # keeps the triangular structure: finish with Gram-Schmidt sweeps
+            orthogonalize_rows_cgs2(ops, comm, T, shard, K, dims=(d,))
+    return T
+
+
+def orthogonalize_rows_cgs2(ops, comm, T, shard, K, dims=(0, 1, 2)):
+    """BLAS-2 classical Gram-Schmidt with re-orthogonalisation, row by row (r01 path; fallback of orthogonalize_rows)."""
     N = shard.n
     h = ops.zeros((max(K, 1),))
     nrm2 = ops.zeros((1,))
-    for d in range(3):
+    for d in dims:
         for k in range(K):
             for _ in range(2):
                 if k > 0:

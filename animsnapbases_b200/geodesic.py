@@ -172,7 +172,10 @@ class HeatGeodesics:
                 graph = torch.cuda.CUDAGraph()
                 timers, ops.timers = ops.timers, None                               # no per-launch timing events inside a capture
                 try:
-                    with torch.cuda.graph(graph):
+                    import os
+                    prio = int(os.environ.get("ASB_SIDE_PRIORITY", "0"))   # kernel nodes inherit the capture stream's priority
+                    cap = torch.cuda.Stream(ops.device, priority=prio)
+                    with torch.cuda.graph(graph, stream=cap):
                         self.support(sidx, mode, lam, dmin, dmax, row0, nloc, sout)
                 finally:
                     ops.timers = timers

@@ -110,7 +110,9 @@ class CudaOps:
         current stream -- or, with `after` (a recorded CUDA event), only after that event; `join()` makes the current
         stream wait for them."""
         if self._side is None:
-            self._side = torch.cuda.Stream(self.device)   # default priority: priority=-1 measured no better (r01: 17.8 s vs 17.6 s)
+            import os
+            prio = int(os.environ.get("ASB_SIDE_PRIORITY", "0"))     # -1: the side stream's CTAs are dispatched first
+            self._side = torch.cuda.Stream(self.device, priority=prio)
         if after is not None:
             self._side.wait_event(after)
         else:

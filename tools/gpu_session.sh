@@ -11,6 +11,11 @@ for step in "$@"; do
     bench1e) timeout 1200 python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/bench1e.json 2> gpurun_out/bench1e.err; echo "bench1e rc=$?"; tail -c 3500 gpurun_out/bench1e.json; tail -5 gpurun_out/bench1e.err ;;
     presets) for c in bunny_splocs armadillo_splocs bar_deim synthetic_sample; do timeout 600 python bench.py --config $c --steps 3 --warmup 3 > gpurun_out/bench_$c.json 2> gpurun_out/bench_$c.err; echo "$c rc=$?"; tail -c 1800 gpurun_out/bench_$c.json; tail -3 gpurun_out/bench_$c.err; done ;;
     u2)     timeout 900 python bench.py --unit pod_deim --steps 2 > gpurun_out/bench_pod_deim.json 2> gpurun_out/bench_pod_deim.err; echo "u2 rc=$?"; tail -c 3000 gpurun_out/bench_pod_deim.json; tail -5 gpurun_out/bench_pod_deim.err ;;
+    trace)  for pr in 0 -1; do echo "== side priority $pr"; ASB_SIDE_PRIORITY=$pr ASB_TRACE_DEFLATE=1 timeout 600 python bench.py --splocs-iters 0 --steps 2 --warmup 1 --no-e2e --no-cpu-baseline 2>&1 | grep -o "\[deflate trace.*\|\"phase_ms_per_step\": {[^}]*}" | tail -3; done ;;
+    admm)   if ASB_ADMM_LAYOUT=5 timeout 180 python -m pytest tests/test_gpu_ops.py -x -q -m gpu -k admm > gpurun_out/admm5_tests.log 2>&1; then
+              tail -2 gpurun_out/admm5_tests.log
+              for l in 5 4; do ASB_ADMM_LAYOUT=$l timeout 300 python tools/kbench.py --only admm 2>&1 | grep admm_solve_x10 | sed "s/^/layout $l: /"; done
+            else echo "layout 5 tests FAILED"; tail -30 gpurun_out/admm5_tests.log; fi ;;
     *) echo "unknown step $step" ;;
   esac
 done
