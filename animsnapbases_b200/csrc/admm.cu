@@ -342,48 +342,96 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                  : "memory");
 }
 
-struct AdmmTma {
-    static constexpr int WM = 4, WN = 1, CTAS = 2, BK = 8, STAGES = 3, ALD = 12, THREADS = 128, NV = 8, NC = 24, DLD = 28;
+// Shapes of the bulk-copy layouts.  G groups of 4 row-warps per CTA; BK columns of Hr per slab, staged [row][ALD]:
+// ALD = 12 for BK = 8 and ALD = 4 for BK = 4 are the strides at which the 64-bit A-fragment loads of a half-warp
+// (rows lr = 0..3, columns lc = 0..3) touch 16 distinct 8-byte slots.
+template <int G_, bool UREG_, int BK_>
+struct AdmmTmaCfg {
+    static constexpr int G = G_;                       // groups (vertex tiles in flight) per CTA
+    static constexpr bool UREG = UREG_;                // dual U in registers (else through L2 every iteration)
+    static constexpr int BK = BK_;
+    static constexpr int ALD = BK_ == 8 ? 12 : 4;
+    static constexpr int STAGES = BK_ == 8 ? 3 : 4;
+    static constexpr int WM = 4, NV = 8, NC = 24, DLD = 28;
+    static constexpr int THREADS = 128 * G_;
+    static constexpr int CTAS = G_ == 1 ? 2 : 1;       // CTAs per SM
+};
+using AdmmTmaPair = AdmmTmaCfg<1, true, 8>;    // 5: two CTAs per SM, 4 warps each, U in registers (255 registers)
+using AdmmTmaDuet = AdmmTmaCfg<2, true, 8>;    // 6: one CTA per SM, two groups that can hold a phase offset
+using AdmmTmaTrio = AdmmTmaCfg<3, false, 4>;   // 7: one CTA per SM, THREE free-running groups (12 warps, <= 168 registers, U
+                                               //    through L2): a lone warp per SM sub-partition issues one DMMA per ~37
+                                               //    cycles, two reach ~18 -- with three groups two are always in their GEMM
+                                               //    phase while the third runs its FP64 prox epilogue
+struct AdmmTma {                               // what the host side needs without a layout
+    static constexpr int NV = 8;
 };
 
-// Hpk[slab][row][0..11]: columns 8 slab .. 8 slab + 7 of Hr row `row`, then 4 zeros
-__global__ void admm_pack_kernel(const double* __restrict__ Hr, int64_t ldh, int rows8, int nslab, double* __restrict__ Hpk) {
-    const int total = nslab * rows8 * AdmmTma::ALD;
+// Hpk[slab][row][0..ALD): columns BK slab .. BK slab + BK - 1 of Hr row `row`, then zeros
+__global__ void admm_pack_kernel(const double* __restrict__ Hr, int64_t ldh, int rows8, int nslab, int bk, int ald,
+                                 double* __restrict__ Hpk) {
+    const int total = nslab * rows8 * ald;
     for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
-        const int c = t % AdmmTma::ALD, r = (t / AdmmTma::ALD) % rows8, sl = t / (AdmmTma::ALD * rows8);
-        Hpk[t] = c < AdmmTma::BK ? Hr[(int64_t)r * ldh + sl * AdmmTma::BK + c] : 0.0;
+        const int c = t % ald, r = (t / ald) % rows8, sl = t / (ald * rows8);
+        Hpk[t] = c < bk ? Hr[(int64_t)r * ldh + sl * bk + c] : 0.0;
     }
 }
 
-template <int MT, int MTN>
-__device__ __forceinline__ void admm_tma_body(double* smem, const double* __restrict__ Hpk, const double* __restrict__ B0,
+// G = 1: the CTA is one group of 4 row-warps (two CTAs per SM).  G >= 2: ONE CTA per SM holds G independent groups (warps
+// 4g .. 4g + 3), each with its own vertex tile, D, slab ring and named barrier -- the same work as G co-resident CTAs.  With
+// G = 2 the groups can additionally see each other's progress through two mbarriers and hold a fixed phase offset (`skew`):
+//   skew 0   free running;
+//   skew 1   a group may start iteration i only when its partner is half way through the slabs of its own current iteration;
+//   skew 2   strict alternation of the GEMM phases (one group on the pipe at a time).
+// Measured on B200 at 1M x K = 200, 10 iterations (profiles/r02_admm_layouts.md): skew changes nothing (98.7 / 98.8 ms) and
+// strict alternation costs 34 %, because ONE group cannot feed the pipe (a 4-warp CTA alone on the SM: 147.7 ms, 37 cycles
+// per DMMA and sub-partition): what the epilogue of one group needs beside it is TWO groups in their GEMM phase -> G = 3.
+template <class Cfg, int MT, int MTN>
+__device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __restrict__ Hpk, const double* __restrict__ B0,
                                               double* __restrict__ Z, double* __restrict__ U, const double* __restrict__ Lambda,
                                               int K, int64_t N, int64_t ld, double inv_rho, int iters, int64_t ntiles, int mt0,
-                                              bool live) {
-    using Cfg = AdmmTma;
-    constexpr int DLD = Cfg::DLD, ALD = Cfg::ALD, STAGES = Cfg::STAGES;
+                                              bool live, int skew) {
+    constexpr int G = Cfg::G, DLD = Cfg::DLD, ALD = Cfg::ALD, STAGES = Cfg::STAGES, BK = Cfg::BK;
+    constexpr bool UREG = Cfg::UREG;
+    constexpr int UR = UREG ? MTN : 1;
     const int rows8 = (K + 7) & ~7;
-    const int nslab = rows8 >> 3;
+    const int nslab = rows8 / BK;                         // rows8 is a multiple of 8, BK is 4 or 8
     const int astage = rows8 * ALD;
     const uint32_t slab_bytes = (uint32_t)astage * 8u;
-    double* Ds = smem;                                   // [rows8][DLD]  Z - U (rows >= K zero)
-    double* As = Ds + (size_t)rows8 * DLD;               // STAGES x [rows8][ALD]
-    uint64_t* full = reinterpret_cast<uint64_t*>(As + (size_t)STAGES * astage);
+    const int grp = G > 1 ? (int)(threadIdx.x >> 7) : 0;
+    const int gt = (int)threadIdx.x - 128 * grp;          // thread index inside the group
+    const size_t group_doubles = (size_t)rows8 * DLD + (size_t)STAGES * astage;
+    double* Ds = smem_all + grp * group_doubles;          // [rows8][DLD]  Z - U (rows >= K zero)
+    double* As = Ds + (size_t)rows8 * DLD;                // STAGES x [rows8][ALD]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_all + G * group_doubles);
+    uint64_t* full = bars + grp * 2 * STAGES;
     uint64_t* empty = full + STAGES;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, lr = lane >> 2, lc = lane & 3;
+    uint64_t* mid = bars + G * 2 * STAGES;                // mid[g]: progress signal of group g (G == 2)
+    const int lane = threadIdx.x & 31, lr = lane >> 2, lc = lane & 3;
     const int64_t C3 = 3 * ld;
-    const int64_t my_tiles = blockIdx.x < ntiles ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-    const int64_t total_all = my_tiles * iters * nslab;  // slabs this CTA consumes over its whole life
+    auto tiles_of = [&](int g) -> int64_t {
+        const int64_t first = (int64_t)blockIdx.x * G + g, step = (int64_t)gridDim.x * G;
+        return first < ntiles ? (ntiles - first + step - 1) / step : 0;
+    };
+    const int64_t my_tiles = tiles_of(grp);
+    const int64_t total_all = my_tiles * iters * nslab;   // slabs this group consumes over its whole life
+    const int64_t partner_iters = G == 2 ? tiles_of(grp ^ 1) * iters : 0;
+    auto group_sync = [&]() {
+        if (G > 1) asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
+        else __syncthreads();
+    };
     if (threadIdx.x == 0) {
-#pragma unroll
-        for (int i = 0; i < STAGES; ++i) {
-            mbar_init(full + i, 1);
-            mbar_init(empty + i, Cfg::WM * Cfg::WN);
+        for (int i = 0; i < G * STAGES; ++i) {
+            mbar_init(bars + (i / STAGES) * 2 * STAGES + (i % STAGES), 1);                    // full
+            mbar_init(bars + (i / STAGES) * 2 * STAGES + STAGES + (i % STAGES), Cfg::WM);      // empty
+        }
+        if (G == 2) {
+            mbar_init(mid + 0, Cfg::WM);
+            mbar_init(mid + 1, Cfg::WM);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    // producer state (thread 0): next slab to issue
+    // producer state (thread 0 of the group): next slab to issue
     int64_t issued = 0;
     int pst = 0, pslab = 0;
     uint32_t pwrap = 0;
@@ -395,22 +443,24 @@ __device__ __forceinline__ void admm_tma_body(double* smem, const double* __rest
         if (++pst == STAGES) { pst = 0; pwrap ^= 1u; }
         if (++pslab == nslab) pslab = 0;
     };
-    if (threadIdx.x == 0)
+    if (gt == 0)
         for (int i = 0; i < STAGES && issued < total_all; ++i) issue();
     // consumer state: next slab to use
     int cst = 0;
     uint32_t cwrap = 0;
     bool first = true;   // no refill before the very first step (the prologue filled every stage)
+    int64_t git = 0;     // iterations this group has started (over all its tiles)
+    const int sig_slab = skew == 2 ? nslab - 1 : (nslab - 1) / 2;   // the slab after which the group signals its progress
     const double* afrag = As + (mt0 * 8 + lr) * ALD + lc;
     const double* bfrag = Ds + lc * DLD + lr;
     double* down = Ds + 2 * lc;   // + k * DLD + d * 8: the thread's own entries of D
 
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (int64_t tile = (int64_t)blockIdx.x * G + grp; tile < ntiles; tile += (int64_t)gridDim.x * G) {
         const int64_t n = tile * Cfg::NV + 2 * lc;   // the thread's two vertices
         const bool ok0 = n < N, ok1 = n + 1 < N;
         const bool inb = live && n < ld;
         // ---- tile load: every thread fetches its own (k, 2 vertices, xyz) entries of Z and U
-        double u[MTN][3][2];
+        double u[UR][3][2];
 #pragma unroll
         for (int i = 0; i < MTN; ++i) {
             const int k = (mt0 + i) * 8 + lr;
@@ -422,8 +472,10 @@ __device__ __forceinline__ void admm_tma_body(double* smem, const double* __rest
                     z = ld2(Z + off);
                     uu = ld2(U + off);
                 }
-                u[i][d][0] = uu.x;
-                u[i][d][1] = uu.y;
+                if (UREG) {
+                    u[i % UR][d][0] = uu.x;
+                    u[i % UR][d][1] = uu.y;
+                }
                 if (live && k < rows8) st2(down + k * DLD + d * 8, make_double2(z.x - uu.x, z.y - uu.y));   // k >= K: zeros
             }
         }
@@ -440,16 +492,22 @@ __device__ __forceinline__ void admm_tma_body(double* smem, const double* __rest
         };
 #pragma unroll
         for (int i = 0; i < MTN; ++i) load_b0(i);
-        __syncthreads();   // D of this tile is complete (and every warp is done with the previous tile's D)
-        for (int it = 0; it < iters; ++it) {
+        group_sync();   // D of this tile is complete (and every warp is done with the previous tile's D)
+        for (int it = 0; it < iters; ++it, ++git) {
+            if (G == 2 && skew) {
+                // group 0 starts iteration a after group 1 signalled in its iteration a - 1; group 1 starts iteration b after
+                // group 0 signalled in ITS iteration b (no wait once the partner has run out of iterations)
+                const int64_t need = grp == 0 ? git - 1 : git;
+                if (need >= 0 && need < partner_iters) mbar_wait(mid + (grp ^ 1), (uint32_t)(need & 1));
+            }
             for (int s = 0; s < nslab; ++s) {
-                if (threadIdx.x == 0 && !first && issued < total_all) issue();   // refill the stage released one step ago
+                if (gt == 0 && !first && issued < total_all) issue();   // refill the stage released one step ago
                 first = false;
                 mbar_wait(full + cst, cwrap);
                 const double* as = afrag + cst * astage;
-                const double* ds = bfrag + s * Cfg::BK * DLD;
+                const double* ds = bfrag + s * BK * DLD;
 #pragma unroll
-                for (int kk = 0; kk < Cfg::BK / 4; ++kk) {
+                for (int kk = 0; kk < BK / 4; ++kk) {
                     double b[3];
 #pragma unroll
                     for (int d = 0; d < 3; ++d) b[d] = ds[kk * 4 * DLD + d * 8];
@@ -461,18 +519,38 @@ __device__ __forceinline__ void admm_tma_body(double* smem, const double* __rest
                     }
                 }
                 __syncwarp();
-                if (lane == 0) mbar_arrive(empty + cst);
+                if (lane == 0) {
+                    mbar_arrive(empty + cst);
+                    if (G == 2 && s == sig_slab) mbar_arrive(mid + grp);
+                }
                 if (++cst == STAGES) { cst = 0; cwrap ^= 1u; }
             }
-            __syncthreads();  // every warp has finished reading D for this iteration
+            group_sync();  // every warp has finished reading D for this iteration
 
-            // ---- epilogue: prox + dual update on the thread's own entries
+            // ---- epilogue: prox + dual update on the thread's own entries.  Lambda of all m-tiles is fetched up front (one L2
+            // latency); without the register copy the old dual U (L2 hits: written by this thread one iteration ago) runs
+            // UDEPTH m-tiles ahead of the arithmetic.
             const bool last = it == iters - 1;
             double2 lam[MTN];
 #pragma unroll
             for (int i = 0; i < MTN; ++i) {
                 const int k = (mt0 + i) * 8 + lr;
                 lam[i] = (inb && k < K) ? ld2(Lambda + (int64_t)k * ld + n) : make_double2(0.0, 0.0);
+            }
+            constexpr int UDEPTH = UREG ? 1 : (MTN < 2 ? MTN : 2);
+            double2 uo[UDEPTH][3];
+            auto fetch_u = [&](int i) {
+                const int k = (mt0 + i) * 8 + lr;
+#pragma unroll
+                for (int d = 0; d < 3; ++d) uo[i % UDEPTH][d] = make_double2(0.0, 0.0);
+                if (!inb || k >= K) return;
+                const int64_t base = (int64_t)k * C3 + n;
+#pragma unroll
+                for (int d = 0; d < 3; ++d) uo[i % UDEPTH][d] = ld2(U + base + (int64_t)d * ld);
+            };
+            if (!UREG) {
+#pragma unroll
+                for (int i = 0; i < UDEPTH; ++i) fetch_u(i);
             }
 #pragma unroll
             for (int i = 0; i < MTN; ++i) {
@@ -482,9 +560,10 @@ __device__ __forceinline__ void admm_tma_body(double* smem, const double* __rest
                 double2 v[3];
 #pragma unroll
                 for (int d = 0; d < 3; ++d) {   // V = C + U
-                    v[d].x = acc[i][d][0] + u[i][d][0];
-                    v[d].y = acc[i][d][1] + u[i][d][1];
+                    v[d].x = acc[i][d][0] + (UREG ? u[i % UR][d][0] : uo[i % UDEPTH][d].x);
+                    v[d].y = acc[i][d][1] + (UREG ? u[i % UR][d][1] : uo[i % UDEPTH][d].y);
                 }
+                if (!UREG && i + UDEPTH < MTN) fetch_u(i + UDEPTH);   // slot i % UDEPTH is free again
                 if (!last) load_b0(i);          // acc[i] is consumed: start the next iteration's C = B0 + ...
                 if (on) {
                     const double sh0 = prox_shrink(v[0].x, v[1].x, v[2].x, lam[i].x, inv_rho);
@@ -496,42 +575,46 @@ __device__ __forceinline__ void admm_tma_body(double* smem, const double* __rest
                         z.y = ok1 ? v[d].y * sh1 : 0.0;
                         u2.x = ok0 ? v[d].x - z.x : 0.0;
                         u2.y = ok1 ? v[d].y - z.y : 0.0;
-                        u[i][d][0] = u2.x;
-                        u[i][d][1] = u2.y;
-                        if (last) {
-                            st2(U + base + (int64_t)d * ld, u2);
-                            st2(Z + base + (int64_t)d * ld, z);
-                        } else {
-                            st2(down + k * DLD + d * 8, make_double2(z.x - u2.x, z.y - u2.y));
+                        if (UREG) {
+                            u[i % UR][d][0] = u2.x;
+                            u[i % UR][d][1] = u2.y;
                         }
+                        if (!UREG || last) st2(U + base + (int64_t)d * ld, u2);
+                        if (last) st2(Z + base + (int64_t)d * ld, z);
+                        else st2(down + k * DLD + d * 8, make_double2(z.x - u2.x, z.y - u2.y));
                     }
                 }
             }
-            if (!last) __syncthreads();  // the new D is complete before any warp multiplies with it
+            if (!last) group_sync();  // the new D is complete before any warp multiplies with it
         }
     }
 }
 
-template <int MT>
-__global__ void __launch_bounds__(AdmmTma::THREADS, AdmmTma::CTAS)
+template <class Cfg, int MT>
+__global__ void __launch_bounds__(Cfg::THREADS, Cfg::CTAS)
 admm_tma_kernel(const double* __restrict__ Hpk, const double* __restrict__ B0, double* __restrict__ Z, double* __restrict__ U,
-                const double* __restrict__ Lambda, int K, int64_t N, int64_t ld, double inv_rho, int iters, int64_t ntiles) {
+                const double* __restrict__ Lambda, int K, int64_t N, int64_t ld, double inv_rho, int iters, int64_t ntiles,
+                int skew) {
     extern __shared__ __align__(128) double smem[];
     int mt0, mtn;
-    int wm = threadIdx.x >> 5;
-    const int slot = (blockIdx.x / max(1u, gridDim.x / 2)) & 1;   // co-resident CTAs: 7-tile warps on different sub-partitions
-    wm = (wm + 2 * slot) % AdmmTma::WM;
-    mtile_range(((K + 7) & ~7) >> 3, AdmmTma::WM, wm, mt0, mtn);
+    int wm = (threadIdx.x >> 5) & 3;
+    // co-resident groups rotate the row-warp roles: the 7-tile warps (K = 200: 7,6,6,6) sit on different SM sub-partitions
+    const int slot = Cfg::G > 1 ? (int)(threadIdx.x >> 7) : (int)((blockIdx.x / max(1u, gridDim.x / 2)) & 1);
+    wm = (wm + (Cfg::G == 3 ? slot : 2 * slot)) % Cfg::WM;
+    mtile_range(((K + 7) & ~7) >> 3, Cfg::WM, wm, mt0, mtn);
     const bool live = mtn > 0;
     if (!live) mt0 = 0;
-    if (mtn == MT) admm_tma_body<MT, MT>(smem, Hpk, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live);
-    else admm_tma_body<MT, (MT > 1 ? MT - 1 : 1)>(smem, Hpk, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live);
+    if (mtn == MT) admm_tma_body<Cfg, MT, MT>(smem, Hpk, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live, skew);
+    else admm_tma_body<Cfg, MT, (MT > 1 ? MT - 1 : 1)>(smem, Hpk, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live, skew);
 }
 
+template <class Cfg>
 static size_t admm_tma_smem_bytes(int64_t K) {
     const int64_t rows8 = (K + 7) & ~7LL;
-    return ((size_t)rows8 * AdmmTma::DLD + (size_t)rows8 * AdmmTma::STAGES * AdmmTma::ALD) * sizeof(double) + 2 * AdmmTma::STAGES * 8;
+    return (size_t)Cfg::G * ((size_t)rows8 * Cfg::DLD + (size_t)rows8 * Cfg::STAGES * Cfg::ALD) * sizeof(double) +
+           (size_t)(Cfg::G * 2 * Cfg::STAGES + 2) * 8;
 }
+
 
 template <class Cfg, int MT>
 __global__ void __launch_bounds__(Cfg::THREADS, Cfg::CTAS)
@@ -599,36 +682,41 @@ static int launch_admm_layout(const double* Hr, int64_t ldh, const double* B0, d
     }
 }
 
-template <int MT>
+template <class Cfg, int MT>
 static int launch_admm_tma_mt(const double* Hpk, const double* B0, double* Z, double* U, const double* Lambda, int64_t K, int64_t N,
-                              int64_t ld, double inv_rho, int iters, cudaStream_t st) {
-    const size_t smem = admm_tma_smem_bytes(K);
-    ASB_CUDA(cudaFuncSetAttribute(admm_tma_kernel<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int64_t ntiles = cdiv(ld, AdmmTma::NV);
-    const unsigned grid = (unsigned)std::min<int64_t>(ntiles, (int64_t)AdmmTma::CTAS * sm_count());
-    admm_tma_kernel<MT><<<grid, AdmmTma::THREADS, smem, st>>>(Hpk, B0, Z, U, Lambda, (int)K, N, ld, inv_rho, iters, ntiles);
+                              int64_t ld, double inv_rho, int iters, int skew, cudaStream_t st) {
+    static const int solo = env_int("ASB_ADMM_TMA_SOLO", 0);   // experiment: one 4-warp CTA per SM (extra shared memory)
+    const size_t smem = admm_tma_smem_bytes<Cfg>(K) + ((Cfg::G == 1 && solo) ? 24 * 1024 : 0);
+    ASB_CUDA(cudaFuncSetAttribute(admm_tma_kernel<Cfg, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t ntiles = cdiv(ld, Cfg::NV);
+    const int64_t slots = Cfg::G > 1 ? sm_count() : (solo ? sm_count() : (int64_t)Cfg::CTAS * sm_count());
+    const unsigned grid = (unsigned)std::min<int64_t>(cdiv(ntiles, Cfg::G), slots);
+    admm_tma_kernel<Cfg, MT><<<grid, Cfg::THREADS, smem, st>>>(Hpk, B0, Z, U, Lambda, (int)K, N, ld, inv_rho, iters, ntiles, skew);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
 }
 
-// bytes of the slab-major copy of Hr the TMA layout streams from
+// bytes of the slab-major copy of Hr the bulk-copy layouts stream from (the larger of the two slab formats)
 static size_t admm_pack_bytes(int64_t K) {
     const int64_t rows8 = (K + 7) & ~7LL;
-    return (size_t)(rows8 / 8) * rows8 * AdmmTma::ALD * sizeof(double);
+    return (size_t)(rows8 / 8) * rows8 * 12 * sizeof(double);
 }
 
+template <class Cfg>
 static int launch_admm_tma(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda, int64_t K,
                            int64_t N, int64_t ld, double inv_rho, int iters, double* pack, cudaStream_t st) {
-    const int rows8 = (int)((K + 7) & ~7LL), nslab = rows8 / 8;
-    admm_pack_kernel<<<64, 256, 0, st>>>(Hr, ldh, rows8, nslab, pack);
+    const int rows8 = (int)((K + 7) & ~7LL), nslab = rows8 / Cfg::BK;
+    static const int skew = env_int("ASB_ADMM_SKEW", 0);
+    admm_pack_kernel<<<64, 256, 0, st>>>(Hr, ldh, rows8, nslab, Cfg::BK, Cfg::ALD, pack);
     ASB_LAUNCH_CHECK();
-    switch ((int)cdiv(cdiv(K, 8), AdmmTma::WM)) {
-#define ASB_ADMM_CASE(MT) case MT: return launch_admm_tma_mt<MT>(pack, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+    switch ((int)cdiv(cdiv(K, 8), Cfg::WM)) {
+#define ASB_ADMM_CASE(MT) case MT: return launch_admm_tma_mt<Cfg, MT>(pack, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, skew, st);
         ASB_ADMM_CASE(1) ASB_ADMM_CASE(2) ASB_ADMM_CASE(3) ASB_ADMM_CASE(4) ASB_ADMM_CASE(5) ASB_ADMM_CASE(6) ASB_ADMM_CASE(7)
-        default: return launch_admm_tma_mt<8>(pack, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
+        default: return launch_admm_tma_mt<Cfg, 8>(pack, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, skew, st);
 #undef ASB_ADMM_CASE
     }
 }
+
 
 static int admm_layout() {
     static const int layout = env_int("ASB_ADMM_LAYOUT", ASB_ADMM_LAYOUT_DEFAULT);   // 5: TMA Pair, 4 / 416: Pair, 12 / 1216: Wide, 16: Tall
@@ -639,7 +727,14 @@ static int launch_admm(const double* Hr, int64_t ldh, const double* B0, double* 
                        int64_t K, int64_t N, int64_t ld, double inv_rho, int iters, double* pack, cudaStream_t st) {
     const int layout = admm_layout();
     constexpr size_t SMEM_MAX = 227 * 1024;   // a layout whose tile does not fit at this K falls through to Pair (139 KB at K = 256)
-    if (layout == 5 && pack) return launch_admm_tma(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, pack, st);
+    if (pack) {   // bulk-copy layouts: 7 trio (default), 6 duet, 5 pair; a layout whose tiles do not fit at this K falls through
+        if (layout == 7 && admm_tma_smem_bytes<AdmmTmaTrio>(K) <= SMEM_MAX)
+            return launch_admm_tma<AdmmTmaTrio>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, pack, st);
+        if ((layout == 6 || layout == 7) && admm_tma_smem_bytes<AdmmTmaDuet>(K) <= SMEM_MAX)
+            return launch_admm_tma<AdmmTmaDuet>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, pack, st);
+        if (layout == 5 || layout == 6 || layout == 7)
+            return launch_admm_tma<AdmmTmaPair>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, pack, st);
+    }
     if (layout == 16 && admm_smem_bytes<AdmmTall>(K) <= SMEM_MAX)
         return launch_admm_layout<AdmmTall>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
     if (layout == 8) return launch_admm_layout<AdmmDuo>(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, st);
@@ -677,7 +772,7 @@ int asb_admm_solve(const double* Hr, int64_t ldh, const double* B0, double* Z, d
     // workspace-free form: the slab-major copy of Hr lives in a per-process device buffer (786 KB at K = 256), so calls of
     // this form must not overlap on different streams; asb_admm_solve_ws has no such restriction
     static void* pack = nullptr;
-    if (!pack && admm_layout() == 5) ASB_CUDA(cudaMalloc(&pack, admm_pack_bytes(256)));
+    if (!pack && admm_layout() >= 5 && admm_layout() <= 7) ASB_CUDA(cudaMalloc(&pack, admm_pack_bytes(256)));
     return asb_admm_solve_ws(Hr, ldh, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, pack, stream);
 }
 

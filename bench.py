@@ -331,8 +331,10 @@ def main():
         build(st)
     sync_all()
     # ---- timed region (device-resident inputs)
-    timed = ["asb_deflate_gemv", "asb_rank_update", "asb_admm_solve", "asb_gemm_nn", "asb_gemm_nt", "asb_weights_sweep",
-             "asb_component_centers", "asb_mf_solve", "asb_mf_solve_delta", "asb_support_map", "asb_vertex_energy"]
+    timed = ["asb_deflate_gemv", "asb_rank_update", "asb_admm_solve_ws", "asb_gemm_nn", "asb_gemm_nt", "asb_weights_sweep",
+             "asb_component_centers", "asb_mf_solve", "asb_mf_solve_delta", "asb_support_map", "asb_vertex_energy",
+             "asb_gram_small", "asb_spd_inverse", "asb_small_gemm", "asb_batched_dot", "asb_axpby", "asb_deflate_finish",
+             "asb_argmax_first", "asb_gather_traj", "asb_traj_rank1"]
     ops.time_kernels(timed)
     ops.reset_launch_count()
     clocks = ClockSampler(local_rank)
@@ -442,7 +444,7 @@ def main():
     per_step = {
         "asb_deflate_gemv": ("hbm", K * 8.0 * F * M),                       # K read passes over R
         "asb_rank_update": ("hbm", -(-K // args.block) * 2 * 8.0 * F * M),   # read + write pass per block of components
-        "asb_admm_solve": ("tensor", Is * Ia * 2.0 * K * K * M),             # Hr (Z - U), Ia iterations fused per launch
+        "asb_admm_solve_ws": ("tensor", Is * Ia * 2.0 * K * K * M),          # Hr (Z - U), Ia iterations fused per launch
         "asb_gemm_nn": ("tensor", Is * 2.0 * K * F * M),                     # B0 = (H^-1 W^T) X
         "asb_gemm_nt": ("tensor", (Is + 1) * (2.0 * F * K + K * (K + 1.0)) * M if Is else 0.0),   # P = X C^T, symmetric Q = C C^T
     }
@@ -459,12 +461,12 @@ def main():
                 tr = json.load(open(os.path.join(ROOT, "profiles", tf)))
                 w = tr["workload"]
                 if world == 1 and (w["vertices"], w["frames"], w["components"], w["admm_iters"]) == (N, F, K, Ia) \
-                        and dom in tr["per_launch_bytes"]:
-                    traffic = tr["per_launch_bytes"][dom]
+                        and dom.replace("_ws", "") in tr["per_launch_bytes"]:
+                    traffic = tr["per_launch_bytes"][dom.replace("_ws", "")]
                     break
             except Exception:
                 pass
-        common = {"kernel": dom, "bound": bound, "traffic": traffic, "avg_launch_ms": ktimes[dom][1] / ktimes[dom][0],
+        common = {"kernel": {"asb_admm_solve_ws": "asb_admm_solve"}.get(dom, dom), "bound": bound, "traffic": traffic, "avg_launch_ms": ktimes[dom][1] / ktimes[dom][0],
                   "launches": ktimes[dom][0], "work_per_launch": work / ktimes[dom][0]}
         if bound == "hbm":
             ach = work / tot_s / 1e9

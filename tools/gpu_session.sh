@@ -16,6 +16,17 @@ for step in "$@"; do
               tail -2 gpurun_out/admm5_tests.log
               for l in 5 4; do ASB_ADMM_LAYOUT=$l timeout 300 python tools/kbench.py --only admm 2>&1 | grep admm_solve_x10 | sed "s/^/layout $l: /"; done
             else echo "layout 5 tests FAILED"; tail -30 gpurun_out/admm5_tests.log; fi ;;
+    duet)   for sk in 1 2 0; do
+              if ASB_ADMM_LAYOUT=6 ASB_ADMM_SKEW=$sk timeout 180 python -m pytest tests/test_gpu_ops.py -x -q -m gpu -k admm > gpurun_out/admm6_$sk.log 2>&1; then
+                ASB_ADMM_LAYOUT=6 ASB_ADMM_SKEW=$sk timeout 300 python tools/kbench.py --only admm 2>&1 | grep admm_solve_x10 | sed "s/^/duet skew $sk: /"
+              else echo "duet skew $sk tests FAILED"; tail -20 gpurun_out/admm6_$sk.log; fi
+            done
+            ASB_ADMM_LAYOUT=5 ASB_ADMM_TMA_SOLO=1 timeout 300 python tools/kbench.py --only admm 2>&1 | grep admm_solve_x10 | sed "s/^/tma solo (1 CTA of 4 warps per SM): /" ;;
+    trio)   for l in 7 5; do
+              if ASB_ADMM_LAYOUT=$l timeout 180 python -m pytest tests/test_gpu_ops.py -x -q -m gpu -k admm > gpurun_out/admm$l.log 2>&1; then
+                ASB_ADMM_LAYOUT=$l timeout 300 python tools/kbench.py --only admm 2>&1 | grep admm_solve_x10 | sed "s/^/layout $l: /"
+              else echo "layout $l tests FAILED"; tail -20 gpurun_out/admm$l.log; fi
+            done ;;
     *) echo "unknown step $step" ;;
   esac
 done
