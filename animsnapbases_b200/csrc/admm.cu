@@ -20,6 +20,11 @@
 //   16   Tall    one CTA per SM, 16 warps = 8 row-warps x 2 vertex groups (<= 4 m-tiles per warp, 128 registers),
 //                U through L2                                                        105.2 ms
 //   8/81 Duo     two CTAs per SM of 8 row-warps x 1 vertex group (U through L2 / in registers)  115.7 / 106.8 ms
+//   5    TmaPair same tile as Pair; Hr streamed from a slab-major copy with ONE cp.async.bulk (TMA, SASS UBLKCP) per slab,
+//                handed over through mbarriers (no CTA barrier per slab), ring running on across tiles    96.6 ms  24.9 TFLOP/s   <- default (r02)
+//   6    TmaDuet one CTA per SM, two groups with an optional phase offset (ASB_ADMM_SKEW 0 / 1 / 2)       98.7 / 98.8 / 132.5 ms
+//   7    TmaTrio one CTA per SM, three groups (12 warps), U through L2, 4-column slabs                     111.1 ms
+//        (r02 measurements and what they rule out: profiles/r02_admm_layouts.md)
 // ASB_ADMM_LOCK=1 adds a per-SM epilogue mutex to the Pair layouts (keeps the two CTAs of an SM half a phase apart so one
 // runs the FP64 prox while the other owns the tensor pipe): 103.5 ms (4) / 104.6 ms (416) -- the two global atomics per
 // iteration cost what the overlap wins, so it is off by default.
@@ -31,7 +36,7 @@
 #include "dmma.cuh"
 #include <cstdlib>
 #ifndef ASB_ADMM_LAYOUT_DEFAULT
-#define ASB_ADMM_LAYOUT_DEFAULT 4
+#define ASB_ADMM_LAYOUT_DEFAULT 5
 #endif
 
 namespace asb {

@@ -369,6 +369,77 @@ def deflate_blocks(ops, comm, X, shard, p, num_blocks, block=8, keep_residual=Fa
     return C, W, table, el, rows.cpu().numpy(), (R if keep_residual else None)
 
 
+def deflate_blocks_with_St(ops, comm, X, shard, p, St, elems, tol, max_steps=None):
+    """`pca_blocks_with_St` (snapbases/constraintsComponents.py:156-271, global support): block deflation driven by the residual
+    in POSITION space.  While |R|_F > tol: v = the vertex with the largest energy of St R (sparse mat-mat on the device, 3 F
+    right-hand sides, partial products all-reduced) decides how many blocks follow -- one per element incident to v -- and
+    every block runs p rank-1 steps at the rows  idx * p + i  where idx is the reference's LOOP COUNTER over those elements,
+    not their ids (:203-209; a quirk the golden fixture pins).  Each step removes one frame-space direction from
+    every row, so the loop ends after about rank(X) steps.  R is explicit and updated after every block (asb_rank_update with
+    nb = p recomputes the energies exactly: |R| is compared with `tol` after every block, like the reference's norm(R)).
+    St: (|V| x ep) scipy sparse, replicated; elems: (e, nodes) host array of the constrained elements.
+    Returns C (nb p, 3, ld), W (F, Kp), table rows [count, idx, |R|_F, sigma_0..sigma_{p-1}], picked vertices."""
+    F, _, ld = X.shape
+    N, row0 = shard.n, shard.row0
+    assert N % p == 0 and row0 % p == 0, "block deflation needs whole elements per shard"
+    elems = np.asarray(elems)
+    cap = (max_steps if max_steps is not None else 2 * F + 4 * p) // p * p + p
+    Kp = (cap + 3) // 4 * 4
+    R = X.clone()
+    W = ops.zeros((F, Kp))
+    C = ops.zeros((cap, 3, ld))
+    meas = ops.zeros((cap, 3))
+    e = ops.vertex_energy(R, N)
+    g = ops.empty((3, ld))
+    traj = ops.zeros((3, F))
+    coef = ops.zeros((16,))
+    scal = ops.zeros((2,))
+    val = ops.zeros((1,))
+    idx = ops.zeros((1,), I64)
+    row_id = ops.zeros((1,), I64)
+    pick = _Picker(ops, comm, F)
+    csr, nv, L = square_csr_slice(ops, St, shard)
+    xb = ops.zeros((3 * F, L))
+    yb = ops.zeros((3 * F, L))
+    ev = ops.zeros((L,))
+
+    def norm_R():
+        t = e[:N].sum().reshape(1) if N else ops.zeros((1,))
+        comm.allreduce_sum(t)
+        return float(np.sqrt(max(float(t.item()), 0.0)))
+
+    table, verts = [], []
+    k = 0
+    nrm = norm_R()
+    while nrm > tol and k + p <= cap:
+        # ---- v = argmax_vertex | (St R)[v, :, :] |^2  (:178)
+        xb[:, :ld].copy_(R.view(3 * F, ld))
+        ops.spmv(csr, xb, yb)
+        comm.allreduce_sum(yb)
+        ops.vertex_energy(yb.view(F, 3, L), nv, out=ev)
+        ops.argmax_first(ev, nv, 0, val, idx)                       # replicated after the all-reduce: no exchange
+        v = int(idx.item())
+        verts.append(v)
+        nel = int((elems == v).any(axis=1).sum())
+        print("vert", v, "elements", nel)
+        for it in range(nel):
+            k0 = k
+            for i in range(p):
+                row_id.fill_(it * p + i)
+                pick.rows(R, N, row_id, row0, W, k0, C, k - k0, traj)
+                ops.traj_rank1(traj, F, False, W, k, k0, coef, scal)
+                ops.deflate_gemv(R, N, W, k, g)
+                ops.deflate_finish(g, C, k, k0, coef, None, scal, e, N, meas[k])
+                k += 1
+            ops.rank_update(R, N, W, C, k0, p, e)
+            nrm = norm_R()
+            sig = meas[k0:k, 0].cpu().numpy()
+            table.append([float(len(table) + 1), float(it), nrm] + [float(x) for x in sig])
+            if nrm < tol or k + p > cap:
+                break
+    return C[:k], W, np.array(table), np.array(verts, dtype=np.int64)
+
+
 # ====================================================================================== SPLOCS (k10-k14)
 def splocs(ops, comm, X, shard, C, W, K, geodesic, num_iters, num_admm, lam, rho, dmin=0.1, dmax=0.25, log=print):
     """SPLOCS global optimisation of snapbases/posComponents.py:132-189 in Gram form.

@@ -7,8 +7,8 @@
   read_mass_bin               snapbases/posSnapshots.py:142-149, snapbases/nonlinear_snapshots.py:181-192
   log_time                    utils/utils.py:209-237    function_timings.txt (first write of the process truncates)
   read_animation / write_components_animation           the `.h5` containers of posSnapshots.read (:108-121) and
-      posComponents.store_animations (:330-341); h5py/libhdf5 are not in this image, so an `.npz` with the SAME keys is
-      read / written when h5py cannot be imported.
+      posComponents.store_animations (:330-341): real HDF5 files through h5mini.py (h5py / libhdf5 are not in this image,
+      SURVEY H8); a name ending in `.npz` selects the numpy container with the same keys.
 """
 from __future__ import annotations
 
@@ -18,6 +18,8 @@ import struct
 import time
 
 import numpy as np
+
+from . import h5mini
 
 _has_written = False
 
@@ -106,15 +108,6 @@ def write_mass_bin(path, mass):
         np.asarray(mass, dtype="<f8").tofile(f)
 
 
-def _h5py():
-    """The real h5py when it is installed (a stand-in module registered by a test shim does not count)."""
-    try:
-        import h5py
-        return h5py if isinstance(h5py.version.version, str) else None
-    except Exception:
-        return None
-
-
 def _npz_sidecar(path):
     return path if path.endswith(".npz") else os.path.splitext(path)[0] + ".npz"
 
@@ -162,21 +155,17 @@ def read_animation(path):
     with `register_animation` yields its MemoryAnimation instead of an array."""
     if path in _MEMORY:
         return _MEMORY[path], _MEMORY[path].tris
-    h5 = _h5py()
-    if h5 is not None and os.path.exists(path) and not path.endswith(".npz"):
-        with h5.File(path, "r") as f:
-            return f["verts"][()], f["tris"][()]
+    if not path.endswith(".npz") and h5mini.is_hdf5(path):     # a real HDF5 container (h5py's gzip-chunked `verts` included)
+        d = h5mini.read_datasets(path, ("verts", "tris"))
+        return d["verts"], d["tris"]
     data = np.load(_npz_sidecar(path))
     return data["verts"], data["tris"]
 
 
-def write_animation(path, verts, tris):
-    h5 = _h5py()
-    if h5 is not None and not path.endswith(".npz"):
-        with h5.File(path, "w") as f:
-            f.create_dataset("verts", data=np.asarray(verts, dtype=np.float32), compression="gzip")
-            f["tris"] = tris
-        return path
+def write_animation(path, verts, tris, attrs=None):
+    """`verts` (float32) / `tris` to `path`: an HDF5 file (h5mini; contiguous datasets) unless the name ends in .npz."""
+    if not path.endswith(".npz"):
+        return h5mini.write_datasets(path, {"verts": np.asarray(verts, dtype=np.float32), "tris": np.asarray(tris)}, attrs)
     out = _npz_sidecar(path)
     np.savez(out, verts=np.asarray(verts, dtype=np.float32), tris=tris)
     return out
@@ -184,16 +173,12 @@ def write_animation(path, verts, tris):
 
 def write_components_animation(path, default_verts, tris, comps):
     """components.h5 of posComponents.store_animations: keys `default`, `tris`, `comp%03d`."""
-    h5 = _h5py()
-    if h5 is not None and not path.endswith(".npz"):
-        with h5.File(path, "w") as f:
-            f["default"] = default_verts
-            f["tris"] = tris
-            for i, c in enumerate(comps):
-                f["comp%03d" % i] = c
-        return path
+    data = {"default": np.asarray(default_verts), "tris": np.asarray(tris)}
+    data.update({"comp%03d" % i: np.asarray(c) for i, c in enumerate(comps)})
+    if not path.endswith(".npz"):
+        return h5mini.write_datasets(path, data)           # what utils/process.py:367-376 (load_splocs) and the viewers read
     out = _npz_sidecar(path)
-    np.savez(out, default=default_verts, tris=tris, **{"comp%03d" % i: c for i, c in enumerate(comps)})
+    np.savez(out, **data)
     return out
 
 
@@ -364,14 +349,8 @@ def convert_sequence_to_hdf5(filename_pattern, loader_function, hdf_output_file,
             count += 1
     verts_all = np.array(verts_all, np.float32)
     verts_all, tris, _, verts_mean, verts_scale = preprocess_mesh_animation(verts_all, tris)
-    h5 = _h5py()
-    if h5 is not None and not hdf_output_file.endswith(".npz"):
-        with h5.File(hdf_output_file, "w") as f:
-            f.create_dataset("verts", data=verts_all, compression="gzip")
-            f["tris"] = tris
-            f.attrs["mean"] = verts_mean
-            f.attrs["scale"] = verts_scale
-        out = hdf_output_file
+    if not hdf_output_file.endswith(".npz"):
+        out = write_animation(hdf_output_file, verts_all, tris, attrs={"mean": verts_mean, "scale": np.float64(verts_scale)})
     else:
         out = _npz_sidecar(hdf_output_file)
         np.savez(out, verts=verts_all, tris=tris, mean=verts_mean, scale=verts_scale)

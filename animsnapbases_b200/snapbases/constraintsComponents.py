@@ -14,8 +14,8 @@ Device work goes through animsnapbases_b200.engine -> libasb.so:
 
   pod             (:274-294)  p * 3 independent PODs of the (e x F) blocks (f32 torch-CPU SVDs in the reference)    engine.pod_per_row
 
-Basis type 'pca_blocks_with_St' (defective in the reference) raises NotImplementedError here
-rather than fall back to the CPU.
+  pca_blocks_with_St (:156-271)  block deflation picked in position space through St, until |R| <= bases_R_tol; keeps the
+                              reference's loop-counter row indexing                              engine.deflate_blocks_with_St
 The plotting / polyscope methods of the reference (:865-1156) are out of scope (graphics: unavailable on this box).
 """
 from __future__ import annotations
@@ -123,12 +123,10 @@ class constraintsComponents:  # Components == bases
             headerSing = ['component', 'singVal']
         if kind not in ("pod", "pod_vectorized", "pca_blocks", "pca_blocks_with_St"):
             raise ValueError("Uknown basis type: ", kind)
-        if kind not in ("pod_vectorized", "pca_blocks", "pod"):
-            raise NotImplementedError(f"constProj_basis_type '{kind}' is not built on the device yet (SURVEY 8(a) a10/a11); "
-                                      "there is no CPU fallback")
         compute = {"pod_vectorized": self.compute_pod_for_vectorized_nonlinear_snapshots_tensor,
                    "pod": self.compute_pod_for_nonlinear_snapshots_tensor,
-                   "pca_blocks": self.compute_nonlinearity_bases_blocks}[kind]
+                   "pca_blocks": self.compute_nonlinearity_bases_blocks,
+                   "pca_blocks_with_St": self.compute_nonlinearity_bases_blocks_utilizing_diffirential_operator}[kind]
         _, comm = runtime.get()
         file_name = os.path.join(p.constProj_output_directory, p.name + "_" + p.constProj_name + self.file_name_sing)
         rows = []                                      # collected on every rank (collectives inside), written by rank 0
@@ -163,6 +161,32 @@ class constraintsComponents:  # Components == bases
         if writer is not None:
             for r in table:
                 writer.writerow([int(r[0]), int(r[1])] + [float(v) for v in r[2:]])
+        print("bases shape", (C.shape[0], snaps.shard.n_global, 3), "number of components", self.numComp)
+
+    @log_time("")
+    def compute_nonlinearity_bases_blocks_utilizing_diffirential_operator(self, writer=None):
+        """`pca_blocks_with_St` (:156-271): block deflation whose picks are made in position space through St, until the
+        residual norm drops under param.bases_R_tol (engine.deflate_blocks_with_St keeps the loop-counter row indexing)."""
+        if self.support == 'local':
+            raise ValueError("Local support maps are not yet available for nonlinear-term components")
+        if self.St is None:
+            raise ValueError("basis type 'pca_blocks_with_St' needs the differential operator St (constProj_weightedSt)")
+        ops, comm = runtime.get()
+        snaps = self.nonlinearSnapshots
+        p = snaps.constraintsSize
+        elems = {"_tets": snaps.tets, "_tris": snaps.tris, "_edges": snaps.edges}.get(snaps.ele_type)
+        if elems is None:
+            print("ERROR! unknown constraints projection type")
+            return
+        C, W, table, verts = engine.deflate_blocks_with_St(ops, comm, snaps.state.X, snaps.shard, p, self.St, elems,
+                                                           float(self.param.bases_R_tol))
+        self._C, self._W, self._host = C, W, {}
+        self.measures_at_largeDeforVerts = table
+        self.largeDeforPoints = verts
+        self.numComp = C.shape[0] // p
+        if writer is not None:
+            for r in table:
+                writer.writerow([int(r[0]), int(r[1])] + [float(x) for x in r[2:]])
         print("bases shape", (C.shape[0], snaps.shard.n_global, 3), "number of components", self.numComp)
 
     @log_time("")

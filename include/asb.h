@@ -164,8 +164,9 @@ int asb_admm_iter(const double* Hr, int64_t ldh, const double* B0, double* Z, do
 /* G[j][l] = sum_f W[f][j] W[f][l] + (j == l ? diag_add : 0)   (posComponents.py:170, :172). */
 int asb_gram_small(const double* W, int64_t ldw, int64_t F, int64_t K, double diag_add, double* G, int64_t ldg,
                    asb_stream_t stream);
-/* Hinv = H^-1 for SPD H (K x K) via Cholesky (replaces cho_factor/cho_solve, posComponents.py:172,:176).
- * H is overwritten by its Cholesky factor. info_dev[0] != 0 if not positive definite. */
+/* Hinv = H^-1 for SPD H (K x K) (replaces cho_factor/cho_solve, posComponents.py:172,:176).  K <= 239: K symmetric sweeps on
+ * the packed triangle in shared memory, H untouched; larger K: Cholesky in global memory, H overwritten by its factor.
+ * info_dev[0] != 0 if a pivot is not positive (H not positive definite). */
 int asb_spd_inverse(double* H, int64_t ldh, int64_t K, double* Hinv, int64_t ldi, double* scratch /* K x ldi */,
                     int* info_dev, asb_stream_t stream);
 /* D = alpha * op(A) * op(B) for small matrices (everything L2 resident); D: m x n, inner k. */

@@ -134,6 +134,18 @@ def pos_case(name, verts0, tris, F, K, n_bumps, sigma, splocs, seed):
         pc2.param.q_orthogonal = False
         pc2.post_process_components()
     out["post_global"] = pc2.comps.copy()
+    # ---- q_orthogonal branch (posComponents.py:285-287): scipy orth per dimension, on a fresh copy of the global components
+    ps3, pc3 = ref_pos_objects(anim, tris, mass, "first", "global", K, "PCA")
+    run_ref_pos(pc3, False)
+    pre = pc3.comps.copy()
+    pre /= ps3.pre_scale_factor
+    pre += ps3.mean[np.newaxis]
+    out["pre_orth"] = pre.copy()                      # what `orth` is applied to (:279-282)
+    with contextlib.redirect_stdout(io.StringIO()):
+        pc3.param.q_orthogonal = True
+        pc3.post_process_components()
+    out["post_global_orth"] = pc3.comps.copy()
+    out["post_global_orth_raw"] = pc3.comps / ps3.invMassL[None, :, None]      # undo the final `*= invMassL` (:289-292)
 
     # ---- port vs reference
     prep = port.prepare_snapshots(anim, mass, "first")
@@ -330,6 +342,64 @@ def bar_geom_case():
                     name + "_verts": np.asarray(cc.geom_interpol_verts, dtype=np.int64)})
         print(f"bar_geom {name}: port == reference; alpha={cc.geom_alpha[:8]} ranges={cc.geom_alpha_ranges}")
     np.savez_compressed(os.path.join(GOLD, "bar_geom.npz"), **out)
+
+
+# ------------------------------------------------------------------------------------------------ pca_blocks_with_St (a11)
+def bar_blocks_st_case():
+    """compute_nonlinearity_bases_blocks_utilizing_diffirential_operator (constraintsComponents.py:156-271) of the unmodified
+    reference on the bar fixture's standardised snapshots -> tests/golden/bar_blocks_st.npz.  The function is well defined on
+    these inputs: every rank-1 step removes one frame-space direction from all rows, so the residual norm passes bases_R_tol
+    after about rank(X) steps (8 blocks for tol = 1e-8, 11 for 1e-13), before the incident-element loop of the first
+    vertex runs out.  Also pins the f32 per-row POD (`pod`, :274-294, torch CPU) for oracle/port.py::pod_per_row_f32."""
+    from snapbases.constraintsComponents import constraintsComponents
+    from snapbases.nonlinear_snapshots import nonlinearSnapshots
+    m = np.load(os.path.join(GOLD, "meshes.npz"))
+    bar = np.load(os.path.join(GOLD, "bar.npz"))
+    verts, tets = m["bar_verts"], bar["tets"].astype(np.int64)
+    e, p = len(tets), 3
+    St = synth.tet_gradient_operator(verts, tets).T.tocsr()
+    out = {}
+    for tag, tol in (("tol8", 1e-8), ("tol13", 1e-13)):
+        ns = object.__new__(nonlinearSnapshots)
+        ns.constraintsSize, ns.num_constained_elements, ns.dim = p, e, 3
+        ns.ele_type, ns.tets = "_tets", tets
+        ns.snapTensor = bar["X"].copy()
+        cc = object.__new__(constraintsComponents)
+        cc.param = types.SimpleNamespace(bases_R_tol=tol)
+        cc.nonlinearSnapshots, cc.St, cc.support, cc.storeSingVal = ns, St, "global", False
+        log = io.StringIO()
+        with contextlib.redirect_stdout(log):
+            cc.compute_nonlinearity_bases_blocks_utilizing_diffirential_operator(None)
+        assert not np.isnan(cc.comps).any()
+        vs = np.array([int(l.split()[1]) for l in log.getvalue().split("\n") if l.startswith("vert")])
+        C, W, M, V = port.nonlinearity_bases_blocks_with_St(bar["X"], e, p, St, tets, tol)
+        assert np.array_equal(C, cc.comps) and np.array_equal(W, cc.weigs) and np.array_equal(M, cc.measures_at_largeDeforVerts)
+        assert np.array_equal(V, vs)
+        out.update({tag + "_comps": cc.comps, tag + "_weigs": cc.weigs, tag + "_meas": cc.measures_at_largeDeforVerts,
+                    tag + "_verts": vs, tag + "_tol": np.array([tol])})
+        print(f"bar_blocks_st {tag}: {cc.comps.shape[0] // p} blocks, verts {vs}, port == reference (bit-equal)")
+    # ---- `pod` basis type: p * 3 float32 SVDs through torch on the CPU (:274-294)
+    ns = object.__new__(nonlinearSnapshots)
+    ns.constraintsSize, ns.num_constained_elements, ns.dim = p, e, 3
+    ns.snapTensor = bar["X"].copy()
+    cc = object.__new__(constraintsComponents)
+    cc.param = types.SimpleNamespace(deim_desired_num_components=8)
+    cc.nonlinearSnapshots = ns
+    with contextlib.redirect_stdout(io.StringIO()):
+        cc.compute_pod_for_nonlinear_snapshots_tensor(None)
+    ref = np.asarray(cc.comps)
+    mine = port.pod_per_row_f32(bar["X"], e, p, 8)
+    worst = 0.0
+    for k in range(ref.shape[0]):
+        for i in range(p):
+            for d in range(3):
+                a, b = ref[k, i::p, d], mine[k, i::p, d]
+                sg = np.sign(float(a @ b)) or 1.0
+                worst = max(worst, float(np.linalg.norm(a - sg * b)))
+    print(f"pod (f32, per row): port (LAPACK sgesdd) vs reference (torch.linalg.svd f32): max mode difference up to sign {worst:.2e}")
+    assert worst < 5e-3, worst          # float32 SVDs from two LAPACK drivers: close modes rotate at 1e-4 .. 1e-3
+    out["pod_f32_comps"] = ref
+    np.savez_compressed(os.path.join(GOLD, "bar_blocks_st.npz"), **out)
 
 
 # ------------------------------------------------------------------------------------------------ geometric DEIM, '_verts'
@@ -539,6 +609,17 @@ def main():
     if "--pd-only" in sys.argv:                # writes pd_local.npz only
         with scratch_cwd():
             return pd_local_case()
+    if "--pos-only" in sys.argv:               # rewrites pos_grid.npz / pos_sphere.npz only
+        with scratch_cwd():
+            m = np.load(os.path.join(GOLD, "meshes.npz"))
+            gv, gt = synth.grid_mesh(24, 20)
+            pos_case("pos_grid", gv, gt, F=24, K=10, n_bumps=5, sigma=0.12, splocs=dict(max_itrs=3, admm=5, lam=2.0, rho=10.0), seed=0)
+            pos_case("pos_sphere", m["sphere_verts"], m["sphere_tris"].astype(np.int64), F=30, K=12, n_bumps=6, sigma=0.2,
+                     splocs=dict(max_itrs=2, admm=10, lam=2.0, rho=10.0), seed=1)
+            return
+    if "--blocks-st-only" in sys.argv:         # reads bar.npz, writes bar_blocks_st.npz only
+        with scratch_cwd():
+            return bar_blocks_st_case()
     if "--verts-only" in sys.argv:             # writes verts_geom.npz only
         with scratch_cwd():
             return verts_geom_case()
@@ -558,6 +639,7 @@ def main():
             return bar_geom_case()
         bar_case()
         bar_geom_case()
+        bar_blocks_st_case()
         bar_reduced_case()
         verts_geom_case()
         pd_local_case()

@@ -373,6 +373,40 @@ def nonlinearity_bases_blocks(X, e, p, k_desired, on_row=None):
     return np.array(C), np.array(W).T, np.array(meas), np.array(S_idx), np.array(S_p)
 
 
+def nonlinearity_bases_blocks_with_St(X, e, p, St, elems, tol, on_row=None):
+    """snapbases/constraintsComponents.py:156-271 (`pca_blocks_with_St`, global support, '_tets' / '_tris' / '_edges').
+    While |R| > tol: the vertex with the largest residual pushed through St (:178) fixes HOW MANY blocks follow (its incident
+    elements); the blocks themselves deflate rows  idx * p + i  with idx the LOOP COUNTER, not the element id (:203-209, SURVEY
+    H6) -- every rank-1 step projects one frame-space direction out of ALL rows, so the loop ends once rank(X) directions are
+    gone.  Returns comps (nb p, ep, 3), weigs (F, nb p), measures rows [count, idx, |R|, sigma_0..], picked vertices."""
+    R = X.copy()
+    C, W, meas, verts = [], [], [], []
+    count = 0
+    elems = np.asarray(elems)
+    while sla.norm(R) > tol:
+        v = int(np.argmax(((St @ np.swapaxes(R, 0, 1).reshape(e * p, -1)) ** 2).sum(axis=1)))       # :178
+        nel = int((elems == v).any(axis=1).sum())                                                    # utils/support.py:210-257
+        verts.append(v)
+        for idx in range(nel):
+            sigma = []
+            for i in range(p):
+                _, sing, Vt = sla.svd(R[:, idx * p + i, :].reshape(R.shape[0], -1).T, full_matrices=False)
+                wk = sing[0] * Vt[0, :]
+                ck = np.tensordot(wk, R, (0, 0)) / np.inner(wk, wk)
+                R -= np.outer(wk, ck).reshape(R.shape)
+                C.append(ck)
+                W.append(wk)
+                sigma.append(sing[0])
+            count += 1
+            row = [count, idx, sla.norm(R)] + sigma
+            meas.append(row)
+            if on_row is not None:
+                on_row(row)
+            if sla.norm(R) < tol:
+                break
+    return np.array(C), np.array(W).T, np.array(meas), np.array(verts, dtype=np.int64)
+
+
 def post_process_constraints(comps, snapTensor, mean, pre_scale_factor, invMassL, standarize, orthogonal, mass_weight):
     """snapbases/constraintsComponents.py:415-446.  Returns (comps', snapTensor')."""
     comps, snap = comps.copy(), snapTensor.copy()

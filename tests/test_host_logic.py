@@ -400,7 +400,7 @@ def test_mirror_error_behaviour(tmp_path):
             cc.compute_components_store_singvalues()
         cc = constraints(constProj_basis_type="pca_blocks_with_St")
         cc.nonlinearSnapshots.snapshots_prepare()
-        with pytest.raises(NotImplementedError):         # defective in the reference: refused, no CPU path
+        with pytest.raises(ValueError, match="differential operator St"):   # this fixture's config names no St file
             cc.compute_components_store_singvalues()
         cc = constraints()
         cc.nonlinearSnapshots.snapshots_prepare()
@@ -483,3 +483,55 @@ def test_scale_bunny_prefix_numpy():
     """First components of the bunny F = 200 fixture (the deflation prefix does not depend on K)."""
     import pipeline_checks
     assert pipeline_checks.check_scale_pos(NumpyOps(), engine.Comm(enabled=False), "bunny_splocs", K=6)
+
+
+def test_bar_blocks_with_St_numpy():
+    """pca_blocks_with_St against the unmodified reference's output (loop-counter row indexing included)."""
+    import pipeline_checks
+    assert pipeline_checks.check_bar_blocks_st(NumpyOps(), engine.Comm(enabled=False))
+
+
+@pytest.mark.parametrize("name", ["pos_grid", "pos_sphere"])
+def test_pos_orth_branch_numpy(name):
+    """q_orthogonal branch of posComponents.post_process_components against the reference's scipy.linalg.orth output."""
+    import pipeline_checks
+    assert pipeline_checks.check_pos_orth(NumpyOps(), engine.Comm(enabled=False), name)
+
+
+# ---- HDF5 containers without h5py (SURVEY H8): animsnapbases_b200/h5mini.py
+def test_h5mini_roundtrip_and_layout(tmp_path):
+    from animsnapbases_b200 import h5mini, hostio
+    rng = np.random.default_rng(0)
+    data = {"default": rng.standard_normal((7, 3)), "tris": rng.integers(0, 7, (9, 3)).astype(np.int32)}
+    data.update({"comp%03d" % i: rng.standard_normal((7, 3)) for i in range(203)})        # more links than one default SNOD holds
+    p = h5mini.write_datasets(str(tmp_path / "components.h5"), data, attrs={"scale": np.float64(2.5), "mean": np.arange(3.0)})
+    raw = open(p, "rb").read()
+    assert raw[:8] == b"\x89HDF\r\n\x1a\n" and raw[8] == 0 and raw[13] == 8 and raw[14] == 8
+    assert struct_u64(raw, 40) == len(raw), "end-of-file address of the superblock"
+    out = h5mini.read_datasets(p)
+    assert sorted(out) == sorted(data) and all(np.array_equal(out[k], v) and out[k].dtype == v.dtype for k, v in data.items())
+    # the writers of the drop-in classes emit real HDF5 now
+    q = hostio.write_components_animation(str(tmp_path / "c2.h5"), data["default"], data["tris"], [data["comp%03d" % i] for i in range(5)])
+    assert h5mini.is_hdf5(q) and sorted(h5mini.read_datasets(q)) == ["comp000", "comp001", "comp002", "comp003", "comp004", "default", "tris"]
+    with pytest.raises(h5mini.H5Error):
+        open(tmp_path / "bad.h5", "wb").write(b"not hdf5 at all")
+        h5mini.read_datasets(str(tmp_path / "bad.h5"))
+
+
+def struct_u64(raw, off):
+    import struct
+    return struct.unpack_from("<Q", raw, off)[0]
+
+
+@pytest.mark.parametrize("shuffle", [False, True])
+def test_h5mini_reads_gzip_chunked_animation(tmp_path, shuffle):
+    """An aligned-animation file laid out the way h5py writes `create_dataset('verts', ..., compression='gzip')`
+    (utils/process.py:88-91): chunked storage, v1 B-tree chunk index, deflate (+ shuffle) filter pipeline, edge chunks."""
+    import h5_fixture
+    from animsnapbases_b200 import hostio
+    rng = np.random.default_rng(1)
+    verts = rng.standard_normal((5, 11, 3)).astype(np.float32)
+    tris = rng.integers(0, 11, (13, 3))
+    p = h5_fixture.write_chunked(str(tmp_path / "anim.h5"), verts, tris, chunk=(2, 4, 3), shuffle=shuffle)
+    v, t = hostio.read_animation(p)
+    assert v.dtype == np.float32 and np.array_equal(v, verts) and np.array_equal(t, tris)
