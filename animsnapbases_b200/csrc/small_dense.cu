@@ -602,10 +602,10 @@ int asb_spd_inverse(double* H, int64_t ldh, int64_t K, double* Hinv, int64_t ldi
                     asb_stream_t stream) {
     ASB_REQUIRE(H && Hinv && scratch && info_dev && K > 0 && K <= 2048, "spd_inverse: bad arguments");
     const size_t smem = ((size_t)K * (K + 1) / 2 + K) * sizeof(double);
-    if (smem <= 227 * 1024) {                       // K <= 239: packed triangle in shared memory
+    if (smem <= 226 * 1024) {                       // K <= 239: packed triangle in shared memory
         static bool attr_set = false;
         if (!attr_set) {
-            ASB_CUDA(cudaFuncSetAttribute(spd_inverse_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            ASB_CUDA(cudaFuncSetAttribute(spd_inverse_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
             attr_set = true;
         }
         spd_inverse_sweep_kernel<<<1, 1024, smem, S(stream)>>>(H, ldh, (int)K, Hinv, ldi, info_dev);
