@@ -406,6 +406,9 @@ __device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __
     const uint32_t slab_bytes = (uint32_t)astage * 8u;
     const int grp = G > 1 ? (int)(threadIdx.x >> 7) : 0;
     const int gt = (int)threadIdx.x - 128 * grp;          // thread index inside the group
+    // the thread that issues the bulk copies: thread 0 of the group, or (experiment bit 8, G == 1) lane 0 of the warp that
+    // owns the most m-tiles (mt0 == 0)
+    const bool prod = (G == 1 && (skew & 8)) ? (mt0 == 0 && live && (threadIdx.x & 31) == 0) : gt == 0;
     const size_t group_doubles = (size_t)rows8 * DLD + (size_t)STAGES * astage;
     double* Ds = smem_all + grp * group_doubles;          // [rows8][DLD]  Z - U (rows >= K zero)
     double* As = Ds + (size_t)rows8 * DLD;                // STAGES x [rows8][ALD]
@@ -450,7 +453,7 @@ __device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __
         if (++pst == STAGES) { pst = 0; pwrap ^= 1u; }
         if (++pslab == nslab) pslab = 0;
     };
-    if (gt == 0)
+    if (prod)
         for (int i = 0; i < STAGES && issued < total_all; ++i) issue();
     // consumer state: next slab to use
     int cst = 0;
@@ -508,7 +511,7 @@ __device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __
                 if (need >= 0 && need < partner_iters) mbar_wait(mid + (grp ^ 1), (uint32_t)(need & 1));
             }
             for (int s = 0; s < nslab; ++s) {
-                if (gt == 0 && !first && issued < total_all) issue();   // refill the stage released one step ago
+                if (prod && !first && issued < total_all) issue();   // refill the stage released one step ago
                 first = false;
                 mbar_wait(full + cst, cwrap);
                 const double* as = afrag + cst * astage;
@@ -526,6 +529,7 @@ __device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __
                     }
                 }
                 __syncwarp();
+                if (G == 1 && (skew & 64)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 if (lane == 0) {
                     mbar_arrive(empty + cst);
                     if (G == 2 && s == sig_slab) mbar_arrive(mid + grp);
@@ -594,6 +598,7 @@ __device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __
             }
             if (!last) group_sync();  // the new D is complete before any warp multiplies with it
         }
+        if (G == 1 && (skew & 32)) group_sync();
     }
 }
 
@@ -606,7 +611,9 @@ admm_tma_kernel(const double* __restrict__ Hpk, const double* __restrict__ B0, d
     int mt0, mtn;
     int wm = (threadIdx.x >> 5) & 3;
     // co-resident groups rotate the row-warp roles: the 7-tile warps (K = 200: 7,6,6,6) sit on different SM sub-partitions
-    const int slot = Cfg::G > 1 ? (int)(threadIdx.x >> 7) : (int)((blockIdx.x / max(1u, gridDim.x / 2)) & 1);
+    int slot = Cfg::G > 1 ? (int)(threadIdx.x >> 7) : (int)((blockIdx.x / max(1u, gridDim.x / 2)) & 1);
+    if (Cfg::G == 1 && (skew & 128)) slot = 0;
+    if (Cfg::G == 1 && (skew & 256)) slot ^= 1;
     wm = (wm + (Cfg::G == 3 ? slot : 2 * slot)) % Cfg::WM;
     mtile_range(((K + 7) & ~7) >> 3, Cfg::WM, wm, mt0, mtn);
     const bool live = mtn > 0;
@@ -652,6 +659,7 @@ static size_t admm_smem_bytes(int64_t K) {
     return ((size_t)rowsk * Cfg::DLD + (size_t)rows8 * Cfg::STAGES * Cfg::ALD) * sizeof(double);
 }
 
+static int g_admm_layout = -1, g_admm_skew = -1;   // -1: from the environment (asb_admm_select_layout overrides both)
 static int env_int(const char* name, int dflt) {
     const char* e = std::getenv(name);
     return e ? std::atoi(e) : dflt;
@@ -713,7 +721,8 @@ template <class Cfg>
 static int launch_admm_tma(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda, int64_t K,
                            int64_t N, int64_t ld, double inv_rho, int iters, double* pack, cudaStream_t st) {
     const int rows8 = (int)((K + 7) & ~7LL), nslab = rows8 / Cfg::BK;
-    static const int skew = env_int("ASB_ADMM_SKEW", 0);
+    static const int env_skew = env_int("ASB_ADMM_SKEW", 0);
+    const int skew = g_admm_skew >= 0 ? g_admm_skew : env_skew;
     admm_pack_kernel<<<64, 256, 0, st>>>(Hr, ldh, rows8, nslab, Cfg::BK, Cfg::ALD, pack);
     ASB_LAUNCH_CHECK();
     switch ((int)cdiv(cdiv(K, 8), Cfg::WM)) {
@@ -727,7 +736,7 @@ static int launch_admm_tma(const double* Hr, int64_t ldh, const double* B0, doub
 
 static int admm_layout() {
     static const int layout = env_int("ASB_ADMM_LAYOUT", ASB_ADMM_LAYOUT_DEFAULT);   // 5: TMA Pair, 4 / 416: Pair, 12 / 1216: Wide, 16: Tall
-    return layout;
+    return g_admm_layout >= 0 ? g_admm_layout : layout;
 }
 
 static int launch_admm(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda,
@@ -759,6 +768,12 @@ static int launch_admm(const double* Hr, int64_t ldh, const double* B0, double* 
 using namespace asb;
 
 extern "C" {
+
+int asb_admm_select_layout(int layout, int skew) {
+    g_admm_layout = layout;
+    g_admm_skew = skew;
+    return ASB_OK;
+}
 
 int64_t asb_admm_workspace_bytes(int64_t K) { return K > 0 && K <= 256 ? (int64_t)admm_pack_bytes(K) : 0; }
 

@@ -156,6 +156,9 @@ int asb_admm_solve(const double* Hr, int64_t ldh, const double* B0, double* Z, d
 int64_t asb_admm_workspace_bytes(int64_t K);
 int asb_admm_solve_ws(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda,
                       int64_t K, int64_t N, int64_t ld, double inv_rho, int64_t iters, void* ws, asb_stream_t stream);
+/* Measurement switch (tools/admm_ab.py, tools/kbench.py): overrides ASB_ADMM_LAYOUT / ASB_ADMM_SKEW for the calls that follow
+ * (layout < 0 / skew < 0: back to the environment).  Not used by the product path. */
+int asb_admm_select_layout(int layout, int skew);
 /* One iteration of the above (asb_admm_solve with iters = 1). */
 int asb_admm_iter(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda,
                   int64_t K, int64_t N, int64_t ld, double inv_rho, asb_stream_t stream);

@@ -27,6 +27,13 @@ for step in "$@"; do
                 ASB_ADMM_LAYOUT=$l timeout 300 python tools/kbench.py --only admm 2>&1 | grep admm_solve_x10 | sed "s/^/layout $l: /"
               else echo "layout $l tests FAILED"; tail -20 gpurun_out/admm$l.log; fi
             done ;;
+    noalloc) timeout 600 python -m pytest tests/test_zz_no_alloc.py -x -q -m gpu > gpurun_out/noalloc.log 2>&1; echo "noalloc (fresh process) rc=$?"; tail -4 gpurun_out/noalloc.log ;;
+    ab)     timeout 900 python tools/admm_ab.py 14290 200 10 2 > gpurun_out/admm_ab.log 2>&1; echo "ab rc=$?"
+            timeout 600 python tools/admm_ab.py 14290 200 1 2 --variants 0,8 >> gpurun_out/admm_ab.log 2>&1; cat gpurun_out/admm_ab.log ;;
+    ncu_list) timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/ncu_launches.csv python bench.py --grid 300 300 --frames 500 --comps 48 --splocs-iters 3 --steps 1 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/ncu_list.log 2>&1; echo "ncu_list rc=$?"; tail -2 gpurun_out/ncu_list.log; wc -l gpurun_out/ncu_launches.csv ;;
+    bench)  timeout 1500 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; echo "bench rc=$?"; tail -c 4000 gpurun_out/bench_default.json; tail -5 gpurun_out/bench_default.err ;;
+    benchN) N=${ASB_NGPU:-8}; timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/bench_${N}gpu.json 2> gpurun_out/bench_${N}gpu.err; echo "bench$N rc=$?"; tail -c 4000 gpurun_out/bench_${N}gpu.json; tail -5 gpurun_out/bench_${N}gpu.err ;;
+    nccl2)  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 tools/nccl_worker.py --mirror-classes > gpurun_out/nccl_worker_2gpu.log 2>&1; echo "nccl2 rc=$?"; tail -15 gpurun_out/nccl_worker_2gpu.log ;;
     *) echo "unknown step $step" ;;
   esac
 done
