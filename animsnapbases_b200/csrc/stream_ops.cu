@@ -1,5 +1,6 @@
 // HBM-bound streaming kernels: boundary layout conversion, mean-centering/standardisation (k2),
 // greedy-deflation passes (k3, k8, k9).  All are coalesced planar passes; reductions are fixed-order.
+#include <mutex>
 #include "common.cuh"
 
 namespace asb {
@@ -468,6 +469,58 @@ int asb_vertex_energy(const double* R, double* e, int64_t F, int64_t N, int64_t 
     const int64_t fps = cdiv(F, slabs);
     const int64_t ns = cdiv(F, fps);
     double* part = ns == 1 ? e : reinterpret_cast<double*>(ws);
+    vertex_energy_kernel<<<dim3((unsigned)gx, (unsigned)ns), 128, 0, S(stream)>>>(R, part, F, N, ld, fps);
+    ASB_LAUNCH_CHECK();
+    if (ns > 1) {
+        sum_slabs_kernel<<<(unsigned)cdiv(ld, 256), 256, 0, S(stream)>>>(part, e, ld, ns);
+        ASB_LAUNCH_CHECK();
+    }
+    return ASB_OK;
+}
+
+// ---- allocation-free form of asb_vertex_energy (no counterpart in the reference; see include/asb.h) ----------------------
+// The slab partials live in a file-scope device array instead of a caller workspace.  In host code `g_static_scratch` is only
+// a stand-in for the symbol: its device address is looked up once per device with cudaGetSymbolAddress (that device current)
+// and that pointer is what the kernels receive.
+#define ASB_STATIC_SCRATCH_DOUBLES 131072   // 1 MiB per GPU that loads the library, held until exit
+static __device__ __align__(256) double g_static_scratch[ASB_STATIC_SCRATCH_DOUBLES];
+
+static int static_scratch(double** out) {
+    constexpr int MAXDEV = 64;
+    static double* ptrs[MAXDEV] = {};
+    static std::mutex mu;
+    int dev = -1;
+    ASB_CUDA(cudaGetDevice(&dev));
+    ASB_REQUIRE(dev >= 0 && dev < MAXDEV, "static scratch: device ordinal out of range");
+    std::lock_guard<std::mutex> guard(mu);
+    if (!ptrs[dev]) {
+        void* p = nullptr;
+        ASB_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+        ASB_REQUIRE(p != nullptr, "static scratch: no device address for the scratch symbol");
+        ptrs[dev] = reinterpret_cast<double*>(p);
+    }
+    *out = ptrs[dev];
+    return ASB_OK;
+}
+
+int64_t asb_static_scratch_doubles(void) { return ASB_STATIC_SCRATCH_DOUBLES; }
+
+int asb_vertex_energy_static(const double* R, double* e, int64_t F, int64_t N, int64_t ld, asb_stream_t stream) {
+    ASB_REQUIRE(R && e && F > 0 && N > 0 && ld >= N, "vertex_energy_static: bad arguments");
+    // the same split into frame slabs as asb_vertex_energy, so the two forms add in the same order (bit-equal results)
+    const int64_t gx = cdiv(ld, 128);
+    const int64_t slabs = pick_slabs(gx, F, 64);
+    const int64_t fps = cdiv(F, slabs);
+    const int64_t ns = cdiv(F, fps);
+    ASB_REQUIRE(ns == 1 || ns * ld <= (int64_t)ASB_STATIC_SCRATCH_DOUBLES,
+                "vertex_energy_static: frame-slab partials (slabs x ld doubles) exceed the 131072-double static scratch; "
+                "use asb_vertex_energy with a caller workspace");
+    double* part = e;
+    if (ns > 1) {
+        const int rc = static_scratch(&part);
+        if (rc != ASB_OK) return rc;
+    }
+    // every partial in [0, ns * ld) is written by the first kernel before the second reads it: nothing to clear
     vertex_energy_kernel<<<dim3((unsigned)gx, (unsigned)ns), 128, 0, S(stream)>>>(R, part, F, N, ld, fps);
     ASB_LAUNCH_CHECK();
     if (ns > 1) {

@@ -82,6 +82,18 @@ int asb_unstandardize(double* T, const double* mean, double scale, int64_t R, in
 /* e[n] = sum_f ((x^2 + y^2) + z^2), f ascending; `block` > 1 sums the energies of `block` consecutive
  * rows into e[n / block] (element energy, snapbases/constraintsComponents.py:86-96). (:78-79) */
 int asb_vertex_energy(const double* R, double* e, int64_t F, int64_t N, int64_t ld, void* ws, asb_stream_t stream);
+/* Allocation-free form of asb_vertex_energy.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs,
+ * outputs, kernels and summation order as asb_vertex_energy (bit-equal results), but the frame-slab partials live in a
+ * file-scope `static __device__` array of asb_static_scratch_doubles() = 131072 doubles (1 MiB, held by every GPU that
+ * loads the library until exit) instead of a caller workspace; the entry point calls no cudaMalloc / cudaFree / allocating
+ * library routine.  Limit: slabs * ld <= 131072 doubles, where slabs <= 64 is the frame split asb_vertex_energy would
+ * choose (slabs = 1, i.e. ld >= 128 * 4 * #SMs, needs no scratch and is always accepted); larger problems are refused with
+ * ASB_ERR_ARG ("... exceed the 131072-double static scratch").  Every call on a device shares the one array: calls that
+ * overlap on the GPU (different streams, no ordering between them) race on it; calls on one stream are ordered and safe.
+ * Nothing has to start at zero: every partial that is read is written earlier in the same call. */
+int64_t asb_static_scratch_doubles(void);
+int asb_vertex_energy_static(const double* R, double* e, int64_t F, int64_t N, int64_t ld, asb_stream_t stream);
 /* out[j] = sum_{i<group} v[j*group + i] (i ascending), j < n / group: element energy over the p constraint rows of an
  * element (indxLargestDeformation, snapbases/constraintsComponents.py:86-96). */
 int asb_group_sum(const double* v, int64_t n, int64_t group, double* out, asb_stream_t stream);
