@@ -34,6 +34,15 @@ for step in "$@"; do
     bench)  timeout 1500 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; echo "bench rc=$?"; tail -c 4000 gpurun_out/bench_default.json; tail -5 gpurun_out/bench_default.err ;;
     benchN) N=${ASB_NGPU:-8}; timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/bench_${N}gpu.json 2> gpurun_out/bench_${N}gpu.err; echo "bench$N rc=$?"; tail -c 4000 gpurun_out/bench_${N}gpu.json; tail -5 gpurun_out/bench_${N}gpu.err ;;
     nccl2)  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 tools/nccl_worker.py --mirror-classes > gpurun_out/nccl_worker_2gpu.log 2>&1; echo "nccl2 rc=$?"; tail -15 gpurun_out/nccl_worker_2gpu.log ;;
+    ab5)    ASB_ADMM_LAYOUT=5 timeout 1200 python -m pytest tests/test_gpu_scale.py tests/test_gpu_ops.py tests/test_gpu_pipeline.py -x -q -m gpu > gpurun_out/layout5_tests.log 2>&1; echo "layout-5 scale+ops+pipeline rc=$?"; tail -3 gpurun_out/layout5_tests.log
+            : > gpurun_out/admm_ab5.log
+            timeout 600 python tools/admm_ab.py 14290 200 10 8 --variants 0 >> gpurun_out/admm_ab5.log 2>&1
+            timeout 600 python tools/admm_ab.py 34834 200 10 4 --variants 0 >> gpurun_out/admm_ab5.log 2>&1
+            timeout 600 python tools/admm_ab.py 200000 200 10 3 --variants 0 >> gpurun_out/admm_ab5.log 2>&1
+            timeout 600 python tools/admm_ab.py 1000000 200 10 2 --variants 0 >> gpurun_out/admm_ab5.log 2>&1
+            timeout 600 python tools/admm_ab.py 100000 136 7 3 --variants 0 >> gpurun_out/admm_ab5.log 2>&1
+            timeout 600 python tools/admm_ab.py 50001 256 5 3 --variants 0 >> gpurun_out/admm_ab5.log 2>&1
+            cat gpurun_out/admm_ab5.log ;;
     *) echo "unknown step $step" ;;
   esac
 done
