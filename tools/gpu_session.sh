@@ -30,7 +30,14 @@ for step in "$@"; do
     noalloc) timeout 600 python -m pytest tests/test_zz_no_alloc.py -x -q -m gpu > gpurun_out/noalloc.log 2>&1; echo "noalloc (fresh process) rc=$?"; tail -4 gpurun_out/noalloc.log ;;
     ab)     timeout 900 python tools/admm_ab.py 14290 200 10 2 > gpurun_out/admm_ab.log 2>&1; echo "ab rc=$?"
             timeout 600 python tools/admm_ab.py 14290 200 1 2 --variants 0,8 >> gpurun_out/admm_ab.log 2>&1; cat gpurun_out/admm_ab.log ;;
-    ncu_list) timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/ncu_launches.csv python bench.py --grid 300 300 --frames 500 --comps 48 --splocs-iters 3 --steps 1 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/ncu_list.log 2>&1; echo "ncu_list rc=$?"; tail -2 gpurun_out/ncu_list.log; wc -l gpurun_out/ncu_launches.csv ;;
+    ncu_list) A="--grid 300 300 --frames 500 --comps 48 --splocs-iters 3 --steps 1 --warmup 1 --no-e2e --no-cpu-baseline"
+            if timeout 600 python bench.py $A > gpurun_out/ncu_list_plain.json 2> gpurun_out/ncu_list_plain.err; then
+              timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:asb:: -c 60000 --csv --log-file gpurun_out/ncu_launches.csv python bench.py $A > gpurun_out/ncu_list.log 2>&1; echo "ncu_list rc=$?"; tail -2 gpurun_out/ncu_list.log; wc -l gpurun_out/ncu_launches.csv
+            else echo "plain run failed"; tail -5 gpurun_out/ncu_list_plain.err; fi ;;
+    ncu_admm) if timeout 300 python tools/kbench.py --only admm > gpurun_out/kbench_admm_plain.log 2>&1; then
+              grep admm_solve gpurun_out/kbench_admm_plain.log
+              timeout 900 ncu --set full --clock-control none --import-source on -k regex:admm_tma_kernel -s 1 -c 1 -o gpurun_out/prof_admm_tma -f python tools/kbench.py --only admm > gpurun_out/ncu_admm.log 2>&1; echo "ncu_admm rc=$?"; tail -2 gpurun_out/ncu_admm.log; ls -la gpurun_out/*.ncu-rep
+            else echo "plain kbench failed"; tail -5 gpurun_out/kbench_admm_plain.log; fi ;;
     bench)  timeout 1500 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; echo "bench rc=$?"; tail -c 4000 gpurun_out/bench_default.json; tail -5 gpurun_out/bench_default.err ;;
     benchN) N=${ASB_NGPU:-8}; timeout 1200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/bench_${N}gpu.json 2> gpurun_out/bench_${N}gpu.err; echo "bench$N rc=$?"; tail -c 4000 gpurun_out/bench_${N}gpu.json; tail -5 gpurun_out/bench_${N}gpu.err ;;
     nccl2)  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 tools/nccl_worker.py --mirror-classes > gpurun_out/nccl_worker_2gpu.log 2>&1; echo "nccl2 rc=$?"; tail -15 gpurun_out/nccl_worker_2gpu.log ;;
@@ -43,6 +50,10 @@ for step in "$@"; do
             timeout 600 python tools/admm_ab.py 100000 136 7 3 --variants 0 >> gpurun_out/admm_ab5.log 2>&1
             timeout 600 python tools/admm_ab.py 50001 256 5 3 --variants 0 >> gpurun_out/admm_ab5.log 2>&1
             cat gpurun_out/admm_ab5.log ;;
+    geoleaf) : > gpurun_out/geo_leaf.log; for l in 32 64 128 256; do timeout 600 python tools/kbench.py --geo 1000 1000 --leaf-size $l 2>&1 | grep geodesic_query >> gpurun_out/geo_leaf.log; done; cat gpurun_out/geo_leaf.log ;;
+    ncu_geo) if timeout 600 python tools/kbench.py --geo 1000 1000 > gpurun_out/geo_plain.log 2>&1; then
+              timeout 1500 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum --clock-control none --graph-profiling node --csv --log-file gpurun_out/ncu_geo.csv python tools/kbench.py --geo 1000 1000 > gpurun_out/ncu_geo.log 2>&1; echo "ncu_geo rc=$?"; tail -2 gpurun_out/ncu_geo.log; wc -l gpurun_out/ncu_geo.csv
+            else echo "plain geo failed"; tail -5 gpurun_out/geo_plain.log; fi ;;
     *) echo "unknown step $step" ;;
   esac
 done

@@ -80,11 +80,17 @@ def geo_bench(nx, ny, leaf_size=64):
         geo.support(srcs[state["i"] % len(srcs)], 0, 1.0, 0.1, 0.25, 0, n, out)
         state["i"] += 1
     t1 = timed(one, reps=12, warm=3)
+
+    def one_graph():
+        geo.support_single(srcs[state["i"] % len(srcs)], 0, 1.0, 0.1, 0.25, 0, n, out)
+        state["i"] += 1
+    tg = timed(one_graph, reps=24, warm=4)
     ids = ops.to_device(rng.integers(0, n, size=40).astype(np.int64))
     outb = ops.zeros((40, geo.ldx))
     tb = timed(lambda: geo.support(ids, 1, 2.0, 0.1, 0.25, 0, n, outb), reps=3, warm=1)
     ob = geo.stats["operator_bytes"]
     print(json.dumps({"kernel": "geodesic_query", "grid": [nx, ny], "setup_s": setup, "operator_bytes": ob, "levels": geo.stats["levels"],
+                      "leaf_size": leaf_size, "single_source_graph_ms": tg * 1e3,
                       "single_source_ms": t1 * 1e3, "single_source_GB/s": 1.5 * ob / t1 / 1e9, "batch40_ms": tb * 1e3,
                       "batch40_ms_per_query": tb * 1e3 / 40, "mf_tall": os.environ.get("ASB_MF_TALL", "1"),
                       "note": "single source: 3 of the 4 triangular passes stream every operator once (1.5 x operator bytes)"}), flush=True)
@@ -93,6 +99,7 @@ def geo_bench(nx, ny, leaf_size=64):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--geo", type=int, nargs=2, metavar=("NX", "NY"), default=None, help="time heat-method geodesic queries on a grid")
+    ap.add_argument("--leaf-size", type=int, default=64)
     ap.add_argument("--verts", type=int, default=1000000)
     ap.add_argument("--frames", type=int, default=2000)
     ap.add_argument("--comps", type=int, default=200)
@@ -104,7 +111,7 @@ def main():
     if args.pd:
         return pd_bench(args.pd[0], args.pd[1])
     if args.geo:
-        return geo_bench(args.geo[0], args.geo[1])
+        return geo_bench(args.geo[0], args.geo[1], args.leaf_size)
     if args.once:
         global timed
         _t = timed
