@@ -13,7 +13,8 @@ namespace asb {
 
 constexpr int MF_ROWS = 32;      // rows (forward) / columns (backward) of Mt per CTA; mfsolve.ROWS_PER_BLOCK
 constexpr int MF_CHUNK = 1024;   // staged vector chunk (doubles)
-constexpr int MF_MRHS_MIN = 3;   // from this many right-hand sides on, the register-blocked multi-RHS kernels run
+constexpr int MF_MRHS_MIN = 3;
+constexpr int MF_LEVEL_COLS = 6;   // level table row: forward work list, its length, backward work list, its length, max n1, max n1 + n2   // from this many right-hand sides on, the register-blocked multi-RHS kernels run
 
 struct FrontDesc {
     long long own_start, n1, n2, mt_off, slot_off, upd_off, ldm, row2;
@@ -183,6 +184,102 @@ __global__ void __launch_bounds__(32 * RG) mf_backward_kernel(const FrontDesc* _
     }
 }
 
+// ------------------------------------------------------------------------------------------ small fronts, one RHS
+// The bottom levels of the tree hold tens of thousands of fronts with n1 <= 64 unknowns: per work item (32 rows / 32 columns
+// of one front) there are a few KB of operator and a chain of dependent loads (descriptor -> index lists -> vector ->
+// operator).  The CTA-per-item kernels above keep 8 items in flight per SM and pay two CTA barriers plus a shuffle reduction
+// per row (r02 ncu, 1M-vertex grid, leaf level: forward 339 us for 409 MB, backward 181 us for 448 MB).  Here ONE WARP owns
+// an item, 8 warps per CTA, no shared memory and no barrier: 64 items in flight per SM.
+//   forward : lane = row, walks its own row of Mt (contiguous), f[j] is broadcast from lane j;  sum over j ascending
+//   backward: lane = column, every row of Mt is one coalesced 256-byte read, v[r] is broadcast;  sum over r ascending
+constexpr int MF_SMALL_WARPS = 8;
+
+__global__ void __launch_bounds__(32 * MF_SMALL_WARPS) mf_forward_small_kernel(const FrontDesc* __restrict__ desc,
+                                                                              const double* __restrict__ vals,
+                                                                              const int32_t* __restrict__ src, int64_t slots,
+                                                                              const int32_t* __restrict__ work, int64_t nwork,
+                                                                              const double* __restrict__ rhs, double* __restrict__ y,
+                                                                              double* __restrict__ upd, int64_t ldx, int64_t ldu) {
+    const int64_t item = (int64_t)blockIdx.x * MF_SMALL_WARPS + (threadIdx.x >> 5);
+    if (item >= nwork) return;
+    const int lane = threadIdx.x & 31;
+    const FrontDesc d = desc[work[2 * item]];
+    const int r0 = work[2 * item + 1];
+    const int64_t b = blockIdx.y;
+    const double* rb = rhs + b * ldx + d.own_start;
+    double* ub = upd + b * ldu;
+    const int32_t* src0 = src + d.slot_off;
+    const int32_t* src1 = src + slots + d.slot_off;
+    const int n1 = (int)d.n1, n = (int)(d.n1 + d.n2);
+    const int r = r0 + lane;
+    const long long srow = r < n1 ? r : d.row2 + (r - n1);
+    const double* rowp = vals + d.mt_off + (r < n ? srow : 0) * d.ldm;
+    // columns this item needs: own rows only reach column r0 + 31 (L11^-1 is lower triangular, the rest is stored zeros)
+    const int cmax = (r0 + MF_ROWS <= n1) ? r0 + MF_ROWS : n1;
+    double acc = 0.0;
+    for (int c0 = 0; c0 < cmax; c0 += 32) {
+        const int len = min(32, cmax - c0);
+        double f = 0.0;
+        if (lane < len) f = rb[c0 + lane] + gather_children(src0, src1, ub, c0 + lane);
+        // ldm is a multiple of 8 and c0 of 32: 16-byte loads
+        const double2* rp2 = reinterpret_cast<const double2*>(rowp + c0);
+        const int len2 = len >> 1;
+#pragma unroll 4
+        for (int j2 = 0; j2 < len2; ++j2) {
+            const double2 a = rp2[j2];
+            acc = fma(a.x, __shfl_sync(0xffffffffu, f, 2 * j2), acc);
+            acc = fma(a.y, __shfl_sync(0xffffffffu, f, 2 * j2 + 1), acc);
+        }
+        if (len & 1) acc = fma(rowp[c0 + len - 1], __shfl_sync(0xffffffffu, f, len - 1), acc);
+    }
+    if (r < n) {
+        if (r < n1)
+            y[b * ldx + d.own_start + r] = acc;
+        else
+            ub[d.upd_off + (r - n1)] = gather_children(src0, src1, ub, r) + acc;
+    }
+}
+
+__global__ void __launch_bounds__(32 * MF_SMALL_WARPS) mf_backward_small_kernel(const FrontDesc* __restrict__ desc,
+                                                                               const double* __restrict__ vals,
+                                                                               const int32_t* __restrict__ bnd,
+                                                                               const int32_t* __restrict__ work, int64_t nwork,
+                                                                               const double* __restrict__ y, double* __restrict__ x,
+                                                                               int64_t ldx) {
+    const int64_t item = (int64_t)blockIdx.x * MF_SMALL_WARPS + (threadIdx.x >> 5);
+    if (item >= nwork) return;
+    const int lane = threadIdx.x & 31;
+    const FrontDesc d = desc[work[2 * item]];
+    const int c0 = work[2 * item + 1];
+    const int64_t b = blockIdx.y;
+    const double* yb = y + b * ldx + d.own_start;
+    double* xb = x + b * ldx;
+    const int32_t* bl = bnd + d.upd_off;
+    const int n1 = (int)d.n1, n = (int)(d.n1 + d.n2);
+    const int col = c0 + lane;
+    const bool col_ok = col < n1;
+    const double* mp = vals + d.mt_off + (col_ok ? col : 0);
+    double acc = 0.0;
+    // own rows r < c0 hold zeros in all of this item's columns (lower triangular): start at c0
+    for (int rb0 = c0; rb0 < n; rb0 += 32) {
+        const int len = min(32, n - rb0);
+        double v = 0.0;
+        long long srow = 0;
+        if (lane < len) {
+            const int r = rb0 + lane;
+            v = r < n1 ? yb[r] : xb[bl[r - n1]];
+            srow = r < n1 ? r : d.row2 + (r - n1);
+        }
+#pragma unroll 4
+        for (int j = 0; j < len; ++j) {
+            const long long sr = __shfl_sync(0xffffffffu, srow, j);
+            const double vj = __shfl_sync(0xffffffffu, v, j);
+            acc = fma(mp[sr * d.ldm], vj, acc);
+        }
+    }
+    if (col_ok) xb[d.own_start + col] = acc;
+}
+
 // ------------------------------------------------------------------------------------------ batched right-hand sides
 // A SPLOCS iteration asks for the distance fields of all new component centres at once (tens of right-hand sides).
 // The single-RHS kernels above re-stream the 0.94 GB operator once per right-hand side (measured: 4 514 solves = 17 TB,
@@ -287,15 +384,17 @@ __global__ void __launch_bounds__(256) mf_forward_mrhs_kernel(const FrontDesc* _
 // from global memory (lane (lr, lc) -> Mt[row lr][k + lc]: four 8-byte lanes fill one 32-byte sector) and needs no
 // cross-lane reduction: D[row lr][rhs 2lc, 2lc+1] is the result.  grid.x = work item (front, first of 32 rows),
 // grid.y = group of 8 right-hand sides; 128 threads = 4 warps x 8 rows.
-constexpr int MF_DLD = MF_FCHUNK + 4;   // fs row stride: == 4 mod 16 -> conflict-free B fragments (lane -> fs[lr][k + lc])
-static_assert(MF_FCHUNK % 8 == 0, "chunks are consumed two k-steps at a time");
-
+// The staged chunk FCH is a template parameter: 512 columns (33 KB) suit the top of the tree, but on the bottom levels (n1 <= 64,
+// tens of thousands of 32 x 32 items per group) that much shared memory left 6 CTAs of 4 warps per SM -- r02 ncu, 40 sources:
+// leaf level 2.08 ms for 2.3 GB.  FCH + 4 == 4 mod 16 keeps the B fragments conflict-free (lane -> fs[lr][k + lc]).
+template <int FCH>
 __global__ void __launch_bounds__(128) mf_forward_dmma_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
                                                              const int32_t* __restrict__ src, int64_t slots,
                                                              const int32_t* __restrict__ work, const double* __restrict__ rhs,
                                                              double* __restrict__ y, double* __restrict__ upd, int64_t ldx,
                                                              int64_t ldu, int nrhs) {
-    __shared__ double fs[MF_NB][MF_DLD];
+    static_assert(FCH % 16 == 0, "chunks are consumed two k-steps at a time; FCH + 4 must be 4 mod 16");
+    __shared__ double fs[MF_NB][FCH + 4];
     const FrontDesc d = desc[work[2 * blockIdx.x]];
     const int r0 = work[2 * blockIdx.x + 1];
     const int64_t b0 = (int64_t)blockIdx.y * MF_NB;
@@ -316,8 +415,8 @@ __global__ void __launch_bounds__(128) mf_forward_dmma_kernel(const FrontDesc* _
     const int jmax_w = r0 + warp * 8 >= n ? 0 : (rl < n1 ? rl + 1 : n1);
     const int cmax = (r0 + MF_ROWS <= n1) ? r0 + MF_ROWS : n1;          // columns the CTA stages
     double acc0 = 0.0, acc1 = 0.0, odd0 = 0.0, odd1 = 0.0;   // two independent DMMA chains (even / odd k-steps)
-    for (int c0 = 0; c0 < cmax; c0 += MF_FCHUNK) {
-        const int len = min(MF_FCHUNK, cmax - c0);
+    for (int c0 = 0; c0 < cmax; c0 += FCH) {
+        const int len = min(FCH, cmax - c0);
         const int len4 = (len + 7) & ~7;
         __syncthreads();
         for (int j = threadIdx.x; j < len4; j += blockDim.x) {
@@ -437,11 +536,12 @@ __global__ void __launch_bounds__(256) mf_backward_mrhs_kernel(const FrontDesc* 
 // 2lc+1] is the result.  grid.x = work item (front, first of 32 columns), grid.y = group of 8 right-hand sides; 128 threads.
 constexpr int MF_VLD = 12;
 
+template <int BCH>
 __global__ void __launch_bounds__(128) mf_backward_dmma_kernel(const FrontDesc* __restrict__ desc, const double* __restrict__ vals,
                                                               const int32_t* __restrict__ bnd, const int32_t* __restrict__ work,
                                                               const double* __restrict__ y, double* __restrict__ x, int64_t ldx,
                                                               int nrhs) {
-    __shared__ double vs[MF_BCHUNK * MF_VLD];
+    __shared__ double vs[BCH * MF_VLD];
     const FrontDesc d = desc[work[2 * blockIdx.x]];
     const int c0 = work[2 * blockIdx.x + 1];
     const int64_t b0 = (int64_t)blockIdx.y * MF_NB;
@@ -456,8 +556,8 @@ __global__ void __launch_bounds__(128) mf_backward_dmma_kernel(const FrontDesc* 
     const double* mp = vals + d.mt_off + (col_ok ? cola : 0);
     double acc0 = 0.0, acc1 = 0.0, odd0 = 0.0, odd1 = 0.0;
     // own rows r < c0 hold zeros in all of this CTA's columns (lower triangular): start at c0 (a multiple of 32)
-    for (int rb0 = c0; rb0 < n; rb0 += MF_BCHUNK) {
-        const int len = min(MF_BCHUNK, n - rb0);
+    for (int rb0 = c0; rb0 < n; rb0 += BCH) {
+        const int len = min(BCH, n - rb0);
         const int len8 = (len + 7) & ~7;
         __syncthreads();
         for (int e = threadIdx.x; e < len8 * MF_NB; e += blockDim.x) {
@@ -507,67 +607,105 @@ static bool mf_tall() {
     return v != 0;
 }
 
+// max_n1 / max_n: the largest n1 / n1 + n2 of the fronts in the work list (0 = unknown): they pick the staged chunk of the
+// batched kernels and send the single-RHS passes of levels made of many small fronts to the warp-per-item kernels
+static int mf_forward_impl(const int64_t* desc, const double* vals, const int32_t* src, int64_t slots, const int32_t* work,
+                           int64_t nwork, const double* rhs, double* y, double* upd, int64_t nrhs, int64_t ldx, int64_t ldu,
+                           int64_t max_n1, cudaStream_t st) {
+    static const int fwd_dmma = [] {
+        const char* e = std::getenv("ASB_MF_FWD_DMMA");
+        return e ? std::atoi(e) : 1;
+    }();
+    static const int small = [] {
+        const char* e = std::getenv("ASB_MF_SMALL");
+        return e ? std::atoi(e) : 1;
+    }();
+    const FrontDesc* fd = reinterpret_cast<const FrontDesc*>(desc);
+    const dim3 gridg((unsigned)nwork, (unsigned)cdiv(nrhs, MF_NB));
+    if (nrhs >= MF_MRHS_MIN && fwd_dmma) {
+        if (small && max_n1 > 0 && max_n1 <= 64)
+            mf_forward_dmma_kernel<64><<<gridg, 128, 0, st>>>(fd, vals, src, slots, work, rhs, y, upd, ldx, ldu, (int)nrhs);
+        else if (small && max_n1 > 0 && max_n1 <= 128)
+            mf_forward_dmma_kernel<128><<<gridg, 128, 0, st>>>(fd, vals, src, slots, work, rhs, y, upd, ldx, ldu, (int)nrhs);
+        else
+            mf_forward_dmma_kernel<MF_FCHUNK><<<gridg, 128, 0, st>>>(fd, vals, src, slots, work, rhs, y, upd, ldx, ldu, (int)nrhs);
+    } else if (nrhs >= MF_MRHS_MIN)
+        mf_forward_mrhs_kernel<<<gridg, 256, 0, st>>>(fd, vals, src, slots, work, rhs, y, upd, ldx, ldu, (int)nrhs);
+    else if (nwork * nrhs <= 2LL * sm_count() && mf_tall())
+        mf_forward_kernel<1><<<dim3((unsigned)nwork, (unsigned)nrhs), 1024, 0, st>>>(fd, vals, src, slots, work, rhs, y, upd, ldx, ldu);
+    else if (small && max_n1 > 0 && max_n1 <= 64 && nwork >= 16LL * sm_count())
+        mf_forward_small_kernel<<<dim3((unsigned)cdiv(nwork, MF_SMALL_WARPS), (unsigned)nrhs), 32 * MF_SMALL_WARPS, 0, st>>>(
+            fd, vals, src, slots, work, nwork, rhs, y, upd, ldx, ldu);
+    else
+        mf_forward_kernel<4><<<dim3((unsigned)nwork, (unsigned)nrhs), 256, 0, st>>>(fd, vals, src, slots, work, rhs, y, upd, ldx, ldu);
+    ASB_LAUNCH_CHECK();
+    return ASB_OK;
+}
+
+static int mf_backward_impl(const int64_t* desc, const double* vals, const int32_t* bnd, const int32_t* work, int64_t nwork,
+                            const double* y, double* x, int64_t nrhs, int64_t ldx, int64_t max_n, cudaStream_t st) {
+    static const int bwd_dmma = [] {
+        const char* e = std::getenv("ASB_MF_BWD_DMMA");
+        return e ? std::atoi(e) : 1;
+    }();
+    static const int small = [] {
+        const char* e = std::getenv("ASB_MF_SMALL");
+        return e ? std::atoi(e) : 1;
+    }();
+    const FrontDesc* fd = reinterpret_cast<const FrontDesc*>(desc);
+    const dim3 gridg((unsigned)nwork, (unsigned)cdiv(nrhs, MF_NB));
+    if (nrhs >= MF_MRHS_MIN && bwd_dmma) {
+        if (small && max_n > 0 && max_n <= 64)
+            mf_backward_dmma_kernel<64><<<gridg, 128, 0, st>>>(fd, vals, bnd, work, y, x, ldx, (int)nrhs);
+        else if (small && max_n > 0 && max_n <= 128)
+            mf_backward_dmma_kernel<128><<<gridg, 128, 0, st>>>(fd, vals, bnd, work, y, x, ldx, (int)nrhs);
+        else
+            mf_backward_dmma_kernel<MF_BCHUNK><<<gridg, 128, 0, st>>>(fd, vals, bnd, work, y, x, ldx, (int)nrhs);
+    } else if (nrhs >= MF_MRHS_MIN)
+        mf_backward_mrhs_kernel<<<gridg, 256, 0, st>>>(fd, vals, bnd, work, y, x, ldx, (int)nrhs);
+    else if (nwork * nrhs <= 2LL * sm_count() && mf_tall())
+        mf_backward_kernel<32><<<dim3((unsigned)nwork, (unsigned)nrhs), 1024, 0, st>>>(fd, vals, bnd, work, y, x, ldx);
+    else if (small && max_n > 0 && max_n <= 256 && nwork >= 16LL * sm_count())
+        mf_backward_small_kernel<<<dim3((unsigned)cdiv(nwork, MF_SMALL_WARPS), (unsigned)nrhs), 32 * MF_SMALL_WARPS, 0, st>>>(
+            fd, vals, bnd, work, nwork, y, x, ldx);
+    else
+        mf_backward_kernel<8><<<dim3((unsigned)nwork, (unsigned)nrhs), 256, 0, st>>>(fd, vals, bnd, work, y, x, ldx);
+    ASB_LAUNCH_CHECK();
+    return ASB_OK;
+}
+
 extern "C" {
 
 int asb_mf_forward(const int64_t* desc, const double* vals, const int32_t* src, int64_t slots, const int32_t* work,
                    int64_t nwork, const double* rhs, double* y, double* upd, int64_t nrhs, int64_t ldx, int64_t ldu,
                    asb_stream_t stream) {
     ASB_REQUIRE(desc && vals && src && work && rhs && y && upd && nwork > 0 && nrhs > 0 && nrhs < 65536, "mf_forward: bad arguments");
-    static const int fwd_dmma = [] {
-        const char* e = std::getenv("ASB_MF_FWD_DMMA");
-        return e ? std::atoi(e) : 1;
-    }();
-    if (nrhs >= MF_MRHS_MIN && fwd_dmma)
-        mf_forward_dmma_kernel<<<dim3((unsigned)nwork, (unsigned)cdiv(nrhs, MF_NB)), 128, 0, S(stream)>>>(
-            reinterpret_cast<const FrontDesc*>(desc), vals, src, slots, work, rhs, y, upd, ldx, ldu, (int)nrhs);
-    else if (nrhs >= MF_MRHS_MIN)
-        mf_forward_mrhs_kernel<<<dim3((unsigned)nwork, (unsigned)cdiv(nrhs, MF_NB)), 256, 0, S(stream)>>>(
-            reinterpret_cast<const FrontDesc*>(desc), vals, src, slots, work, rhs, y, upd, ldx, ldu, (int)nrhs);
-    else if (nwork * nrhs <= 2LL * sm_count() && mf_tall())
-        mf_forward_kernel<1><<<dim3((unsigned)nwork, (unsigned)nrhs), 1024, 0, S(stream)>>>(
-            reinterpret_cast<const FrontDesc*>(desc), vals, src, slots, work, rhs, y, upd, ldx, ldu);
-    else
-        mf_forward_kernel<4><<<dim3((unsigned)nwork, (unsigned)nrhs), 256, 0, S(stream)>>>(
-            reinterpret_cast<const FrontDesc*>(desc), vals, src, slots, work, rhs, y, upd, ldx, ldu);
-    ASB_LAUNCH_CHECK();
-    return ASB_OK;
+    return mf_forward_impl(desc, vals, src, slots, work, nwork, rhs, y, upd, nrhs, ldx, ldu, 0, S(stream));
 }
 
 int asb_mf_backward(const int64_t* desc, const double* vals, const int32_t* bnd, const int32_t* work, int64_t nwork,
                     const double* y, double* x, int64_t nrhs, int64_t ldx, asb_stream_t stream) {
     ASB_REQUIRE(desc && vals && bnd && work && y && x && nwork > 0 && nrhs > 0 && nrhs < 65536, "mf_backward: bad arguments");
-    static const int bwd_dmma = [] {
-        const char* e = std::getenv("ASB_MF_BWD_DMMA");
-        return e ? std::atoi(e) : 1;
-    }();
-    if (nrhs >= MF_MRHS_MIN && bwd_dmma)
-        mf_backward_dmma_kernel<<<dim3((unsigned)nwork, (unsigned)cdiv(nrhs, MF_NB)), 128, 0, S(stream)>>>(
-            reinterpret_cast<const FrontDesc*>(desc), vals, bnd, work, y, x, ldx, (int)nrhs);
-    else if (nrhs >= MF_MRHS_MIN)
-        mf_backward_mrhs_kernel<<<dim3((unsigned)nwork, (unsigned)cdiv(nrhs, MF_NB)), 256, 0, S(stream)>>>(
-            reinterpret_cast<const FrontDesc*>(desc), vals, bnd, work, y, x, ldx, (int)nrhs);
-    else if (nwork * nrhs <= 2LL * sm_count() && mf_tall())
-        mf_backward_kernel<32><<<dim3((unsigned)nwork, (unsigned)nrhs), 1024, 0, S(stream)>>>(
-            reinterpret_cast<const FrontDesc*>(desc), vals, bnd, work, y, x, ldx);
-    else
-        mf_backward_kernel<8><<<dim3((unsigned)nwork, (unsigned)nrhs), 256, 0, S(stream)>>>(
-            reinterpret_cast<const FrontDesc*>(desc), vals, bnd, work, y, x, ldx);
-    ASB_LAUNCH_CHECK();
-    return ASB_OK;
+    return mf_backward_impl(desc, vals, bnd, work, nwork, y, x, nrhs, ldx, 0, S(stream));
 }
 
 int asb_mf_solve(const int64_t* desc, const double* vals, const int32_t* src, int64_t slots, const int32_t* bnd,
                  const int64_t* levels, int64_t nlevels, const double* rhs, double* y, double* x, double* upd, int64_t nrhs,
                  int64_t ldx, int64_t ldu, asb_stream_t stream) {
     ASB_REQUIRE(levels && nlevels > 0 && nlevels < 4096, "mf_solve: bad level table");
+    ASB_REQUIRE(desc && vals && src && bnd && rhs && y && x && upd && nrhs > 0 && nrhs < 65536, "mf_solve: bad arguments");
     for (int64_t l = nlevels - 1; l >= 0; --l) {
-        const int rc = asb_mf_forward(desc, vals, src, slots, reinterpret_cast<const int32_t*>(levels[4 * l]), levels[4 * l + 1], rhs,
-                                      y, upd, nrhs, ldx, ldu, stream);
+        const int64_t* lv = levels + MF_LEVEL_COLS * l;
+        if (lv[1] <= 0) continue;
+        const int rc = mf_forward_impl(desc, vals, src, slots, reinterpret_cast<const int32_t*>(lv[0]), lv[1], rhs, y, upd, nrhs, ldx,
+                                       ldu, lv[4], S(stream));
         if (rc != ASB_OK) return rc;
     }
     for (int64_t l = 0; l < nlevels; ++l) {
-        const int rc = asb_mf_backward(desc, vals, bnd, reinterpret_cast<const int32_t*>(levels[4 * l + 2]), levels[4 * l + 3], y, x,
-                                       nrhs, ldx, stream);
+        const int64_t* lv = levels + MF_LEVEL_COLS * l;
+        if (lv[3] <= 0) continue;
+        const int rc = mf_backward_impl(desc, vals, bnd, reinterpret_cast<const int32_t*>(lv[2]), lv[3], y, x, nrhs, ldx, lv[5],
+                                        S(stream));
         if (rc != ASB_OK) return rc;
     }
     return ASB_OK;
@@ -595,8 +733,9 @@ int asb_mf_solve_delta(const int64_t* desc, const double* vals, const int32_t* s
         ASB_LAUNCH_CHECK();
     }
     for (int64_t l = 0; l < nlevels; ++l) {
-        const int rc = asb_mf_backward(desc, vals, bnd, reinterpret_cast<const int32_t*>(levels[4 * l + 2]), levels[4 * l + 3], y, x,
-                                       nrhs, ldx, stream);
+        const int64_t* lv = levels + MF_LEVEL_COLS * l;
+        if (lv[3] <= 0) continue;
+        const int rc = mf_backward_impl(desc, vals, bnd, reinterpret_cast<const int32_t*>(lv[2]), lv[3], y, x, nrhs, ldx, lv[5], st);
         if (rc != ASB_OK) return rc;
     }
     return ASB_OK;

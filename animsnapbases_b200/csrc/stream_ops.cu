@@ -321,10 +321,13 @@ __global__ void __launch_bounds__(128) rank_update_kernel(double* __restrict__ R
         }
         __syncthreads();
         if (act) {
+            // FU frames per trip with all 3 * FU loads issued before the arithmetic: one frame per trip left 3 loads in flight
+            // per thread (r01 ncu: 31 % occupancy, 4.5 TB/s); the per-element operation order and the order of the energy
+            // sum over f are unchanged
+            constexpr int FU = 4;
             double* p = R + fb * 3 * ld + n;
-            for (int64_t f = fb; f < fe; ++f, p += 3 * ld) {
-                double x = p[0], y = p[ld], z = p[2 * ld];
-                const double* wr = wsh + (f - fb) * NB;
+            int64_t f = fb;
+            auto one = [&](double x, double y, double z, const double* wr, double* q) {
 #pragma unroll
                 for (int j = 0; j < NB; ++j) {
                     // `R -= outer(wk, ck)`: product rounded, then subtracted (no fma), j ascending
@@ -333,11 +336,21 @@ __global__ void __launch_bounds__(128) rank_update_kernel(double* __restrict__ R
                     y = __dsub_rn(y, __dmul_rn(wj, c[j][1]));
                     z = __dsub_rn(z, __dmul_rn(wj, c[j][2]));
                 }
-                p[0] = x;
-                p[ld] = y;
-                p[2 * ld] = z;
+                q[0] = x;
+                q[ld] = y;
+                q[2 * ld] = z;
                 e += __dadd_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)), __dmul_rn(z, z));
+            };
+            for (; f + FU <= fe; f += FU, p += FU * 3 * ld) {
+                double v[FU][3];
+#pragma unroll
+                for (int u = 0; u < FU; ++u)
+#pragma unroll
+                    for (int d = 0; d < 3; ++d) v[u][d] = p[(u * 3 + d) * ld];
+#pragma unroll
+                for (int u = 0; u < FU; ++u) one(v[u][0], v[u][1], v[u][2], wsh + (f - fb + u) * NB, p + u * 3 * ld);
             }
+            for (; f < fe; ++f, p += 3 * ld) one(p[0], p[ld], p[2 * ld], wsh + (f - fb) * NB, p);
         }
     }
     if (n < ld) e_part[(int64_t)blockIdx.y * ld + n] = e;

@@ -336,11 +336,14 @@ class MultifrontalSolver:
         self.order_host = sym.order
         self.work_fwd = [ops.to_device(w) for w in sym.work_fwd]
         self.work_bwd = [ops.to_device(w) for w in sym.work_bwd]
-        # host table for asb_mf_solve (root level first): work-list pointers and lengths of every level
+        # host table for asb_mf_solve (root level first): work-list pointers and lengths of every level, and the largest n1 /
+        # n1 + n2 of its fronts (the kernels pick their staging size and the small-front variants by them)
         self.levels_host = None
         if hasattr(ops, "mf_solve"):
-            self.levels_host = np.array([[wf.data_ptr(), wf.shape[0], wb.data_ptr(), wb.shape[0]]
-                                         for wf, wb in zip(self.work_fwd, self.work_bwd)], dtype=np.int64)
+            nn_all = sym.n1 + sym.n2
+            self.levels_host = np.array([[wf.data_ptr(), wf.shape[0], wb.data_ptr(), wb.shape[0],
+                                          int(sym.n1[sym.depth == d].max()), int(nn_all[sym.depth == d].max())]
+                                         for d, (wf, wb) in enumerate(zip(self.work_fwd, self.work_bwd))], dtype=np.int64)
         # tree tables for asb_mf_solve_delta: parent / depth / first elimination position of every front, and the number
         # of 32-row blocks of the largest front of every level
         self.tree = None

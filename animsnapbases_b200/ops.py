@@ -447,7 +447,8 @@ class CudaOps:
                    y.shape[0], y.stride(0))
 
     def mf_solve(self, desc, vals, src, slots, bnd, levels_host, rhs, y, x, upd):
-        """All levels of one multifrontal solve from a single C call; levels_host: (nlevels, 4) int64 numpy (root first)."""
+        """All levels of one multifrontal solve from a single C call; levels_host: (nlevels, 6) int64 numpy (root first):
+        forward work list and length, backward work list and length, max n1, max n1 + n2 of the level."""
         self._call("asb_mf_solve", self._p(desc), self._p(vals), self._p(src), slots, self._p(bnd),
                    ctypes.c_void_p(levels_host.ctypes.data), levels_host.shape[0], self._p(rhs), self._p(y), self._p(x), self._p(upd),
                    rhs.shape[0], rhs.stride(0), upd.stride(0))

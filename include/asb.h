@@ -268,8 +268,10 @@ int asb_mf_backward(const int64_t* desc, const double* vals, const int32_t* bnd,
                     const double* y, double* x, int64_t nrhs, int64_t ldx, asb_stream_t stream);
 /* One complete solve = asb_mf_forward over the levels (deepest first) then asb_mf_backward (root first), issued from ONE
  * call so that the 2 x depth launches of a query go out back to back (a heat-method query is latency bound: 60 launches of
- * ~10-100 us).  `levels` is a HOST array, nlevels x 4 int64, root level first:
- * {device pointer of the level's forward work list, its length, device pointer of the backward work list, its length}. */
+ * ~10-100 us).  `levels` is a HOST array, nlevels x 6 int64, root level first:
+ * {device pointer of the level's forward work list, its length, device pointer of the backward work list, its length,
+ *  largest n1 of the level's fronts, largest n1 + n2} -- the last two (0 = unknown) size the staging buffers of the batched
+ * kernels and send single right-hand sides on levels of many small fronts (n1 <= 64) to warp-per-item kernels. */
 int asb_mf_solve(const int64_t* desc, const double* vals, const int32_t* src, int64_t slots, const int32_t* bnd,
                  const int64_t* levels, int64_t nlevels, const double* rhs, double* y, double* x, double* upd, int64_t nrhs,
                  int64_t ldx, int64_t ldu, asb_stream_t stream);

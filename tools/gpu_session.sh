@@ -54,6 +54,9 @@ for step in "$@"; do
     ncu_geo) if timeout 600 python tools/kbench.py --geo 1000 1000 > gpurun_out/geo_plain.log 2>&1; then
               timeout 1500 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum --clock-control none --graph-profiling node --csv --log-file gpurun_out/ncu_geo.csv python tools/kbench.py --geo 1000 1000 > gpurun_out/ncu_geo.log 2>&1; echo "ncu_geo rc=$?"; tail -2 gpurun_out/ncu_geo.log; wc -l gpurun_out/ncu_geo.csv
             else echo "plain geo failed"; tail -5 gpurun_out/geo_plain.log; fi ;;
+    geo1)   timeout 600 python tools/kbench.py --geo 1000 1000 2>&1 | grep geodesic_query | tee gpurun_out/geo1.log | cut -c1-600
+            ASB_MF_SMALL=0 timeout 600 python tools/kbench.py --geo 1000 1000 2>&1 | grep geodesic_query | sed 's/^/ASB_MF_SMALL=0 /' | tee -a gpurun_out/geo1.log | cut -c1-600 ;;
+    stream) timeout 600 python tools/kbench.py --only stream 2>&1 | tee gpurun_out/kbench_stream.log | tail -12 ;;
     *) echo "unknown step $step" ;;
   esac
 done
