@@ -189,6 +189,27 @@ __global__ void argmax_stage1_kernel(const double* __restrict__ v, int64_t n, in
     a = block_argmax(a, shv, shi);
     if (threadIdx.x == 0) { pv[blockIdx.x] = a.v; pi[blockIdx.x] = a.i; }
 }
+// stage 1 of the masked variant: only entries whose vertex lies OUTSIDE the ball |pos[i] - pos[centre]| <= radius compete
+__global__ void argmax_outside_stage1_kernel(const double* __restrict__ v, int64_t n, int64_t chunk, int64_t index_offset,
+                                             const double* __restrict__ pos, const int64_t* __restrict__ centre, double r2,
+                                             double* __restrict__ pv, long long* __restrict__ pi) {
+    __shared__ double shv[33];
+    __shared__ long long shi[33];
+    const int64_t i0 = (int64_t)blockIdx.x * chunk, i1 = min(n, i0 + chunk);
+    const int64_t c = centre[0];
+    const double cx = pos[3 * c], cy = pos[3 * c + 1], cz = pos[3 * c + 2];
+    ArgMax a;
+    a.v = -INFINITY;
+    a.i = 0x7fffffffffffffffLL;
+    for (int64_t i = i0 + threadIdx.x; i < i1; i += blockDim.x) {
+        const double* p = pos + 3 * (i + index_offset);
+        const double dx = p[0] - cx, dy = p[1] - cy, dz = p[2] - cz;
+        const double x = v[i];
+        if (dx * dx + dy * dy + dz * dz > r2 && x > a.v) { a.v = x; a.i = i; }
+    }
+    a = block_argmax(a, shv, shi);
+    if (threadIdx.x == 0) { pv[blockIdx.x] = a.v; pi[blockIdx.x] = a.i; }
+}
 __global__ void argmax_stage2_kernel(const double* __restrict__ pv, const long long* __restrict__ pi, int64_t nb,
                                      int64_t index_offset, double* __restrict__ out_val, int64_t* __restrict__ out_idx) {
     __shared__ double shv[33];
@@ -203,7 +224,46 @@ __global__ void argmax_stage2_kernel(const double* __restrict__ pv, const long l
         a = argmax_combine(a, t);
     }
     a = block_argmax(a, shv, shi);
-    if (threadIdx.x == 0) { out_val[0] = a.v; out_idx[0] = (int64_t)a.i + index_offset; }
+    if (threadIdx.x == 0) {
+        out_val[0] = a.v;
+        out_idx[0] = a.i == 0x7fffffffffffffffLL ? (int64_t)a.i : (int64_t)a.i + index_offset;   // no candidate: INT64_MAX
+    }
+}
+
+// second stage of the masked argmax: (value, global index bit pattern) as ONE 16-byte record, ready for an all-gather
+__global__ void argmax_pair_stage2_kernel(const double* __restrict__ pv, const long long* __restrict__ pi, int64_t nb,
+                                          int64_t index_offset, double* __restrict__ out_pair) {
+    __shared__ double shv[33];
+    __shared__ long long shi[33];
+    ArgMax a;
+    a.v = -INFINITY;
+    a.i = 0x7fffffffffffffffLL;
+    for (int64_t b = threadIdx.x; b < nb; b += blockDim.x) {
+        ArgMax t;
+        t.v = pv[b];
+        t.i = pi[b];
+        a = argmax_combine(a, t);
+    }
+    a = block_argmax(a, shv, shi);
+    if (threadIdx.x == 0) {
+        out_pair[0] = a.v;
+        const long long gi = a.i == 0x7fffffffffffffffLL ? a.i : a.i + index_offset;   // no candidate: INT64_MAX
+        out_pair[1] = __longlong_as_double(gi);
+    }
+}
+// largest value over `world` records, ties to the lowest index (np.argmax over the concatenated shards); no candidate
+// anywhere (-inf): the fallback index
+__global__ void select_pair_kernel(const double* __restrict__ all, int world, const int64_t* __restrict__ fallback,
+                                   int64_t* __restrict__ out_idx) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double bv = -INFINITY;
+    long long bi = 0x7fffffffffffffffLL;
+    for (int r = 0; r < world; ++r) {
+        const double v = all[2 * r];
+        const long long i = __double_as_longlong(all[2 * r + 1]);
+        if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; }
+    }
+    out_idx[0] = (bv == -INFINITY || bi == 0x7fffffffffffffffLL) ? fallback[0] : (int64_t)bi;
 }
 
 // g_part[fs][c] = sum_{f in slab} w[f] R[f][c]; two columns per thread, 8 frames in flight
@@ -561,6 +621,28 @@ int asb_argmax_first(const double* v, int64_t n, int64_t index_offset, double* o
     argmax_stage1_kernel<<<(unsigned)nb, 256, 0, S(stream)>>>(v, n, chunk, pv, pi);
     ASB_LAUNCH_CHECK();
     argmax_stage2_kernel<<<1, 256, 0, S(stream)>>>(pv, pi, nb, index_offset, out_val, out_idx);
+    ASB_LAUNCH_CHECK();
+    return ASB_OK;
+}
+
+int asb_argmax_outside_ball(const double* v, int64_t n, int64_t index_offset, const double* pos, const int64_t* centre,
+                            double radius, double* out_pair, void* ws, asb_stream_t stream) {
+    ASB_REQUIRE(v && pos && centre && out_pair && ws && n > 0 && radius >= 0.0, "argmax_outside_ball: bad arguments");
+    int64_t nb = std::min<int64_t>(cdiv(n, 1024), 2048);
+    const int64_t chunk = cdiv(n, nb);
+    nb = cdiv(n, chunk);
+    double* pv = reinterpret_cast<double*>(ws);
+    long long* pi = reinterpret_cast<long long*>(pv + 2048);
+    argmax_outside_stage1_kernel<<<(unsigned)nb, 256, 0, S(stream)>>>(v, n, chunk, index_offset, pos, centre, radius * radius, pv, pi);
+    ASB_LAUNCH_CHECK();
+    argmax_pair_stage2_kernel<<<1, 256, 0, S(stream)>>>(pv, pi, nb, index_offset, out_pair);
+    ASB_LAUNCH_CHECK();
+    return ASB_OK;
+}
+
+int asb_select_pair(const double* all, int64_t world, const int64_t* fallback, int64_t* out_idx, asb_stream_t stream) {
+    ASB_REQUIRE(all && fallback && out_idx && world > 0 && world < (1 << 20), "select_pair: bad arguments");
+    select_pair_kernel<<<1, 32, 0, S(stream)>>>(all, (int)world, fallback, out_idx);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
 }

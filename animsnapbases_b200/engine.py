@@ -178,6 +178,27 @@ def prepare_snapshots(ops, comm, verts_local, mass_local, rest_shape, shard, sta
 # ====================================================================================== deflation (k3-k9)
 def deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1, dmax=0.25, block=8,
             keep_residual=True):
+    """`_deflate` on the current stream, or (ASB_MAIN_PRIORITY=-1, CUDA only) on a high-priority stream of its own so that the
+    short dependent kernels of a pick are dispatched ahead of the geodesic queries running beside them."""
+    prio = int(_os.environ.get("ASB_MAIN_PRIORITY", "0"))
+    if prio == 0 or getattr(ops, "name", "") != "cuda":
+        return _deflate(ops, comm, X, shard, K, local_support, geodesic, dmin, dmax, block, keep_residual)
+    cur = torch.cuda.current_stream(ops.device)
+    hp = getattr(ops, "_main_hp", None)
+    if hp is None:
+        hp = ops._main_hp = torch.cuda.Stream(ops.device, priority=prio)
+    hp.wait_stream(cur)
+    with torch.cuda.stream(hp):
+        out = _deflate(ops, comm, X, shard, K, local_support, geodesic, dmin, dmax, block, keep_residual)
+    cur.wait_stream(hp)
+    for t in out:
+        if isinstance(t, torch.Tensor):
+            t.record_stream(cur)
+    return out
+
+
+def _deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1, dmax=0.25, block=8,
+             keep_residual=True):
     """Greedy deflation of snapbases/posComponents.py:67-122 on a row shard.
 
     The residual R is explicit (like the reference) but the K rank-1 updates are applied `block` at a time
@@ -202,6 +223,32 @@ def deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1
     s = ops.zeros((1, ld)) if local_support else None
     pick = _Picker(ops, comm, F)
     trace = _Trace(ops) if _os.environ.get("ASB_TRACE_DEFLATE") and getattr(ops, "name", "") == "cuda" else None
+    # Pick prediction (local support only).  A component with local support changes the residual -- and with it the energies
+    # the next pick is taken from -- only where its support map is non-zero: within geodesic, hence Euclidean, distance dmax of
+    # its vertex.  So while component k is still being deflated, the largest energy OUTSIDE that ball already names pick k + 1
+    # unless that pick falls inside the ball, and the heat-method query of the predicted vertex (single source, latency bound,
+    # replicated on every rank: the critical path of a component on 8 GPUs) can run one component ahead, beside the HBM pass of
+    # component k.  The prediction is verified against the real pick on the host (two int64 through pinned memory, read while
+    # the HBM pass runs); a miss just runs the query as before, so results never depend on it.
+    # Measured on B200s (1M x 2000, K = 200; 96 % of the picks predicted): 8 GPUs 584 -> 552 ms of deflation per build; on 1 and
+    # 2 GPUs the HBM pass (6.7 / 3.5 ms) is longer than the query and the memory system is saturated either way, the early query
+    # only gets in the way of the short kernels of the next pick (2 GPUs: 1 249 -> 1 286 ms).  Hence on from 4 ranks;
+    # ASB_DEFLATE_PREDICT=0 / 1 forces it off / on.
+    want = _os.environ.get("ASB_DEFLATE_PREDICT", "")
+    predict = (local_support and getattr(geodesic, "vpos", None) is not None and hasattr(ops, "argmax_outside_ball")
+               and K > 1 and (want == "1" or (want != "0" and comm.world >= 4)))
+    if predict:
+        s_buf = [s, ops.zeros((1, ld))]
+        spec_idx = [ops.zeros((1,), I64), ops.zeros((1,), I64)]       # prediction made at component k: buffer k & 1
+        spec_idx[0].fill_(-1)
+        spec_idx[1].fill_(-1)
+        spec_pair = ops.zeros((2,))
+        spec_all = ops.zeros((comm.world, 2))
+        pair = ops.zeros((2,), I64)
+        pinned = getattr(ops, "name", "") == "cuda"
+        pair_host = torch.empty((2,), dtype=I64, pin_memory=pinned)
+        radius = float(_os.environ.get("ASB_DEFLATE_PREDICT_RADIUS", "1.05")) * float(dmax)
+        cur, have_spec, hits = 0, False, 0
     k0 = 0
     for k in range(K):
         if trace is not None:
@@ -209,6 +256,10 @@ def deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1
         ops.argmax_first(e, N, row0, val, idx)
         pick(R, N, val, idx, row0, W, k0, C, k - k0, traj)
         picked[k:k + 1].copy_(idx)
+        if predict:
+            pair[0:1].copy_(idx)
+            pair[1:2].copy_(spec_idx[(k - 1) & 1])
+            pair_host.copy_(pair, non_blocking=True)
         ops.traj_rank1(traj, F, local_support, W, k, k0, coef, scal)
         picked_ev = ops.record_event() if local_support else None
         if trace is not None:
@@ -216,7 +267,40 @@ def deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1
         ops.deflate_gemv(R, N, W, k, g)
         if trace is not None:
             trace.mark("gemv")
-        if local_support:
+        if local_support and predict:
+            if picked_ev is not None:
+                picked_ev.synchronize()                     # the HBM pass just queued keeps the GPU busy meanwhile
+            hit = have_spec and int(pair_host[0]) == int(pair_host[1])
+            hits += int(hit)
+            if have_spec:
+                cur ^= 1                                    # the buffer the query of the predicted vertex wrote (or writes) into
+            s_cur = s_buf[cur]
+            m_ready = None
+            if k + 1 < K:
+                # lane 1: prediction of pick k + 1 from the energies BEFORE component k is deflated (finish below waits for it).
+                # It has a stream of its own: behind the queries of lane 0 it -- and, through the in-order NCCL stream, the
+                # all-gather of the NEXT real pick -- would wait for a query it does not depend on.
+                with ops.fork(after=picked_ev, lane=1):
+                    ops.argmax_outside_ball(e, N, row0, geodesic.vpos, idx, radius, spec_pair)
+                    comm.all_gather_rows(spec_pair, out=spec_all)
+                    ops.select_pair(spec_all, comm.world, idx, spec_idx[k & 1])     # nothing outside the ball: the same vertex
+                    m_ready = ops.record_event()
+            with ops.fork(after=picked_ev, lane=0):
+                if trace is not None:
+                    trace.mark("geo0")
+                if not hit:
+                    geodesic.support_single(idx, 0, 1.0, dmin, dmax, row0, N, s_cur)
+                cur_ready = ops.record_event()              # s_cur holds the support map of pick k
+                if trace is not None:
+                    trace.mark("geo1")
+                if k + 1 < K:
+                    ops.wait_event(m_ready)
+                    geodesic.support_single(spec_idx[k & 1], 0, 1.0, dmin, dmax, row0, N, s_buf[cur ^ 1])
+                    have_spec = True
+            ops.wait_event(cur_ready)
+            ops.wait_event(m_ready)
+            s_use = s_cur
+        elif local_support:
             # the heat-method query of the picked vertex (single source, latency bound, replicated on every rank) runs on the
             # side stream beside the HBM-bound pass.  It is queued AFTER the pass (r01 queued its ~75 launches first: 2 ms of
             # host time per component during which the main stream sat idle) and as ONE CUDA-graph launch.
@@ -227,9 +311,10 @@ def deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1
                 if trace is not None:
                     trace.mark("geo1")
             ops.join()
+            s_use = s
         if trace is not None:
             trace.mark("joined")
-        ops.deflate_finish(g, C, k, k0, coef, s[0] if local_support else None, scal, e, N, meas[k])
+        ops.deflate_finish(g, C, k, k0, coef, s_use[0] if local_support else None, scal, e, N, meas[k])
         if trace is not None:
             trace.mark("finished")
         if k - k0 + 1 == block or k == K - 1:
@@ -237,6 +322,10 @@ def deflate(ops, comm, X, shard, K, local_support=False, geodesic=None, dmin=0.1
             k0 = k + 1
         if trace is not None:
             trace.mark("end")
+    if predict:
+        ops.join()
+        if hasattr(geodesic, "stats"):
+            geodesic.stats["predicted_picks"] = geodesic.stats.get("predicted_picks", 0) + hits
     _reduce_norms(comm, meas)
     if trace is not None:
         trace.report()

@@ -99,6 +99,7 @@ class HeatGeodesics:
         h = np.mean([_veclen(e01), _veclen(e12), _veclen(e20)])
         self.t = m * h ** 2
         Lc, va = cotan_laplacian(verts, tris)
+        self.vpos = ops.to_device(np.ascontiguousarray(verts))        # rest positions (n, 3): pick prediction of engine.deflate
         self.heat = MultifrontalSolver(ops, (sparse.diags(va) - self.t * Lc).tocsr(), verts, leaf_size)
         self.pois = MultifrontalSolver(ops, (-Lc).tocsr(), verts, leaf_size, ground=0)
         self.tri = ops.to_device(tris.astype(np.int32))

@@ -105,19 +105,22 @@ class CudaOps:
             ws = self._ws[key] = torch.empty(int(nbytes) + 256, dtype=torch.uint8, device=self.device)
         return ws
 
-    def fork(self, after=None):
-        """Context manager: run the enclosed launches on the side stream, ordered after everything issued so far on the
-        current stream -- or, with `after` (a recorded CUDA event), only after that event; `join()` makes the current
-        stream wait for them."""
+    def fork(self, after=None, lane=0):
+        """Context manager: run the enclosed launches on a side stream (`lane` 0 or 1: two independent side streams), ordered
+        after everything issued so far on the current stream -- or, with `after` (a recorded CUDA event), only after that
+        event; `join()` makes the current stream wait for them."""
         if self._side is None:
+            self._side = {}
+        st = self._side.get(lane)
+        if st is None:
             import os
             prio = int(os.environ.get("ASB_SIDE_PRIORITY", "0"))     # -1: the side stream's CTAs are dispatched first
-            self._side = torch.cuda.Stream(self.device, priority=prio)
+            st = self._side[lane] = torch.cuda.Stream(self.device, priority=prio)
         if after is not None:
-            self._side.wait_event(after)
+            st.wait_event(after)
         else:
-            self._side.wait_stream(torch.cuda.current_stream(self.device))
-        return torch.cuda.stream(self._side)
+            st.wait_stream(torch.cuda.current_stream(self.device))
+        return torch.cuda.stream(st)
 
     def record_event(self):
         """A CUDA event recorded on the current stream (ordering handle for `fork(after=...)`)."""
@@ -127,7 +130,8 @@ class CudaOps:
 
     def join(self):
         if self._side is not None:
-            torch.cuda.current_stream(self.device).wait_stream(self._side)
+            for st in self._side.values():
+                torch.cuda.current_stream(self.device).wait_stream(st)
 
     def ws_for(self, rows: int, cols: int):
         return self.workspace(self.lib.asb_workspace_bytes(int(rows), int(cols)))
@@ -216,6 +220,23 @@ class CudaOps:
             return
         self._call("asb_argmax_first", self._p(v), n, index_offset, self._p(out_val), self._p(out_idx),
                    self._p(self.ws_for(1, n)))
+
+    def argmax_outside_ball(self, v, n, index_offset, pos, centre, radius, out_pair):
+        """out_pair (2,) f64 = {largest v[i] whose vertex i + index_offset lies outside the ball, bits of its global index}."""
+        if n == 0:                                        # empty shard: never wins
+            out_pair[0] = -float("inf")
+            out_pair[1:2].view(I64).fill_(torch.iinfo(torch.int64).max)
+            return
+        self._call("asb_argmax_outside_ball", self._p(v), n, index_offset, self._p(pos), self._p(centre), float(radius),
+                   self._p(out_pair), self._p(self.ws_for(1, n)))
+
+    def select_pair(self, all_pairs, world, fallback, out_idx):
+        self._call("asb_select_pair", self._p(all_pairs), int(world), self._p(fallback), self._p(out_idx))
+
+    def wait_event(self, ev):
+        """Make the current stream wait for a recorded event (finer than join(): the side stream may keep running)."""
+        if ev is not None:
+            torch.cuda.current_stream(self.device).wait_event(ev)
 
     def group_sum(self, v, n, group, out):
         if n == 0:

@@ -101,6 +101,18 @@ int asb_group_sum(const double* v, int64_t n, int64_t group, double* out, asb_st
  * ws: asb_workspace_bytes(1, n). */
 int asb_argmax_first(const double* v, int64_t n, int64_t index_offset, double* out_val, int64_t* out_idx,
                      void* ws, asb_stream_t stream);
+/* asb_argmax_first restricted to the entries whose vertex lies outside the ball of `radius` around vertex *centre (device,
+ * global index): pos = global (n_vertices x 3) rest positions, entry i belongs to vertex i + index_offset.  The result is ONE
+ * 16-byte record out_pair = {value, bit pattern of the global int64 index} (no entry outside the ball: {-inf, INT64_MAX}),
+ * the unit of the all-gather over row shards; asb_select_pair reduces `world` such records (largest value, ties to the lowest
+ * index; nothing anywhere: *fallback).  Used to predict the next deflation pick while the current one is still being
+ * deflated: a component with local support (posComponents.py:61-64, :96-99) changes the residual only within geodesic --
+ * hence Euclidean -- distance max_dist of its vertex, so the largest energy outside that ball is the next
+ * `indxLargestDeformation` (:84-90) unless the next pick falls inside it; the engine verifies the prediction against the
+ * real pick, so results never depend on it.  ws: asb_workspace_bytes(1, n). */
+int asb_argmax_outside_ball(const double* v, int64_t n, int64_t index_offset, const double* pos, const int64_t* centre,
+                            double radius, double* out_pair, void* ws, asb_stream_t stream);
+int asb_select_pair(const double* all, int64_t world, const int64_t* fallback, int64_t* out_idx, asb_stream_t stream);
 /* traj[d][f] = R[f][d][idx] - sum_{j<npend} Wp[f*ldw + j] * Cp[j][d][idx]   where idx = *idx_dev - row0;
  * no-op (traj untouched) when idx is outside [0, N): only the owning shard writes. (:83, R[:, idx, :]) */
 int asb_gather_traj(const double* R, int64_t F, int64_t N, int64_t ld, const int64_t* idx_dev, int64_t row0,

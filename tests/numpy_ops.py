@@ -27,7 +27,7 @@ class NumpyOps:
         self.launches = 0
 
     # plumbing -------------------------------------------------------------------------------------
-    def fork(self, after=None):
+    def fork(self, after=None, lane=0):
         import contextlib
         return contextlib.nullcontext()
 
@@ -106,6 +106,34 @@ class NumpyOps:
         e.numpy()[:] = 0
         e.numpy()[:N] = ((r[:, 0, :N] ** 2 + r[:, 1, :N] ** 2) + r[:, 2, :N] ** 2).sum(axis=0)
         return e
+
+    def argmax_outside_ball(self, v, n, index_offset, pos, centre, radius, out_pair):
+        out_pair[0] = -np.inf
+        out_pair[1:2].view(torch.int64)[0] = np.iinfo(np.int64).max
+        if n == 0:
+            return
+        P = pos.numpy()
+        d = P[index_offset:index_offset + n] - P[int(centre[0])]
+        ok = (d * d).sum(axis=1) > float(radius) ** 2
+        if not ok.any():
+            return
+        a = np.where(ok, v.numpy()[:n], -np.inf)
+        i = int(np.argmax(a))
+        out_pair[0] = float(a[i])
+        out_pair[1:2].view(torch.int64)[0] = i + index_offset
+
+    def select_pair(self, all_pairs, world, fallback, out_idx):
+        A = all_pairs.reshape(-1)[:2 * world].reshape(world, 2)
+        vals = A[:, 0].numpy()
+        ids = A[:, 1].contiguous().view(torch.int64).numpy()
+        best = vals.max()
+        if best == -np.inf:
+            out_idx[0] = int(fallback[0])
+            return
+        out_idx[0] = int(ids[vals == best].min())
+
+    def wait_event(self, ev):
+        pass
 
     def argmax_first(self, v, n, index_offset, out_val, out_idx):
         if n == 0:

@@ -92,6 +92,43 @@ def test_argmax_large(cuda_ops):
     assert int(idx.item()) == 17
 
 
+def test_argmax_outside_ball(cuda_ops):
+    """asb_argmax_outside_ball against the numpy statement: first maximum among the vertices outside the ball, shard offset,
+    and the no-candidate answer (-inf, INT64_MAX)."""
+    from numpy_ops import NumpyOps
+    rng = np.random.default_rng(5)
+    nglob, row0, n = 50_000, 12_345, 30_011
+    pos = torch.from_numpy(rng.random((nglob, 3)))
+    v = torch.from_numpy(rng.random(n))
+    centre_id = row0 + 777
+    far = np.nonzero(((pos.numpy()[row0:row0 + n] - pos.numpy()[centre_id]) ** 2).sum(axis=1) > 0.3 ** 2)[0]
+    v[777] = 5.0                                   # the global maximum sits at the centre: must be skipped
+    v[int(far[10])] = v[int(far[3])] = 3.0         # tie outside the ball: the lower index wins
+    centre = torch.tensor([centre_id], dtype=torch.int64)
+    ref = NumpyOps()
+    rp = torch.zeros(2, dtype=torch.float64)
+    ref.argmax_outside_ball(v, n, row0, pos, centre, 0.3, rp)
+    pair, idx = cuda_ops.zeros((2,)), cuda_ops.zeros((1,), torch.int64)
+    vd, pd, cd = dev(cuda_ops, v), dev(cuda_ops, pos), dev(cuda_ops, centre)
+    cuda_ops.argmax_outside_ball(vd, n, row0, pd, cd, 0.3, pair)
+    got = pair.cpu()
+    assert float(got[0]) == float(rp[0]) == 3.0
+    assert int(got[1:2].view(torch.int64)[0]) == int(rp[1:2].view(torch.int64)[0]) == row0 + int(far[3])
+    # reduction over "ranks": the record of this shard against a better one, a tie with a lower index, and nothing at all
+    allp = torch.zeros((3, 2), dtype=torch.float64)
+    allp[0] = got
+    allp[1, 0], allp[2, 0] = 3.0, 2.0
+    allp[1, 1:2].view(torch.int64)[0] = 11
+    allp[2, 1:2].view(torch.int64)[0] = 5
+    cuda_ops.select_pair(dev(cuda_ops, allp), 3, cd, idx)
+    assert int(idx.item()) == 11
+    cuda_ops.argmax_outside_ball(vd, n, row0, pd, cd, 10.0, pair)
+    got = pair.cpu()
+    assert float(got[0]) == -np.inf and int(got[1:2].view(torch.int64)[0]) == np.iinfo(np.int64).max
+    cuda_ops.select_pair(pair, 1, cd, idx)
+    assert int(idx.item()) == centre_id
+
+
 @pytest.mark.parametrize("local", [False, True])
 def test_traj_and_gemv_finish_update(cuda_ops, local):
     rng = np.random.default_rng(4)

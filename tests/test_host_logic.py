@@ -61,6 +61,13 @@ def test_position_pipeline_host_logic(name):
     assert pipeline_checks.check_positions(NumpyOps(), engine.Comm(enabled=False), name)
 
 
+def test_position_pipeline_with_pick_prediction(monkeypatch):
+    """engine.deflate with the next pick predicted one component ahead (default from 4 ranks on, forced here): the picks, the
+    components and everything downstream must be what they are without it."""
+    monkeypatch.setenv("ASB_DEFLATE_PREDICT", "1")
+    assert pipeline_checks.check_positions(NumpyOps(), engine.Comm(enabled=False), "pos_grid")
+
+
 def test_bunny_live_oracle_host_logic():
     """BASELINE config 1/2 mesh (bunny, N = 14 290) at an oracle-friendly frame count: engine over the numpy statement of the
     kernels == oracle/port.py run live (deflation with geodesic support + SPLOCS)."""
@@ -196,6 +203,8 @@ def test_two_rank_gloo_row_sharding(world):
     geodesic all-to-all) + POD + DEIM + geometric DEIM + reconstruction reproduce the single-process golden results."""
     port_no = str(29613 + world)
     env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=port_no, PYTHONPATH=ROOT + os.pathsep + os.path.join(ROOT, "tests"))
+    if world == 2:
+        env["ASB_DEFLATE_PREDICT"] = "1"            # 5 ranks predict by default (>= 4); cover the forced path on 2 as well
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr",
                         "127.0.0.1", "--master-port", port_no, os.path.join(ROOT, "tests", "gloo_worker.py")],
                        capture_output=True, text=True, env=env, timeout=900)

@@ -57,6 +57,10 @@ for step in "$@"; do
     geo1)   timeout 600 python tools/kbench.py --geo 1000 1000 2>&1 | grep geodesic_query | tee gpurun_out/geo1.log | cut -c1-600
             ASB_MF_SMALL=0 timeout 600 python tools/kbench.py --geo 1000 1000 2>&1 | grep geodesic_query | sed 's/^/ASB_MF_SMALL=0 /' | tee -a gpurun_out/geo1.log | cut -c1-600 ;;
     stream) timeout 600 python tools/kbench.py --only stream 2>&1 | tee gpurun_out/kbench_stream.log | tail -12 ;;
+    traceN) N=${ASB_NGPU:-2}; for pr in 0 -1; do echo "== side priority $pr"; ASB_SIDE_PRIORITY=$pr ASB_TRACE_DEFLATE=1 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus $N --splocs-iters 0 --steps 2 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/trace_${N}gpu.log 2>&1; echo "trace$N rc=$?"; grep -o "\[deflate trace.*\|\"phase_ms_per_step\": {[^}]*}" gpurun_out/trace_${N}gpu.log | tail -3; done ;;
+    deflN)  N=${ASB_NGPU:-8}; for cfg in "ASB_DEFLATE_PREDICT=1 ASB_MAIN_PRIORITY=0" "ASB_DEFLATE_PREDICT=1 ASB_MAIN_PRIORITY=-1" "ASB_DEFLATE_PREDICT=0 ASB_MAIN_PRIORITY=0"; do
+              env $cfg timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29514 bench.py --gpus $N --splocs-iters 0 --steps 3 --warmup 2 --no-e2e --no-cpu-baseline > gpurun_out/defl_${N}gpu.log 2>&1
+              echo "$cfg rc=$? $(grep -o '"phase_ms_per_step": {[^}]*}' gpurun_out/defl_${N}gpu.log | tail -1) $(grep -o "'predicted_picks': [0-9]*" gpurun_out/defl_${N}gpu.log | tail -1)"; done ;;
     *) echo "unknown step $step" ;;
   esac
 done
