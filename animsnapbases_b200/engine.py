@@ -336,8 +336,8 @@ class _Trace:
     """ASB_TRACE_DEFLATE=1: CUDA events at the stations of a deflation step (on whichever stream is current when they are
     marked); `report` prints the mean time between consecutive stations.  Diagnostic only."""
 
-    def __init__(self, ops):
-        self.ops, self.rows, self.cur = ops, [], None
+    def __init__(self, ops, pairs=None, what="deflate"):
+        self.ops, self.rows, self.cur, self.pairs, self.what = ops, [], None, pairs, what
 
     def mark(self, name):
         import torch
@@ -350,14 +350,15 @@ class _Trace:
 
     def report(self):
         self.ops.synchronize()
-        pairs = [("start", "picked"), ("picked", "gemv"), ("geo0", "geo1"), ("picked", "geo0"), ("gemv", "joined"),
-                 ("joined", "finished"), ("finished", "end"), ("start", "end")]
+        pairs = self.pairs or [("start", "picked"), ("picked", "gemv"), ("geo0", "geo1"), ("picked", "geo0"), ("gemv", "joined"),
+                               ("joined", "finished"), ("finished", "end"), ("start", "end")]
         out = {}
         for a, b in pairs:
             v = [r[a].elapsed_time(r[b]) for r in self.rows if a in r and b in r]
             if v:
                 out[a + "->" + b] = round(float(np.mean(v)), 4)
-        print("[deflate trace, ms per component, %d components] %s" % (len(self.rows), out), flush=True)
+        print("[%s trace, ms per %s, %d of them] %s" % (self.what, "component" if self.what == "deflate" else "iteration",
+                                                        len(self.rows), out), flush=True)
 
 
 class _Picker:
@@ -599,12 +600,21 @@ def splocs(ops, comm, X, shard, C, W, K, geodesic, num_iters, num_admm, lam, rho
     centres(False)
     post_ids()
     centre_hist = []
+    trace = _Trace(ops, [("start", "small"), ("small", "b0"), ("b0", "joined"), ("geo0", "geo1"), ("start", "geo0"),
+                         ("joined", "admm"), ("admm", "grams"), ("grams", "end"), ("start", "end")], "splocs") \
+        if _os.environ.get("ASB_TRACE_SPLOCS") and getattr(ops, "name", "") == "cuda" else None
     for it in range(num_iters):
+        if trace is not None:
+            trace.mark("start")
         ops.weights_sweep(P, Q, W, F, K)
         ops.gram_small(W, F, K, rho, H)                                 # H = W^T W + rho I
         ops.spd_inverse(H, K, Hinv, info)
         ops.small_gemm(0, 1, K, F, K, 1.0, Hinv, W, Aw)                 # Aw = H^-1 W^T   (K x F)
+        if trace is not None:
+            trace.mark("small")
         ops.gemm_nn(Aw, K, F, Xm, M, 1.0, B0.view(K, M))                # B0 = H^-1 (W^T X)
+        if trace is not None:
+            trace.mark("b0")
         if ids_ready is not None:
             ids_ready.synchronize()
         ids = ids_host.tolist()                                         # K ints (memoisation key)
@@ -612,15 +622,25 @@ def splocs(ops, comm, X, shard, C, W, K, geodesic, num_iters, num_admm, lam, rho
         # support maps of the new centres on the side stream, ordered after `centres()` of the previous iteration only (not
         # after the B0 GEMM just queued): they run beside it; Lambda is read by the ADMM launch below, after the join
         with ops.fork(after=ids_ready):
+            if trace is not None:
+                trace.mark("geo0")
             geodesic.support(idx, 1, lam, dmin, dmax, row0, N, Lambda, ids_host=ids, comm=comm)
+            if trace is not None:
+                trace.mark("geo1")
         ops.join()
+        if trace is not None:
+            trace.mark("joined")
         if K8 == Kp:
             ops.axpby(Hr[:K].view(1, -1), rho, Hinv.view(1, -1), None, 0.0, None, K * Kp)
         else:                                                           # K % 8 != 0: scale, then re-stride into the padding
             ops.axpby(Hr_c.view(1, -1), rho, Hinv.view(1, -1), None, 0.0, None, K * Kp)
             Hr[:K, :K].copy_(Hr_c[:, :K])
         ops.admm_solve(Hr, B0, C, U, Lambda, K, N, 1.0 / rho, num_admm)
+        if trace is not None:
+            trace.mark("admm")
         P, Q = grams()
+        if trace is not None:
+            trace.mark("grams")
         centres(True)
         post_ids()
         # energy = |X - W C|^2 + sum Lambda |c|  via  |X|^2 - 2 <W, P> + <W Q, W>
@@ -632,7 +652,11 @@ def splocs(ops, comm, X, shard, C, W, K, geodesic, num_iters, num_admm, lam, rho
         scal3[2:3] = sp.sum()
         scal_host[it].copy_(scal3, non_blocking=True)
         info_host[it:it + 1].copy_(info, non_blocking=True)
+        if trace is not None:
+            trace.mark("end")
     ops.synchronize()
+    if trace is not None:
+        trace.report()
     hist = []
     for it in range(num_iters):
         if int(info_host[it]) != 0:

@@ -112,7 +112,8 @@ class HeatGeodesics:
                       "operator_bytes": self.heat.stats["operator_bytes"] + self.pois.stats["operator_bytes"]}
         self._cache = {}
         self._graphs = {}            # captured single-source queries (support_single); None = capture failed, stay eager
-        self.cache_rows = 4          # memoised maps kept per request size: at most cache_rows * B rows per key (LRU)
+        import os
+        self.cache_rows = int(os.environ.get("ASB_GEO_CACHE_ROWS", "4"))   # memoised maps kept: at most cache_rows * B rows per key (LRU)
 
     _instances = {}              # (device, digest of mesh, leaf size) -> HeatGeodesics: the factorisation depends on the mesh only
 

@@ -32,7 +32,7 @@ for step in "$@"; do
             timeout 600 python tools/admm_ab.py 14290 200 1 2 --variants 0,8 >> gpurun_out/admm_ab.log 2>&1; cat gpurun_out/admm_ab.log ;;
     ncu_list) A="--grid 300 300 --frames 500 --comps 48 --splocs-iters 3 --steps 1 --warmup 1 --no-e2e --no-cpu-baseline"
             if timeout 600 python bench.py $A > gpurun_out/ncu_list_plain.json 2> gpurun_out/ncu_list_plain.err; then
-              timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:asb:: -c 60000 --csv --log-file gpurun_out/ncu_launches.csv python bench.py $A > gpurun_out/ncu_list.log 2>&1; echo "ncu_list rc=$?"; tail -2 gpurun_out/ncu_list.log; wc -l gpurun_out/ncu_launches.csv
+              timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name-base demangled -k regex:asb:: -c 60000 --csv --log-file gpurun_out/ncu_launches.csv python bench.py $A > gpurun_out/ncu_list.log 2>&1; echo "ncu_list rc=$?"; tail -2 gpurun_out/ncu_list.log; wc -l gpurun_out/ncu_launches.csv
             else echo "plain run failed"; tail -5 gpurun_out/ncu_list_plain.err; fi ;;
     ncu_admm) if timeout 300 python tools/kbench.py --only admm > gpurun_out/kbench_admm_plain.log 2>&1; then
               grep admm_solve gpurun_out/kbench_admm_plain.log
@@ -61,6 +61,8 @@ for step in "$@"; do
     deflN)  N=${ASB_NGPU:-8}; for cfg in "ASB_DEFLATE_PREDICT=1 ASB_MAIN_PRIORITY=0" "ASB_DEFLATE_PREDICT=1 ASB_MAIN_PRIORITY=-1" "ASB_DEFLATE_PREDICT=0 ASB_MAIN_PRIORITY=0"; do
               env $cfg timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29514 bench.py --gpus $N --splocs-iters 0 --steps 3 --warmup 2 --no-e2e --no-cpu-baseline > gpurun_out/defl_${N}gpu.log 2>&1
               echo "$cfg rc=$? $(grep -o '"phase_ms_per_step": {[^}]*}' gpurun_out/defl_${N}gpu.log | tail -1) $(grep -o "'predicted_picks': [0-9]*" gpurun_out/defl_${N}gpu.log | tail -1)"; done ;;
+    strace) for pr in 0 -1; do echo "== side priority $pr"; ASB_SIDE_PRIORITY=$pr ASB_TRACE_SPLOCS=1 timeout 600 python bench.py --splocs-iters 12 --steps 1 --warmup 1 --no-e2e --no-cpu-baseline 2>&1 | grep -o "\[splocs trace.*\|\"phase_ms_per_step\": {[^}]*}" | tail -2; done ;;
+    cache)  for cr in 12; do ASB_GEO_CACHE_ROWS=$cr timeout 900 python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/bench_cache$cr.json 2> gpurun_out/bench_cache$cr.err; echo "cache_rows=$cr rc=$? $(grep -o '"value": [0-9.]*' gpurun_out/bench_cache$cr.json | head -1) $(grep -o '"phase_ms_per_step": {[^}]*}' gpurun_out/bench_cache$cr.json) $(grep -o '"geodesic": {[^}]*}' gpurun_out/bench_cache$cr.json)"; done ;;
     *) echo "unknown step $step" ;;
   esac
 done
