@@ -63,6 +63,10 @@ for step in "$@"; do
               echo "$cfg rc=$? $(grep -o '"phase_ms_per_step": {[^}]*}' gpurun_out/defl_${N}gpu.log | tail -1) $(grep -o "'predicted_picks': [0-9]*" gpurun_out/defl_${N}gpu.log | tail -1)"; done ;;
     strace) for pr in 0 -1; do echo "== side priority $pr"; ASB_SIDE_PRIORITY=$pr ASB_TRACE_SPLOCS=1 timeout 600 python bench.py --splocs-iters 12 --steps 1 --warmup 1 --no-e2e --no-cpu-baseline 2>&1 | grep -o "\[splocs trace.*\|\"phase_ms_per_step\": {[^}]*}" | tail -2; done ;;
     cache)  for cr in 12; do ASB_GEO_CACHE_ROWS=$cr timeout 900 python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu-baseline > gpurun_out/bench_cache$cr.json 2> gpurun_out/bench_cache$cr.err; echo "cache_rows=$cr rc=$? $(grep -o '"value": [0-9.]*' gpurun_out/bench_cache$cr.json | head -1) $(grep -o '"phase_ms_per_step": {[^}]*}' gpurun_out/bench_cache$cr.json) $(grep -o '"geodesic": {[^}]*}' gpurun_out/bench_cache$cr.json)"; done ;;
+    final)  timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/tests_final.log 2>&1; echo "tests rc=$?"; tail -3 gpurun_out/tests_final.log
+            timeout 600 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/smoke.log
+            ( time timeout 1500 python bench.py ) > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; echo "bench default rc=$?"; tail -c 1500 gpurun_out/bench_default.json; tail -6 gpurun_out/bench_default.err
+            ( time timeout 900 python bench.py --impl reference --steps 1 --warmup 0 ) > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "bench reference rc=$?"; tail -c 1200 gpurun_out/bench_reference.json; tail -4 gpurun_out/bench_reference.err ;;
     *) echo "unknown step $step" ;;
   esac
 done
