@@ -34,6 +34,9 @@ PRESETS = {
     # config 4: armadillo, F = 200 (config/examples/armadillo_gFall_tetstrainSubspace.json:36-38), as config 2
     "armadillo_splocs": dict(kind="pos", mesh="armadillo", frames=200, comps=200, bumps=12, sigma=0.15, seed=4,
                              splocs=(20, 10, 2.0, 10.0)),
+    # config 4 at the longer of the two frame counts SURVEY 8(d) names for "full range of motion" (F = 200 and F = 1 000)
+    "armadillo_splocs_f1000": dict(kind="pos", mesh="armadillo", frames=1000, comps=200, bumps=12, sigma=0.15, seed=4,
+                                   splocs=(20, 10, 2.0, 10.0)),
     # config 5's CPU-runnable sample: N = 1e5, F = 500, K = 200, 2 x 10 SPLOCS
     "synthetic_sample": dict(kind="pos", mesh="grid", grid=(400, 250), frames=500, comps=200, bumps=32, sigma=0.08, seed=0,
                              splocs=(2, 10, 2.0, 10.0)),

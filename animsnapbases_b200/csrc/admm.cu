@@ -405,9 +405,6 @@ __device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __
     const uint32_t slab_bytes = (uint32_t)astage * 8u;
     const int grp = G > 1 ? (int)(threadIdx.x >> 7) : 0;
     const int gt = (int)threadIdx.x - 128 * grp;          // thread index inside the group
-    // the thread that issues the bulk copies: thread 0 of the group, or (experiment bit 8, G == 1) lane 0 of the warp that
-    // owns the most m-tiles (mt0 == 0)
-    const bool prod = (G == 1 && (skew & 8)) ? (mt0 == 0 && live && (threadIdx.x & 31) == 0) : gt == 0;
     const size_t group_doubles = (size_t)rows8 * DLD + (size_t)STAGES * astage;
     double* Ds = smem_all + grp * group_doubles;          // [rows8][DLD]  Z - U (rows >= K zero)
     double* As = Ds + (size_t)rows8 * DLD;                // STAGES x [rows8][ALD]
@@ -452,7 +449,7 @@ __device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __
         if (++pst == STAGES) { pst = 0; pwrap ^= 1u; }
         if (++pslab == nslab) pslab = 0;
     };
-    if (prod)
+    if (gt == 0)
         for (int i = 0; i < STAGES && issued < total_all; ++i) issue();
     // consumer state: next slab to use
     int cst = 0;
@@ -510,7 +507,7 @@ __device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __
                 if (need >= 0 && need < partner_iters) mbar_wait(mid + (grp ^ 1), (uint32_t)(need & 1));
             }
             for (int s = 0; s < nslab; ++s) {
-                if (prod && !first && issued < total_all) issue();   // refill the stage released one step ago
+                if (gt == 0 && !first && issued < total_all) issue();   // refill the stage released one step ago
                 first = false;
                 mbar_wait(full + cst, cwrap);
                 const double* as = afrag + cst * astage;
@@ -528,7 +525,6 @@ __device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __
                     }
                 }
                 __syncwarp();
-                if (G == 1 && (skew & 64)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                 if (lane == 0) {
                     mbar_arrive(empty + cst);
                     if (G == 2 && s == sig_slab) mbar_arrive(mid + grp);
@@ -597,7 +593,6 @@ __device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __
             }
             if (!last) group_sync();  // the new D is complete before any warp multiplies with it
         }
-        if (G == 1 && (skew & 32)) group_sync();
     }
 }
 
@@ -610,9 +605,7 @@ admm_tma_kernel(const double* __restrict__ Hpk, const double* __restrict__ B0, d
     int mt0, mtn;
     int wm = (threadIdx.x >> 5) & 3;
     // co-resident groups rotate the row-warp roles: the 7-tile warps (K = 200: 7,6,6,6) sit on different SM sub-partitions
-    int slot = Cfg::G > 1 ? (int)(threadIdx.x >> 7) : (int)((blockIdx.x / max(1u, gridDim.x / 2)) & 1);
-    if (Cfg::G == 1 && (skew & 128)) slot = 0;
-    if (Cfg::G == 1 && (skew & 256)) slot ^= 1;
+    const int slot = Cfg::G > 1 ? (int)(threadIdx.x >> 7) : (int)((blockIdx.x / max(1u, gridDim.x / 2)) & 1);
     wm = (wm + (Cfg::G == 3 ? slot : 2 * slot)) % Cfg::WM;
     mtile_range(((K + 7) & ~7) >> 3, Cfg::WM, wm, mt0, mtn);
     const bool live = mtn > 0;

@@ -1,11 +1,11 @@
 #!/usr/bin/env python
 """Bitwise A/B of two ADMM kernel layouts on the same inputs (needs a GPU).
 
-    python tools/admm_ab.py N K ITERS [REPS] [--variants 0,8,32,64,128,256]
+    python tools/admm_ab.py N K ITERS [REPS] [--layout 5] [--variants 0]
 
-Runs asb_admm_solve_ws with layout 4 (cp.async pair, the product default) and layout 5 (bulk-copy pair) -- the latter once
-per experiment variant (bits of the `skew` argument, see admm_tma_body) -- and reports, per variant and repetition, how
-many entries of Z differ bit for bit, which vertex tiles they fall into (tile -> CTA slot, round of that CTA) and which
+Runs asb_admm_solve_ws with layout 4 (cp.async pair, r01's kernel) and layout 5 (bulk-copy pair, the product default; or
+--layout 6 / 7 with --variants = the duet's ASB_ADMM_SKEW values) and reports, per variant and repetition, how many entries
+of Z differ bit for bit, which vertex tiles they fall into (tile -> CTA slot, round of that CTA) and which
 rows (-> which row-warp's m-tile).  The two kernels accumulate in the same order, so a correct layout 5 differs nowhere.
 """
 from __future__ import annotations
@@ -28,7 +28,7 @@ def main():
     ap.add_argument("K", type=int)
     ap.add_argument("iters", type=int)
     ap.add_argument("reps", type=int, nargs="?", default=2)
-    ap.add_argument("--variants", default="0,8,32,64,128,256")
+    ap.add_argument("--variants", default="0")
     ap.add_argument("--layout", type=int, default=5)
     a = ap.parse_args()
     ops = ops_mod.CudaOps()

@@ -29,7 +29,7 @@ for step in "$@"; do
             done ;;
     noalloc) timeout 600 python -m pytest tests/test_zz_no_alloc.py -x -q -m gpu > gpurun_out/noalloc.log 2>&1; echo "noalloc (fresh process) rc=$?"; tail -4 gpurun_out/noalloc.log ;;
     ab)     timeout 900 python tools/admm_ab.py 14290 200 10 2 > gpurun_out/admm_ab.log 2>&1; echo "ab rc=$?"
-            timeout 600 python tools/admm_ab.py 14290 200 1 2 --variants 0,8 >> gpurun_out/admm_ab.log 2>&1; cat gpurun_out/admm_ab.log ;;
+            timeout 600 python tools/admm_ab.py 14290 200 1 2 >> gpurun_out/admm_ab.log 2>&1; cat gpurun_out/admm_ab.log ;;
     ncu_list) A="--grid 300 300 --frames 500 --comps 48 --splocs-iters 3 --steps 1 --warmup 1 --no-e2e --no-cpu-baseline"
             if timeout 600 python bench.py $A > gpurun_out/ncu_list_plain.json 2> gpurun_out/ncu_list_plain.err; then
               timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none --kernel-name-base demangled -k regex:asb:: -c 60000 --csv --log-file gpurun_out/ncu_launches.csv python bench.py $A > gpurun_out/ncu_list.log 2>&1; echo "ncu_list rc=$?"; tail -2 gpurun_out/ncu_list.log; wc -l gpurun_out/ncu_launches.csv
