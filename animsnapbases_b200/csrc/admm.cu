@@ -395,7 +395,7 @@ template <class Cfg, int MT, int MTN>
 __device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __restrict__ Hpk, const double* __restrict__ B0,
                                               double* __restrict__ Z, double* __restrict__ U, const double* __restrict__ Lambda,
                                               int K, int64_t N, int64_t ld, double inv_rho, int iters, int64_t ntiles, int mt0,
-                                              bool live, int skew) {
+                                              bool live, int skew, int zero) {
     constexpr int G = Cfg::G, DLD = Cfg::DLD, ALD = Cfg::ALD, STAGES = Cfg::STAGES, BK = Cfg::BK;
     constexpr bool UREG = Cfg::UREG;
     constexpr int UR = UREG ? MTN : 1;
@@ -512,6 +512,14 @@ __device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __
                 mbar_wait(full + cst, cwrap);
                 const double* as = afrag + cst * astage;
                 const double* ds = bfrag + s * BK * DLD;
+                // `tok` collects a word of every A fragment this lane loads from the stage; the release below is issued with
+                // an address that depends on it ((tok & zero) == 0 at run time, `zero` being a kernel argument the compiler cannot
+                // fold).  Without that dependency ptxas schedules SYNCS.ARRIVE right behind the ISSUE of the last LDS (the DMMAs
+                // that consume the fragments sink below it), the arrival can overtake the shared-memory read, the issuing thread
+                // refills the stage through the async proxy and the last m-tile of the slowest warp multiplies with the NEXT
+                // lap's slab (seen on a B200 at N = 14 290, K = 200: wrong entries only in m-tile 6 of the 7-tile warp, only in
+                // CTAs whose issuing thread sits in a 6-tile warp, run-to-run different -- tools/admm_ab.py).
+                unsigned tok = 0;
 #pragma unroll
                 for (int kk = 0; kk < BK / 4; ++kk) {
                     double b[3];
@@ -520,13 +528,14 @@ __device__ __forceinline__ void admm_tma_body(double* smem_all, const double* __
 #pragma unroll
                     for (int i = 0; i < MTN; ++i) {
                         const double a = as[i * 8 * ALD + kk * 4];
+                        tok |= (unsigned)__double2hiint(a);
 #pragma unroll
                         for (int d = 0; d < 3; ++d) dmma(acc[i][d][0], acc[i][d][1], a, b[d]);
                     }
                 }
                 __syncwarp();
                 if (lane == 0) {
-                    mbar_arrive(empty + cst);
+                    mbar_arrive(empty + cst + (tok & (unsigned)zero));   // every LDS of this stage has returned its data
                     if (G == 2 && s == sig_slab) mbar_arrive(mid + grp);
                 }
                 if (++cst == STAGES) { cst = 0; cwrap ^= 1u; }
@@ -600,7 +609,7 @@ template <class Cfg, int MT>
 __global__ void __launch_bounds__(Cfg::THREADS, Cfg::CTAS)
 admm_tma_kernel(const double* __restrict__ Hpk, const double* __restrict__ B0, double* __restrict__ Z, double* __restrict__ U,
                 const double* __restrict__ Lambda, int K, int64_t N, int64_t ld, double inv_rho, int iters, int64_t ntiles,
-                int skew) {
+                int skew, int zero) {
     extern __shared__ __align__(128) double smem[];
     int mt0, mtn;
     int wm = (threadIdx.x >> 5) & 3;
@@ -610,8 +619,9 @@ admm_tma_kernel(const double* __restrict__ Hpk, const double* __restrict__ B0, d
     mtile_range(((K + 7) & ~7) >> 3, Cfg::WM, wm, mt0, mtn);
     const bool live = mtn > 0;
     if (!live) mt0 = 0;
-    if (mtn == MT) admm_tma_body<Cfg, MT, MT>(smem, Hpk, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live, skew);
-    else admm_tma_body<Cfg, MT, (MT > 1 ? MT - 1 : 1)>(smem, Hpk, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live, skew);
+    if (mtn == MT) admm_tma_body<Cfg, MT, MT>(smem, Hpk, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live, skew, zero);
+    else admm_tma_body<Cfg, MT, (MT > 1 ? MT - 1 : 1)>(smem, Hpk, B0, Z, U, Lambda, K, N, ld, inv_rho, iters, ntiles, mt0, live, skew,
+                                                        zero);
 }
 
 template <class Cfg>
@@ -698,7 +708,9 @@ static int launch_admm_tma_mt(const double* Hpk, const double* B0, double* Z, do
     const int64_t ntiles = cdiv(ld, Cfg::NV);
     const int64_t slots = Cfg::G > 1 ? sm_count() : (solo ? sm_count() : (int64_t)Cfg::CTAS * sm_count());
     const unsigned grid = (unsigned)std::min<int64_t>(cdiv(ntiles, Cfg::G), slots);
-    admm_tma_kernel<Cfg, MT><<<grid, Cfg::THREADS, smem, st>>>(Hpk, B0, Z, U, Lambda, (int)K, N, ld, inv_rho, iters, ntiles, skew);
+    static volatile int runtime_zero = 0;   // see admm_tma_body: a zero the compiler cannot see through
+    admm_tma_kernel<Cfg, MT><<<grid, Cfg::THREADS, smem, st>>>(Hpk, B0, Z, U, Lambda, (int)K, N, ld, inv_rho, iters, ntiles, skew,
+                                                              runtime_zero);
     ASB_LAUNCH_CHECK();
     return ASB_OK;
 }

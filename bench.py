@@ -10,7 +10,7 @@ animation, ingest, standardisation, build, D2H of components and weights.
     python bench.py                                      # 1 GPU, headline workload
     torchrun --nproc-per-node N bench.py --gpus N        # row-sharded over N GPUs (strong scaling, same total workload)
     python bench.py --config bunny_splocs                # BASELINE configs 1-4 and the N = 1e5 sample: bunny_pca, bunny_splocs,
-                                                         # bar_deim, armadillo_splocs, synthetic_sample
+                                                         # bar_deim, armadillo_splocs[_f1000], synthetic_sample
     python bench.py --unit pod_deim                      # unit U2: Gram POD + eigensolve + back-projection + DEIM, 3e6 rows x 2000
     python bench.py --impl reference [--config ...]      # the reference's own CPU code on the same config (oracle/ref_runner.py)
 """
@@ -33,7 +33,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "pca_splocs_basis_build_time"
 UNIT = "s"
-PRESET_NAMES = ["synthetic", "bunny_pca", "bunny_splocs", "bar_deim", "armadillo_splocs", "synthetic_sample"]
+PRESET_NAMES = ["synthetic", "bunny_pca", "bunny_splocs", "bar_deim", "armadillo_splocs", "armadillo_splocs_f1000", "synthetic_sample"]
 
 
 def parse():

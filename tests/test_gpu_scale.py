@@ -20,7 +20,7 @@ def _save(name, rep):
             json.dump(rep, fh, indent=1, default=float)
 
 
-@pytest.mark.parametrize("name", ["bunny_splocs", "armadillo_splocs", "synthetic_sample"])
+@pytest.mark.parametrize("name", ["bunny_splocs", "armadillo_splocs", "armadillo_splocs_f1000", "synthetic_sample"])
 def test_position_configs_at_scale(cuda_ops, name):
     if not os.path.exists(os.path.join(os.path.dirname(__file__), "golden", f"scale_{name}.npz")):
         pytest.skip(f"fixture scale_{name}.npz not generated")

@@ -474,7 +474,7 @@ def test_tet_grid_generator():
 def test_scale_inputs_are_reproducible():
     """configs.build_inputs regenerates, bit for bit, the inputs the at-scale fixtures were computed on (IEEE-only arithmetic)."""
     from animsnapbases_b200 import configs
-    for name in ("bunny_splocs", "bar_deim", "armadillo_splocs"):
+    for name in ("bunny_splocs", "bar_deim", "armadillo_splocs", "armadillo_splocs_f1000"):
         f = os.path.join(GOLDEN, f"scale_{name}.npz")
         if os.path.exists(f):
             assert configs.build_inputs(name)["digest"] == str(np.load(f)["digest"]), name

@@ -67,6 +67,8 @@ for step in "$@"; do
             timeout 600 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/smoke.log
             ( time timeout 1500 python bench.py ) > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; echo "bench default rc=$?"; tail -c 1500 gpurun_out/bench_default.json; tail -6 gpurun_out/bench_default.err
             ( time timeout 900 python bench.py --impl reference --steps 1 --warmup 0 ) > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "bench reference rc=$?"; tail -c 1200 gpurun_out/bench_reference.json; tail -4 gpurun_out/bench_reference.err ;;
+    f1000)  timeout 900 python -m pytest tests/test_gpu_scale.py -q -m gpu -k f1000 -rs > gpurun_out/scale_f1000.log 2>&1; echo "scale f1000 rc=$?"; tail -3 gpurun_out/scale_f1000.log
+            c=armadillo_splocs_f1000; timeout 600 python bench.py --config $c --steps 3 --warmup 3 > gpurun_out/bench_$c.json 2> gpurun_out/bench_$c.err; echo "$c rc=$?"; tail -c 1500 gpurun_out/bench_$c.json; tail -3 gpurun_out/bench_$c.err ;;
     *) echo "unknown step $step" ;;
   esac
 done
