@@ -21,7 +21,7 @@
 //                U through L2                                                        105.2 ms
 //   8/81 Duo     two CTAs per SM of 8 row-warps x 1 vertex group (U through L2 / in registers)  115.7 / 106.8 ms
 //   5    TmaPair same tile as Pair; Hr streamed from a slab-major copy with ONE cp.async.bulk (TMA, SASS UBLKCP) per slab,
-//                handed over through mbarriers (no CTA barrier per slab), ring running on across tiles    96.6 ms  24.9 TFLOP/s
+//                handed over through mbarriers (no CTA barrier per slab), ring running on across tiles    97.0 ms  24.7 TFLOP/s
 //                <- default (r02); bit-identical to layout 4 on the same inputs (tools/admm_ab.py, profiles/r02_admm_layouts.md)
 //   6    TmaDuet one CTA per SM, two groups with an optional phase offset (ASB_ADMM_SKEW 0 / 1 / 2)       98.7 / 98.8 / 132.5 ms
 //   7    TmaTrio one CTA per SM, three groups (12 warps), U through L2, 4-column slabs                     111.1 ms

@@ -172,8 +172,9 @@ int asb_gemm_nn(const double* A, int64_t lda, int64_t r, int64_t q, const double
  * memory for all iterations: Z and U cross HBM once per call.  B0, Z, U: K x 3*ld planar; Lambda: K x ld.  K <= 256. */
 int asb_admm_solve(const double* Hr, int64_t ldh, const double* B0, double* Z, double* U, const double* Lambda,
                    int64_t K, int64_t N, int64_t ld, double inv_rho, int64_t iters, asb_stream_t stream);
-/* Same with a caller-owned workspace of asb_admm_workspace_bytes(K) bytes (16-byte aligned): the bulk-copy layouts (ASB_ADMM_LAYOUT=5/6/7;
- * the default layout 4 stages Hr with per-thread cp.async and ignores the workspace) stream Hr from a slab-major copy Hpk[slab][row][12] (one contiguous 19.2 KB block per 8-column slab at K = 200) with one
+/* Same with a caller-owned workspace of asb_admm_workspace_bytes(K) bytes (16-byte aligned): the default kernel
+ * (ASB_ADMM_LAYOUT=5; 6 / 7 are its one-CTA-per-SM variants, 4 is r01's cp.async kernel, which ignores the workspace) streams
+ * Hr from a slab-major copy Hpk[slab][row][12] (one contiguous 19.2 KB block per 8-column slab at K = 200) with one
  * `cp.async.bulk` (TMA) per slab completed on mbarriers.  asb_admm_solve keeps that copy in a buffer of the library
  * (allocated on first use), so its calls must not overlap on different streams.  K > 256 is refused with ASB_ERR_ARG in
  * both forms (accumulators of ceil(K / 32) m-tiles per warp must fit the register file). */
