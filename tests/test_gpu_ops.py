@@ -287,6 +287,45 @@ def test_admm_solve(cuda_ops, K, N, iters):
     assert float(Zg[:, :, N:].abs().max().item()) == 0.0 and float(Ug[:, :, N:].abs().max().item()) == 0.0
 
 
+def test_admm_bulk_copy_kernel_is_bit_identical_to_cp_async_kernel(cuda_ops):
+    """The default ADMM kernel (bulk copies + mbarriers, layout 5) and r01's cp.async kernel (layout 4) accumulate every entry
+    in the same order, so they must agree bit for bit -- at a size where a CTA runs several vertex tiles (N = 14 290: 1 787
+    tiles on 296 CTAs) and the co-resident CTAs of an SM drift apart.  Guards the hand-over of the slab ring: a stage released
+    before its last fragment load has returned shows up here as whole vertex tiles that differ from run to run
+    (profiles/r02_admm_layouts.md)."""
+    K, N, iters = 200, 14290, 10
+    ld = (N + 31) // 32 * 32
+    g = torch.Generator(device="cpu").manual_seed(1)
+    Wm = torch.randn((300, K), generator=g, dtype=torch.float64)
+    H = 10.0 * torch.linalg.inv(Wm.T @ Wm / 300 + 10.0 * torch.eye(K, dtype=torch.float64))
+    k16 = (K + 15) // 16 * 16
+    Hr = torch.zeros((k16, k16), dtype=torch.float64)
+    Hr[:K, :K] = H
+
+    def field(scale):
+        t = torch.zeros((K, 3, ld), dtype=torch.float64)
+        t[:, :, :N] = scale * torch.randn((K, 3, N), generator=g, dtype=torch.float64)
+        return dev(cuda_ops, t)
+    B0, Z0, U0 = field(1.0), field(1.0), field(0.1)
+    Lam = torch.zeros((K, ld), dtype=torch.float64)
+    Lam[:, :N] = 0.5 * torch.rand((K, N), generator=g, dtype=torch.float64)
+    Hr, Lam = dev(cuda_ops, Hr), dev(cuda_ops, Lam)
+
+    def run(layout):
+        cuda_ops.lib.asb_admm_select_layout(layout, 0)
+        Z, U = Z0.clone(), U0.clone()
+        cuda_ops.admm_solve(Hr, B0, Z, U, Lam, K, N, 0.1, iters)
+        torch.cuda.synchronize()
+        return Z, U
+    try:
+        Z4, U4 = run(4)
+        for rep in range(4):
+            Z5, U5 = run(5)
+            assert int((Z5 != Z4).sum()) == 0 and int((U5 != U4).sum()) == 0, f"repetition {rep}"
+    finally:
+        cuda_ops.lib.asb_admm_select_layout(-1, -1)
+
+
 # ------------------------------------------------------------------------------------------------ small dense
 @pytest.mark.parametrize("F,K", [(24, 10), (200, 64), (333, 201)])
 def test_small_dense(cuda_ops, F, K):
