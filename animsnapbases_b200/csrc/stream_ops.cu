@@ -1,5 +1,6 @@
 // HBM-bound streaming kernels: boundary layout conversion, mean-centering/standardisation (k2),
 // greedy-deflation passes (k3, k8, k9).  All are coalesced planar passes; reductions are fixed-order.
+#include <cstdlib>
 #include <mutex>
 #include "common.cuh"
 
@@ -355,7 +356,7 @@ __global__ void deflate_meas_kernel(const double* __restrict__ partial, int64_t 
 }
 
 // R[f][.][n] -= sum_j Wb[f][j] * Cb[j][.][n]; exact energies of the new R. One vertex per thread.
-template <int NB>
+template <int NB, int FU = 4>
 __global__ void __launch_bounds__(128) rank_update_kernel(double* __restrict__ R, int64_t F, int64_t N, int64_t ld,
                                                          const double* __restrict__ Wb, int64_t ldw,
                                                          const double* __restrict__ Cb, int nb,
@@ -382,9 +383,8 @@ __global__ void __launch_bounds__(128) rank_update_kernel(double* __restrict__ R
         __syncthreads();
         if (act) {
             // FU frames per trip with all 3 * FU loads issued before the arithmetic: one frame per trip left 3 loads in flight
-            // per thread (r01 ncu: 31 % occupancy, 4.5 TB/s); the per-element operation order and the order of the energy
+            // per thread (r01 ncu: 31 % occupancy, 4.5 TB/s; FU = 4: 5.02 TB/s, FU = 8: 5.34 TB/s at NB = 8); the per-element operation order and the order of the energy
             // sum over f are unchanged
-            constexpr int FU = 4;
             double* p = R + fb * 3 * ld + n;
             int64_t f = fb;
             auto one = [&](double x, double y, double z, const double* wr, double* q) {
@@ -690,8 +690,18 @@ int asb_rank_update(double* R, int64_t F, int64_t N, int64_t ld, const double* W
     dim3 grid((unsigned)gx, (unsigned)ns);
     if (nb <= 4)
         rank_update_kernel<4><<<grid, 128, 0, S(stream)>>>(R, F, N, ld, Wb, ldw, Cb, (int)nb, fps, part);
-    else if (nb <= 8)
-        rank_update_kernel<8><<<grid, 128, 0, S(stream)>>>(R, F, N, ld, Wb, ldw, Cb, (int)nb, fps, part);
+    else if (nb <= 8) {
+        static const int fu = [] {
+            const char* e = std::getenv("ASB_RANK_FU");
+            return e ? std::atoi(e) : 8;   // frames in flight per thread: 8 -> 17.97 ms, 4 -> 19.13 ms per 2 S pass (B200, 1M x 2000)
+        }();
+        if (fu == 2)
+            rank_update_kernel<8, 2><<<grid, 128, 0, S(stream)>>>(R, F, N, ld, Wb, ldw, Cb, (int)nb, fps, part);
+        else if (fu == 4)
+            rank_update_kernel<8, 4><<<grid, 128, 0, S(stream)>>>(R, F, N, ld, Wb, ldw, Cb, (int)nb, fps, part);
+        else
+            rank_update_kernel<8, 8><<<grid, 128, 0, S(stream)>>>(R, F, N, ld, Wb, ldw, Cb, (int)nb, fps, part);
+    }
     else
         rank_update_kernel<16><<<grid, 128, 0, S(stream)>>>(R, F, N, ld, Wb, ldw, Cb, (int)nb, fps, part);
     ASB_LAUNCH_CHECK();
